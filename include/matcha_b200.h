@@ -1,0 +1,89 @@
+/*
+ * matcha_b200.h -- C ABI of libmatcha_b200.so (hand-written sm_100a CUDA).
+ *
+ * Plain pointers and sizes only; no torch types.  Every entry point returns 0 on
+ * success or a negative MB200_ERR_* code; matcha_b200_error_string() names it.
+ * All *_dev pointers are device pointers on the current CUDA device; `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  Device entry points
+ * are asynchronous on `stream`, re-entrant, keep no global state and allocate nothing.
+ *
+ * Reference interfaces replaced (paths under /root/reference):
+ *   matcha_b200_mas_compute_batch_alignments  <- compute_batch_alignments,
+ *        matcha/utils/monotonic_align/core.pyx:101-128 (and :16-96 per utterance)
+ *   matcha_b200_mas_lengths_from_mask         <- the two mask reductions of
+ *        maximum_path, matcha/utils/monotonic_align/__init__.py:52-53
+ *   matcha_b200_mas_maximum_path_host         <- the host-buffer round trip of
+ *        maximum_path, __init__.py:45-55 (numpy in, numpy out)
+ */
+#ifndef MATCHA_B200_H
+#define MATCHA_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MB200_OK                 0
+#define MB200_ERR_INVALID_ARG   -1   /* null pointer, non-positive size */
+#define MB200_ERR_UNSUPPORTED   -2   /* shape beyond what the kernel handles */
+#define MB200_ERR_CUDA          -3   /* a CUDA runtime/driver call failed; see matcha_b200_last_cuda_error */
+#define MB200_ERR_NO_DEVICE     -4   /* no sm_100 device current */
+
+/* element type of the alignment written by the MAS kernel (both are 4 bytes wide) */
+#define MB200_PATH_I32  0            /* int32 0/1, what core.pyx writes */
+#define MB200_PATH_F32  1            /* float 0.0/1.0, what maximum_path returns for fp32 input */
+
+const char *matcha_b200_error_string(int code);
+/* cudaError_t of the last failing CUDA call made by this thread through the library */
+int matcha_b200_last_cuda_error(void);
+/* "major.minor.patch" of the library */
+const char *matcha_b200_version(void);
+
+/*
+ * Monotonic alignment search over a batch (core.pyx:101-128).
+ *   paths_dev   [B][T_x][T_y] int32 or float (path_dtype); EVERY element is written
+ *               (0 outside the path, including padded rows/columns), so the buffer need
+ *               not be pre-zeroed (the reference requires pre-zeroing, __init__.py:49).
+ *   values_dev  [B][T_x][T_y] float log-likelihoods, C-contiguous.  NOT modified (the
+ *               reference overwrites it with cumulative scores, core.pyx:83-85; its only
+ *               caller passes a private copy, so this is not observable through maximum_path).
+ *   mask_dev    NULL, or [B][T_x][T_y] float: scores are value*mask as in __init__.py:45.
+ *               With NULL the caller asserts mask==1 on [0,t_x)x[0,t_y), which holds for the
+ *               outer product of two prefix masks built at matcha_tts.py:271.
+ *   t_xs_dev, t_ys_dev  [B] int32 valid lengths.
+ *   penalty     boundary_penalty / max_neg_val (-1e9 in the reference).
+ *   status_dev  NULL, or one int32 that receives (atomically added) the number of items
+ *               whose lengths violate 1 <= t_x <= t_y, t_x <= T_x, t_y <= T_y.  The reference
+ *               has undefined behaviour for those; here their path is all zeros.
+ */
+int matcha_b200_mas_compute_batch_alignments(
+    void *paths_dev, int path_dtype,
+    const float *values_dev, const float *mask_dev,
+    const int *t_xs_dev, const int *t_ys_dev,
+    int B, int T_x, int T_y, float penalty,
+    int *status_dev, void *stream);
+
+/* t_xs[b] = (int) sum_x mask[b][x][0],  t_ys[b] = (int) sum_y mask[b][0][y]   (__init__.py:52-53) */
+int matcha_b200_mas_lengths_from_mask(
+    const float *mask_dev, int B, int T_x, int T_y,
+    int *t_xs_dev, int *t_ys_dev, void *stream);
+
+/*
+ * Host-buffer convenience with the reference's C-level contract (core.pyx:101-107):
+ * copies values/lengths to the device, runs the kernel, copies int32 paths back and
+ * synchronises.  Returns the number of out-of-domain items (>= 0) or a negative error.
+ * Device scratch is allocated and freed inside the call.
+ */
+int matcha_b200_mas_maximum_path_host(
+    int *paths_host, const float *values_host,
+    const int *t_xs_host, const int *t_ys_host,
+    int B, int T_x, int T_y, float penalty);
+
+/* Launch geometry the MAS kernel would use for a shape (for bench/launch accounting):
+ * out[0]=grid, out[1]=block, out[2]=dynamic smem bytes, out[3]=rows per lane (R),
+ * out[4]=pipeline stages, out[5]=1 if the TMA path is taken, out[6]=CTAs per SM. */
+int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int aligned16, int out[8]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MATCHA_B200_H */

@@ -1,0 +1,71 @@
+"""ctypes binding of libmatcha_b200.so (the C ABI in include/matcha_b200.h)."""
+import ctypes
+import os
+
+_PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB = None
+
+
+class LibraryNotBuilt(RuntimeError):
+    pass
+
+
+class MatchaB200Error(RuntimeError):
+    def __init__(self, code, where):
+        lib = load_library()
+        msg = lib.matcha_b200_error_string(code).decode()
+        cuda = lib.matcha_b200_last_cuda_error()
+        super().__init__(f"{where}: {msg} (code {code}, last CUDA error {cuda})")
+        self.code = code
+
+
+def lib_path():
+    return os.path.join(_PKG_ROOT, "lib", "libmatcha_b200.so")
+
+
+def load_library():
+    """Loads the CUDA library; raises LibraryNotBuilt if it has not been compiled."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise LibraryNotBuilt(
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  matcha_b200 has no CPU fallback.")
+    lib = ctypes.CDLL(path)
+    c_int, c_void_p, c_float, c_char_p = ctypes.c_int, ctypes.c_void_p, ctypes.c_float, ctypes.c_char_p
+    lib.matcha_b200_error_string.restype = c_char_p
+    lib.matcha_b200_error_string.argtypes = [c_int]
+    lib.matcha_b200_last_cuda_error.restype = c_int
+    lib.matcha_b200_version.restype = c_char_p
+    lib.matcha_b200_mas_compute_batch_alignments.restype = c_int
+    lib.matcha_b200_mas_compute_batch_alignments.argtypes = [
+        c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_int, c_int, c_int, c_float, c_void_p, c_void_p]
+    lib.matcha_b200_mas_lengths_from_mask.restype = c_int
+    lib.matcha_b200_mas_lengths_from_mask.argtypes = [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]
+    lib.matcha_b200_mas_maximum_path_host.restype = c_int
+    lib.matcha_b200_mas_maximum_path_host.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float]
+    lib.matcha_b200_mas_query_launch.restype = c_int
+    lib.matcha_b200_mas_query_launch.argtypes = [c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int * 8)]
+    _LIB = lib
+    return lib
+
+
+def check(code, where):
+    if code < 0:
+        raise MatchaB200Error(code, where)
+    return code
+
+
+# every symbol include/matcha_b200.h declares (tests check the .so exports all of them)
+DECLARED_SYMBOLS = (
+    "matcha_b200_error_string",
+    "matcha_b200_last_cuda_error",
+    "matcha_b200_version",
+    "matcha_b200_mas_compute_batch_alignments",
+    "matcha_b200_mas_lengths_from_mask",
+    "matcha_b200_mas_maximum_path_host",
+    "matcha_b200_mas_query_launch",
+)

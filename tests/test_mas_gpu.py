@@ -1,0 +1,147 @@
+"""GPU parity tests for the MAS kernel: bit-exact against the golden vectors (made from the
+reference's compiled core.pyx) and against the C oracle on seeded inputs.  Everything goes
+through the C ABI (ctypes) behind matcha_b200.monotonic_align."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import mas as omas
+from tests.mas_cases import check_path_properties, gen, golden_case, golden_full
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ma():
+    assert torch.cuda.is_available()
+    from matcha_b200 import monotonic_align
+    return monotonic_align
+
+
+def _run(ma, v, m, **kw):
+    dev = torch.device("cuda:0")
+    out = ma.maximum_path(torch.from_numpy(v).to(dev), torch.from_numpy(m).to(dev), **kw)
+    torch.cuda.synchronize()
+    assert out.dtype == torch.float32 and out.shape == v.shape
+    o = out.cpu().numpy()
+    assert np.isin(o, (0.0, 1.0)).all()
+    return o.astype(np.int32)
+
+
+@pytest.mark.parametrize("name", sorted(gen.cases().keys()))
+def test_golden_full_mask_mode(ma, mas_golden, name):
+    v, m, p = golden_case(mas_golden, name)
+    assert np.array_equal(_run(ma, v, m, mask_mode="full"), p)
+
+
+@pytest.mark.parametrize("name", sorted(k for k in gen.cases().keys() if k != "holey_mask"))
+def test_golden_prefix_mask_mode(ma, mas_golden, name):
+    v, m, p = golden_case(mas_golden, name)
+    assert np.array_equal(_run(ma, v, m, mask_mode="prefix"), p)
+
+
+def test_golden_config1_full_size(ma, mas_golden):
+    v, m, p = golden_full(mas_golden)
+    assert np.array_equal(_run(ma, v, m, mask_mode="prefix"), p)
+    assert np.array_equal(_run(ma, v, m, mask_mode="full"), p)
+
+
+@pytest.mark.parametrize("name", ["randn_ragged", "quantised_ties", "tile_edges", "tall_450x520"])
+def test_host_buffer_c_abi_matches_golden(ma, mas_golden, name):
+    # compute_batch_alignments(paths, values, t_xs, t_ys) with numpy buffers, as core.pyx:101-107
+    v, m, p = golden_case(mas_golden, name)
+    vals = np.ascontiguousarray((v * m).astype(np.float32))
+    keep = vals.copy()
+    paths = np.full(v.shape, 7, dtype=np.int32)          # need not be pre-zeroed
+    t_x, t_y = m.sum(1)[:, 0].astype(np.int32), m.sum(2)[:, 0].astype(np.int32)
+    bad = ma.compute_batch_alignments(paths, vals, t_x, t_y)
+    assert bad == 0 and np.array_equal(paths, p)
+    assert np.array_equal(vals.view(np.uint32), keep.view(np.uint32)), "values must not be clobbered"
+
+
+SHAPES = [  # (B, T_x, T_y): every rows-per-lane variant, TMA and non-TMA (T_y % 4 != 0), multi row block
+    (3, 20, 64), (5, 70, 333), (4, 130, 404), (3, 200, 1000), (2, 260, 801), (2, 330, 700),
+    (2, 400, 2000), (2, 450, 1203), (1, 900, 1500), (9, 31, 32), (2, 1, 5), (3, 97, 97),
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("ties", [False, True])
+def test_random_vs_oracle(ma, shape, ties):
+    B, T_x, T_y = shape
+    rng = np.random.default_rng(hash((B, T_x, T_y, ties)) % (2 ** 31))
+    v = rng.standard_normal((B, T_x, T_y), dtype=np.float32)
+    if ties:
+        v = np.round(v * 2).astype(np.float32)
+    m = gen.ragged_mask(rng, B, T_x, T_y, lo=0.5)
+    want = omas.maximum_path_oracle(v, m)
+    for mode in ("prefix", "full"):
+        got = _run(ma, v, m, mask_mode=mode)
+        assert np.array_equal(got, want), f"{shape} ties={ties} mode={mode}"
+
+
+def test_int32_paths_and_unaligned_base(ma):
+    rng = np.random.default_rng(5)
+    B, T_x, T_y = 3, 40, 120
+    dev = torch.device("cuda:0")
+    big = torch.from_numpy(rng.standard_normal(B * T_x * T_y + 1, dtype=np.float32)).to(dev)
+    v = big[1:].view(B, T_x, T_y)                       # 4-byte aligned only -> cp.async path
+    assert v.data_ptr() % 16 != 0
+    m = gen.ragged_mask(rng, B, T_x, T_y)
+    t_x = torch.from_numpy(m.sum(1)[:, 0].astype(np.int32)).to(dev)
+    t_y = torch.from_numpy(m.sum(2)[:, 0].astype(np.int32)).to(dev)
+    got = ma.maximum_path_from_lengths(v, t_x, t_y, out_dtype=torch.int32)
+    want = omas.maximum_path_oracle(v.cpu().numpy(), m)
+    assert got.dtype == torch.int32 and np.array_equal(got.cpu().numpy(), want)
+
+
+def test_out_of_domain_lengths_give_zero_path_and_status(ma):
+    dev = torch.device("cuda:0")
+    v = torch.randn(4, 8, 8, device=dev)
+    t_x = torch.tensor([0, 8, 3, 9], dtype=torch.int32, device=dev)
+    t_y = torch.tensor([8, 7, 8, 8], dtype=torch.int32, device=dev)
+    out = ma.maximum_path_from_lengths(v, t_x, t_y)
+    assert out[[0, 1, 3]].abs().sum().item() == 0 and out[2].sum().item() == 8
+    with pytest.raises(ValueError):
+        ma.maximum_path_from_lengths(v, t_x, t_y, check_lengths=True)
+
+
+def test_half_precision_and_cpu_tensor_inputs(ma):
+    rng = np.random.default_rng(11)
+    v = rng.standard_normal((2, 12, 40), dtype=np.float32)
+    m = gen.ragged_mask(rng, 2, 12, 40)
+    vh = torch.from_numpy(v).half()
+    want = omas.maximum_path_oracle((vh * torch.from_numpy(m).half()).float().numpy(), m)
+    out = ma.maximum_path(vh.cuda(), torch.from_numpy(m).half().cuda())
+    assert out.dtype == torch.float16 and np.array_equal(out.float().cpu().numpy().astype(np.int32), want)
+    out_cpu = ma.maximum_path(torch.from_numpy(v), torch.from_numpy(m))   # CPU in -> CPU out, computed on the GPU
+    assert out_cpu.device.type == "cpu"
+    assert np.array_equal(out_cpu.numpy().astype(np.int32), omas.maximum_path_oracle(v, m))
+
+
+@pytest.mark.parametrize("shape", [(64, 400, 2000), (512, 128, 800)])
+def test_full_size_properties_and_sampled_parity(ma, shape):
+    """BASELINE.json configs[1] sizes: invariants on every item, oracle parity on a sample."""
+    B, T_x, T_y = shape
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev); g.manual_seed(3)
+    v = torch.randn(B, T_x, T_y, device=dev, generator=g)
+    rng = np.random.default_rng(9)
+    t_x = np.maximum(1, (T_x * (0.7 + 0.3 * rng.random(B))).astype(np.int32))
+    t_y = np.maximum(t_x, (T_y * (0.7 + 0.3 * rng.random(B))).astype(np.int32)).astype(np.int32)
+    out = ma.maximum_path_from_lengths(v, torch.from_numpy(t_x).to(dev), torch.from_numpy(t_y).to(dev),
+                                       out_dtype=torch.int32)
+    again = ma.maximum_path_from_lengths(v, torch.from_numpy(t_x).to(dev), torch.from_numpy(t_y).to(dev),
+                                         out_dtype=torch.int32)
+    assert torch.equal(out, again), "deterministic"
+    # column sums / durations on the device, then the full invariants on a sample
+    col = out.sum(1)
+    yy = torch.arange(T_y, device=dev)[None, :]
+    assert torch.equal(col, (yy < torch.from_numpy(t_y).to(dev)[:, None]).to(col.dtype))
+    idx = list(range(0, B, max(1, B // 16)))
+    sub = out[idx].cpu().numpy()
+    check_path_properties(sub, t_x[idx], t_y[idx])
+    vs = np.ascontiguousarray(v[idx].cpu().numpy())
+    want = np.zeros(vs.shape, np.int32)
+    omas.oracle_compute_batch_alignments(want, vs, t_x[idx], t_y[idx])
+    assert np.array_equal(sub, want)
