@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel-only", action="store_true", help="profiling aid: skip the e2e and CPU-baseline legs")
     return ap.parse_args()
 
 
@@ -223,6 +224,14 @@ def run_ours(a):
     total_ms = float(t.item())
     ms_per_step = total_ms / a.steps
     value_rate = world * B / (ms_per_step / 1e3)
+
+    if a.kernel_only:
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "value": value_rate, "unit": UNIT, "ms_per_step": ms_per_step,
+                              "kernel_only": True}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # e2e: pinned numpy buffers through the core.pyx-shaped host entry (H2D + kernel + D2H per call)
     vh = torch.empty(B, T_x, T_y, dtype=torch.float32).pin_memory()
