@@ -4,21 +4,27 @@
 // mel frames with the "ties go to token x-1" rule of :73, then the backtrack of :87-92).
 // Results are bit-exact with the compiled reference; see DESIGN.md §MAS for the argument.
 //
-// Shape of the kernel (one persistent CTA = 6 warps, utterances dealt round-robin):
-//   warp 0  DP warp.  Lane l owns R consecutive tokens (rows) x0..x0+R-1 of the current
-//           row block (32*R tokens); one step per mel frame (column): a single shfl_up
-//           brings Q[y-1][x0-1] from lane l-1, the other R-1 predecessors are registers.
-//           The "came from x-1" bit of every cell is packed 32 frames per word and kept in
-//           shared memory, so the backtrack never leaves the SM.
-//   warp 1  producer.  Streams the fp32 score tile of each 32-frame chunk (only the rows
-//           inside the DP band) into a ring of 128B-swizzled stages with TMA
-//           (cp.async.bulk.tensor, completion on an mbarrier); when the tensor breaks
-//           TMA's 16-byte rules (T_y % 4 != 0 or a misaligned base) the same warp fills
-//           the same layout with 4-byte cp.async.
-//   warps 2-5  writers.  Turn the per-token start frames found by the backtrack into the
-//           dense 0/1 alignment with 16-byte streaming stores, overlapping the DP of the
-//           CTA's next utterance.
+// One persistent CTA per SM slot, utterances dealt round-robin.  Warp roles:
+//   warps 0..NDP-1  DP warps, an anti-diagonal wavefront over (row block, 32-frame chunk):
+//           warp w owns tokens [32*R*w, 32*R*(w+1)); lane l owns R consecutive tokens.  One
+//           step per mel frame: a single shfl_up brings Q[y-1][x0-1] from lane l-1, the other
+//           R-1 predecessors are registers.  Warp w runs one chunk behind warp w-1 and gets the
+//           boundary row Q[.][32*R*w-1] through a 2-deep shared-memory ring guarded by
+//           mbarriers.  The "came from x-1" bit of every cell is packed 32 frames per word
+//           and kept in shared memory, so the backtrack never leaves the SM.
+//   warp NDP        producer.  Streams the fp32 score rows each DP warp needs for its next
+//           chunk (only rows inside the DP band) into per-warp rings of 128B-swizzled
+//           stages with TMA (cp.async.bulk.tensor, completion on an mbarrier), in the
+//           wavefront's own order; when the tensor breaks TMA's 16-byte rules
+//           (T_y % 4 != 0 or a misaligned base) the same warp fills the same layout with
+//           4-byte cp.async.
+//   last 4 warps    writers.  Turn the per-token start frames found by the backtrack into
+//           the dense 0/1 alignment with 16-byte streaming stores, overlapping the DP of
+//           the CTA's next utterance.
 #include "common.cuh"
+
+#include <stdlib.h>
+#include <string.h>
 
 namespace mb200 {
 
@@ -26,8 +32,14 @@ constexpr int kChunk = 32;        // mel frames per tile
 constexpr int kBoxRows = 32;      // tokens per TMA box
 constexpr int kBoxBytes = kBoxRows * kChunk * 4;
 constexpr int kWriterWarps = 4;
-constexpr int kThreads = 32 * (2 + kWriterWarps);
 constexpr int kMaxStages = 8;
+constexpr int kBndDepth = 2;      // boundary-row ring depth between neighbouring DP warps
+constexpr int kBndFloats = 36;    // [0]=Q[32c-1], [1..32]=Q[32c..32c+31], padded to 16 bytes
+
+// most DP warps a CTA may carry for a given rows-per-lane (register budget of the SM)
+__host__ __device__ constexpr int max_dp_warps(int R) {
+    return R <= 3 ? 14 : (R <= 5 ? 8 : (R <= 7 ? 6 : (R <= 9 ? 4 : 3)));
+}
 
 struct MasParams {
     const float *value;
@@ -39,12 +51,13 @@ struct MasParams {
     int B, T_x, T_y;
     float penalty;
     uint32_t one_bits;   // bit pattern of "1" in the output element type
-    int nstage;
-    int txp;             // row pitch of the bit matrix (multiple of 32*R)
+    int ndp;             // DP warps in the CTA
+    int nstage;          // ring depth per DP warp
+    int txp;             // T_x rounded up to 32: row pitch of the bit matrix and of a stage
     int n_chunks;        // ceil(T_y / 32)
     int use_tma;
     int vec_store;       // output rows are 16-byte aligned
-    int multi;           // more than one row block per utterance may occur
+    int bits_global;     // bit matrix too big for shared memory: keep it in the utterance's own output region
 };
 
 struct ItemInfo { int tx, ty, valid, pad; };
@@ -62,18 +75,28 @@ __device__ __forceinline__ void rb_chunk_range(int r0, int r1, int tx, int ty, i
     c1 = y_last / kChunk;
 }
 
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
+
 // ------------------------------------------------------------------ DP over one chunk
+// `stage` points at this warp's first row inside the stage.  has_prev: lane 0 takes
+// Q[y-1][x0-1] from the boundary slot `bin` written by the previous warp; put_next: lane 31
+// publishes its last row into `bout` for the next warp.
 template <int R, bool HAS_MASK, bool DIAG>
 __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uint32_t stage,
-                                         int lane, int y_base, int x0, float penalty,
-                                         bool multi, bool first_rb, uint32_t bin, uint32_t bout) {
+                                         uint32_t mask_off, int rows_avail, int lane, int y_base,
+                                         int x0, float penalty, bool has_prev, uint32_t bin,
+                                         bool put_next, uint32_t bout) {
     uint32_t row_addr[R], row_sw[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        int rho = R * lane + r;
+        int rho = min(R * lane + r, rows_avail - 1);   // rows past the stage re-read its last row (never used)
         row_addr[r] = stage + rho * 128;
         row_sw[r] = (rho & 7) << 4;
     }
+    float *bo = reinterpret_cast<float *>(__cvta_shared_to_generic(bout));
+    if (put_next && lane == 31) bo[0] = q[R - 1];
 #pragma unroll 1
     for (int g = 0; g < 8; ++g) {
         float4 v[R];
@@ -82,13 +105,13 @@ __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uin
             uint32_t a = row_addr[r] + ((uint32_t)(g << 4) ^ row_sw[r]);
             v[r] = lds128(a);
             if (HAS_MASK) {
-                float4 m = lds128(a + R * kBoxBytes);
+                float4 m = lds128(a + mask_off);
                 v[r].x *= m.x; v[r].y *= m.y; v[r].z *= m.z; v[r].w *= m.w;
             }
         }
         const int y0 = y_base + 4 * g;
         float4 upv = make_float4(0.f, 0.f, 0.f, 0.f), outv = upv;
-        if (multi && !first_rb && lane == 0) upv = lds128(bin + y0 * 4);
+        if (has_prev && lane == 0) upv = lds128(bin + 16 * g);
         const uint32_t mg = 1u << (4 * g);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -96,7 +119,7 @@ __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uin
             const uint32_t mj = mg << j;
             float up = __shfl_up_sync(0xffffffffu, q[R - 1], 1);
             if (lane == 0) {
-                if (multi && !first_rb) up = (j == 0) ? upv.x : (j == 1) ? upv.y : (j == 2) ? upv.z : upv.w;
+                if (has_prev) up = (j == 0) ? upv.x : (j == 1) ? upv.y : (j == 2) ? upv.z : upv.w;
                 else up = (y == 0) ? 0.0f : penalty;             // core.pyx:63-64
             }
             const int dy = y - x0;
@@ -111,14 +134,11 @@ __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uin
                 q[r] = __fadd_rn(best, s);                       // core.pyx:80
                 bits[r] |= d ? mj : 0u;                          // core.pyx:75,78
             }
-            if (multi) {
-                if (j == 0) outv.x = q[R - 1]; else if (j == 1) outv.y = q[R - 1];
-                else if (j == 2) outv.z = q[R - 1]; else outv.w = q[R - 1];
-            }
+            if (j == 0) outv.x = q[R - 1]; else if (j == 1) outv.y = q[R - 1];
+            else if (j == 2) outv.z = q[R - 1]; else outv.w = q[R - 1];
         }
-        if (multi && lane == 31) {
-            // Q[y][last row of the block] is what the next block reads as Q[y'-1][x0-1] at y' = y+1
-            float *o = reinterpret_cast<float *>(__cvta_shared_to_generic(bout)) + y0 + 1;
+        if (put_next && lane == 31) {
+            float *o = bo + 1 + 4 * g;
             o[0] = outv.x; o[1] = outv.y; o[2] = outv.z; o[3] = outv.w;
         }
     }
@@ -126,56 +146,68 @@ __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uin
 
 // ------------------------------------------------------------------ shared-memory carve-up
 struct MasSmem {
-    uint32_t stages;   // nstage * stage_bytes, 1024-aligned
+    uint32_t stages;   // nstage stage sets of txp rows x 128 B (x2 with a mask), 1024-aligned
     uint32_t bits;     // n_chunks * txp words
-    uint32_t qb;       // 2 * n_chunks*32 floats (row-block boundary rows), only if multi
+    uint32_t bnd;      // (ndp-1) * kBndDepth * kBndFloats floats
     uint32_t cs;       // 2 * (txp + 4) ints: start frame of every token (+ end sentinel)
     uint32_t info;     // 2 * ItemInfo
-    uint32_t bars;     // full[nstage], empty[nstage], bfull[2], bempty[2]
+    uint32_t itw;      // ndp ints: producer's per-ring fill counters
+    uint32_t bars;     // full/empty [ndp*nstage], bdfull/bdempty [(ndp-1)*depth], bfull/bempty [2]
+    uint32_t stage_bytes;
     uint32_t total;
 };
 
-__host__ __device__ inline MasSmem mas_smem_layout(int R, bool has_mask, int nstage, int txp,
-                                                   int n_chunks, bool multi) {
+__host__ __device__ inline MasSmem mas_smem_layout(bool has_mask, int ndp, int nstage, int txp,
+                                                   int n_chunks, bool bits_global) {
     MasSmem s;
     uint32_t off = 0;
-    const uint32_t stage_bytes = (uint32_t)R * kBoxBytes * (has_mask ? 2 : 1);
-    s.stages = off; off += (uint32_t)nstage * stage_bytes;
-    s.bits = off;   off += (uint32_t)n_chunks * (uint32_t)txp * 4u;
-    s.qb = off;     off += multi ? 2u * (uint32_t)(n_chunks * kChunk + 4) * 4u : 0u;
+    s.stage_bytes = (uint32_t)txp * 128u * (has_mask ? 2u : 1u);
+    s.stages = off; off += (uint32_t)nstage * s.stage_bytes;
+    s.bits = off;   off += bits_global ? 0u : (uint32_t)n_chunks * (uint32_t)txp * 4u;
+    s.bnd = off;    off += (uint32_t)(ndp - 1) * kBndDepth * kBndFloats * 4u;
     s.cs = off;     off += 2u * (uint32_t)(txp + 4) * 4u;
     s.info = off;   off += 2u * (uint32_t)sizeof(ItemInfo);
+    s.itw = off;    off += ((uint32_t)ndp * 4u + 15u) & ~15u;
     off = (off + 7u) & ~7u;
-    s.bars = off;   off += (2u * (uint32_t)nstage + 4u) * 8u;
+    s.bars = off;
+    off += (2u * (uint32_t)ndp * (uint32_t)nstage + 2u * (uint32_t)(ndp - 1) * kBndDepth + 4u) * 8u;
     s.total = off + 1024u;   // slack for the manual 1024-byte alignment of the base
     return s;
 }
 
 // ------------------------------------------------------------------ the kernel
 template <int R, bool HAS_MASK>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(32 * (max_dp_warps(R) + 1 + kWriterWarps))
 mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_m,
            const MasParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-    const MasSmem L = mas_smem_layout(R, HAS_MASK, p.nstage, p.txp, p.n_chunks, p.multi != 0);
+    const MasSmem L = mas_smem_layout(HAS_MASK, p.ndp, p.nstage, p.txp, p.n_chunks, p.bits_global != 0);
     constexpr int RB = 32 * R;
-    constexpr uint32_t kStageBytes = (uint32_t)R * kBoxBytes * (HAS_MASK ? 2 : 1);
+    const int ndp = p.ndp, nstage = p.nstage;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t bar_full = base + L.bars;
-    const uint32_t bar_empty = bar_full + 8u * p.nstage;
-    const uint32_t bar_bfull = bar_empty + 8u * p.nstage;
-    const uint32_t bar_bempty = bar_bfull + 16u;
-    uint32_t *bits_g = reinterpret_cast<uint32_t *>(gbase + L.bits);
+    // barrier addresses
+    const uint32_t bar_full = base + L.bars;                               // [w][s]
+    const uint32_t bar_empty = bar_full + 8u * ndp * nstage;               // [w][s]
+    const uint32_t bar_bdfull = bar_empty + 8u * ndp * nstage;             // [w][d], w < ndp-1
+    const uint32_t bar_bdempty = bar_bdfull + 8u * (ndp - 1) * kBndDepth;  // [w][d]
+    const uint32_t bar_bfull = bar_bdempty + 8u * (ndp - 1) * kBndDepth;   // [2]
+    const uint32_t bar_bempty = bar_bfull + 16u;                           // [2]
+    uint32_t *bits_smem = reinterpret_cast<uint32_t *>(gbase + L.bits);
     int *cs_g = reinterpret_cast<int *>(gbase + L.cs);
     ItemInfo *info_g = reinterpret_cast<ItemInfo *>(gbase + L.info);
+    const uint32_t mask_off = (uint32_t)p.txp * 128u;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.nstage; ++s) {
-            mbar_init(bar_full + 8u * s, p.use_tma ? 1u : 32u);
-            mbar_init(bar_empty + 8u * s, 1u);
+        for (int i = 0; i < ndp * nstage; ++i) {
+            mbar_init(bar_full + 8u * i, p.use_tma ? 1u : 32u);
+            mbar_init(bar_empty + 8u * i, 1u);
+        }
+        for (int i = 0; i < (ndp - 1) * kBndDepth; ++i) {
+            mbar_init(bar_bdfull + 8u * i, 1u);
+            mbar_init(bar_bdempty + 8u * i, 1u);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar_bfull + 8u * i, 1u);
@@ -185,30 +217,40 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
     }
     __syncthreads();
 
-    if (warp == 1) {
+    if (warp == ndp) {
         // ============================ producer ============================
         if (p.use_tma && lane == 0) {
             tma_prefetch_desc(&tmap_v);
             if (HAS_MASK) tma_prefetch_desc(&tmap_m);
         }
-        uint32_t it = 0;
+        uint32_t *itw = reinterpret_cast<uint32_t *>(gbase + L.itw);
+        if (lane < ndp) itw[lane] = 0u;
+        __syncwarp();
         for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
             const int tx = p.t_xs[b], ty = p.t_ys[b];
             if (!lengths_valid(tx, ty, p.T_x, p.T_y)) continue;
-            const int n_rb = (tx + RB - 1) / RB;
-            for (int rb = 0; rb < n_rb; ++rb) {
-                const int r0 = rb * RB, r1 = min(r0 + RB, tx);
-                int c0, c1;
-                rb_chunk_range(r0, r1, tx, ty, c0, c1);
-                for (int c = c0; c <= c1; ++c, ++it) {
-                    const uint32_t s = it % (uint32_t)p.nstage, ph = (it / (uint32_t)p.nstage) & 1u;
-                    const uint32_t stage = base + L.stages + s * kStageBytes;
-                    const uint32_t full = bar_full + 8u * s;
+            const int n_act = (tx + RB - 1) / RB;
+            int cz0, t_end;
+            rb_chunk_range((n_act - 1) * RB, tx, tx, ty, cz0, t_end);
+            t_end += n_act - 1;
+            // wavefront order: DP warp w reaches chunk c at step t = c + w
+            for (int t = 0; t <= t_end; ++t) {
+                const int w_hi = min(n_act - 1, t);
+                for (int w = 0; w <= w_hi; ++w) {
+                    const int c = t - w;
+                    const int r0 = w * RB, r1 = min(r0 + RB, tx);
+                    int c0, c1;
+                    rb_chunk_range(r0, r1, tx, ty, c0, c1);
+                    if (c < c0 || c > c1) continue;
+                    const uint32_t it = itw[w];
+                    const uint32_t s = it % (uint32_t)nstage, ph = (it / (uint32_t)nstage) & 1u;
+                    const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
+                    const uint32_t full = bar_full + 8u * (w * nstage + s);
                     // rows of this block inside the band over frames [32c, 32c+32)
                     const int lo = max(r0, tx + kChunk * c - ty);
                     const int hi = min(r1, kChunk * c + kChunk);
                     const int j0 = (lo - r0) / kBoxRows, j1 = (hi - 1 - r0) / kBoxRows;
-                    if (lane == 0) mbar_wait(bar_empty + 8u * s, ph ^ 1u);
+                    if (lane == 0) mbar_wait_sleep(bar_empty + 8u * (w * nstage + s), ph ^ 1u, 20);
                     __syncwarp();
                     if (p.use_tma) {
                         if (lane == 0) {
@@ -217,7 +259,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                                 const int row = b * p.T_x + r0 + kBoxRows * j;
                                 tma_load_2d(stage + j * kBoxBytes, &tmap_v, full, kChunk * c, row);
                                 if (HAS_MASK)
-                                    tma_load_2d(stage + (R + j) * kBoxBytes, &tmap_m, full, kChunk * c, row);
+                                    tma_load_2d(stage + mask_off + j * kBoxBytes, &tmap_m, full, kChunk * c, row);
                             }
                         }
                     } else {
@@ -228,90 +270,120 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                                 const size_t g = ((size_t)b * p.T_x + r0 + rho) * (size_t)p.T_y + col;
                                 const uint32_t d = stage + rho * 128 + ((((uint32_t)lane >> 2) ^ (rho & 7)) << 4) + (lane & 3) * 4;
                                 cp_async_4(d, p.value + g);
-                                if (HAS_MASK) cp_async_4(d + R * kBoxBytes, p.mask + g);
+                                if (HAS_MASK) cp_async_4(d + mask_off, p.mask + g);
                             }
                         }
                         cp_async_mbar_arrive_noinc(full);
                     }
+                    __syncwarp();
+                    if (lane == 0) itw[w] = it + 1u;
+                    __syncwarp();
                 }
             }
         }
-    } else if (warp == 0) {
-        // ============================ DP + backtrack ============================
-        uint32_t it = 0, k = 0;
+    } else if (warp < ndp) {
+        // ============================ DP wavefront + backtrack ============================
+        const int w = warp;
+        uint32_t it = 0, hin = 0, hout = 0, k = 0;
+        const int r0 = w * RB;
+        const int x0 = r0 + R * lane;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const int tx = p.t_xs[b], ty = p.t_ys[b];
             const bool valid = lengths_valid(tx, ty, p.T_x, p.T_y);
             const uint32_t buf = k & 1u;
             int *cs = cs_g + buf * (p.txp + 4);
-            if (lane == 0) mbar_wait(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u);
-            __syncwarp();
+            // generic pointer: shared memory, or (fallback) the start of this utterance's output
+            uint32_t *bits_g = p.bits_global ? (p.out + (size_t)b * p.T_x * p.T_y) : bits_smem;
             if (valid) {
-                const int n_rb = (tx + RB - 1) / RB;
-                for (int rb = 0; rb < n_rb; ++rb) {
-                    const int r0 = rb * RB, r1 = min(r0 + RB, tx);
-                    int c0, c1;
+                const int n_act = (tx + RB - 1) / RB;
+                if (w < n_act) {
+                    const int r1 = min(r0 + RB, tx);
+                    int c0, c1, c0p = 0, c1p = -1;
                     rb_chunk_range(r0, r1, tx, ty, c0, c1);
-                    const int cd = (r1 - 1) / kChunk;      // last chunk that holds a diagonal cell
-                    const uint32_t bin = base + L.qb + ((rb & 1) ^ 1) * (uint32_t)(p.n_chunks * kChunk + 4) * 4u;
-                    const uint32_t bout = base + L.qb + (rb & 1) * (uint32_t)(p.n_chunks * kChunk + 4) * 4u;
-                    const int x0 = r0 + R * lane;
+                    if (w > 0) rb_chunk_range(r0 - RB, r0, tx, ty, c0p, c1p);
+                    const bool has_prev = w > 0, has_next = (w + 1 < n_act);
+                    const int c0n = (r0 + RB) / kChunk;     // first chunk of the next warp
+                    const int cd = (r1 - 1) / kChunk;       // last chunk that holds a diagonal cell
                     float q[R];
                     uint32_t bits[R];
 #pragma unroll
                     for (int r = 0; r < R; ++r) q[r] = p.penalty;      // core.pyx:52-53
                     for (int c = c0; c <= c1; ++c, ++it) {
-                        const uint32_t s = it % (uint32_t)p.nstage, ph = (it / (uint32_t)p.nstage) & 1u;
-                        const uint32_t stage = base + L.stages + s * kStageBytes;
+                        const uint32_t s = it % (uint32_t)nstage, ph = (it / (uint32_t)nstage) & 1u;
+                        const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
+                        const bool in_h = has_prev && c <= c1p;
+                        const bool out_h = has_next && c >= c0n;
+                        const uint32_t din = hin % kBndDepth, dout = hout % kBndDepth;
+                        const uint32_t bin = base + L.bnd + (((w - 1) * kBndDepth + din) * kBndFloats) * 4u;
+                        const uint32_t bout = base + L.bnd + ((w * kBndDepth + dout) * kBndFloats) * 4u;
 #pragma unroll
                         for (int r = 0; r < R; ++r) bits[r] = 0u;
-                        mbar_wait(bar_full + 8u * s, ph);
-                        if (c <= cd)
-                            dp_chunk<R, HAS_MASK, true>(q, bits, stage, lane, kChunk * c, x0, p.penalty,
-                                                        p.multi != 0, rb == 0, bin, bout);
-                        else
-                            dp_chunk<R, HAS_MASK, false>(q, bits, stage, lane, kChunk * c, x0, p.penalty,
-                                                         p.multi != 0, rb == 0, bin, bout);
-                        uint32_t *w = bits_g + (size_t)c * p.txp + x0;
-#pragma unroll
-                        for (int r = 0; r < R; ++r) w[r] = bits[r];
+                        mbar_wait(bar_full + 8u * (w * nstage + s), ph);
+                        if (in_h && lane == 0)
+                            mbar_wait(bar_bdfull + 8u * ((w - 1) * kBndDepth + din), (hin / kBndDepth) & 1u);
+                        if (out_h && lane == 31)
+                            mbar_wait(bar_bdempty + 8u * (w * kBndDepth + dout), ((hout / kBndDepth) & 1u) ^ 1u);
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(bar_empty + 8u * s);
+                        if (c <= cd)
+                            dp_chunk<R, HAS_MASK, true>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
+                                                        has_prev, bin, out_h, bout);
+                        else
+                            dp_chunk<R, HAS_MASK, false>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
+                                                         has_prev, bin, out_h, bout);
+                        uint32_t *wd = bits_g + (size_t)c * p.txp + x0;
+#pragma unroll
+                        for (int r = 0; r < R; ++r)
+                            if (x0 + r < p.txp) wd[r] = bits[r];
+                        __syncwarp();
+                        if (lane == 0) {
+                            mbar_arrive(bar_empty + 8u * (w * nstage + s));
+                            if (in_h) mbar_arrive(bar_bdempty + 8u * ((w - 1) * kBndDepth + din));
+                        }
+                        if (out_h && lane == 31) mbar_arrive(bar_bdfull + 8u * (w * kBndDepth + dout));
+                        hin += in_h ? 1u : 0u;
+                        hout += out_h ? 1u : 0u;
                     }
                 }
+                // every DP warp has stored its bits before the backtrack reads them
                 __syncwarp();
-                if (lane == 0) {
+                asm volatile("bar.sync 1, %0;" ::"r"(ndp * 32) : "memory");
+                if (w == 0 && lane == 0) {
+                    mbar_wait_sleep(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 64);
                     // backtrack, core.pyx:87-92: token idx owns frames [cs[idx], cs[idx+1])
                     int idx = tx - 1, y = ty - 1;
                     cs[tx] = ty;
                     while (idx > 0) {
                         int c = y >> 5;
-                        uint32_t w = bits_g[(size_t)c * p.txp + idx] & (0xffffffffu >> (31 - (y & 31)));
-                        while (w == 0u) { --c; w = bits_g[(size_t)c * p.txp + idx]; }
-                        const int yp = (c << 5) + 31 - __clz(w);
+                        const volatile uint32_t *bv = bits_g;
+                        uint32_t wv = bv[(size_t)c * p.txp + idx] & (0xffffffffu >> (31 - (y & 31)));
+                        while (wv == 0u) { --c; wv = bv[(size_t)c * p.txp + idx]; }
+                        const int yp = (c << 5) + 31 - __clz(wv);
                         cs[idx] = yp;
                         y = yp - 1;
                         --idx;
                     }
                     cs[0] = 0;
+                    info_g[buf].tx = tx; info_g[buf].ty = ty; info_g[buf].valid = 1;
+                    mbar_arrive(bar_bfull + 8u * buf);
                 }
-            } else if (lane == 0 && p.status != nullptr) {
-                atomicAdd(p.status, 1);
-            }
-            if (lane == 0) {
-                info_g[buf].tx = tx; info_g[buf].ty = ty; info_g[buf].valid = valid ? 1 : 0;
+                // the next utterance's DP may overwrite the bit matrix only after the backtrack
+                __syncwarp();
+                asm volatile("bar.sync 1, %0;" ::"r"(ndp * 32) : "memory");
+            } else if (w == 0 && lane == 0) {
+                mbar_wait_sleep(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 64);
+                if (p.status != nullptr) atomicAdd(p.status, 1);
+                info_g[buf].tx = 0; info_g[buf].ty = 0; info_g[buf].valid = 0;
                 mbar_arrive(bar_bfull + 8u * buf);
             }
-            __syncwarp();
         }
     } else {
         // ============================ writers ============================
-        const int ww = warp - 2;
+        const int ww = warp - ndp - 1;
         uint32_t k = 0;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const uint32_t buf = k & 1u;
             const int *cs = cs_g + buf * (p.txp + 4);
-            mbar_wait(bar_bfull + 8u * buf, (k >> 1) & 1u);
+            mbar_wait_sleep(bar_bfull + 8u * buf, (k >> 1) & 1u, 200);
             const int tx = info_g[buf].valid ? info_g[buf].tx : 0;
             uint32_t *out = p.out + (size_t)b * p.T_x * p.T_y;
             const uint32_t one = p.one_bits;
@@ -320,14 +392,15 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                     int s = 0, e = 0;
                     if (x < tx) { s = cs[x]; e = cs[x + 1]; }
                     uint4 *row = reinterpret_cast<uint4 *>(out + (size_t)x * p.T_y);
-                    for (int c4 = lane; c4 * 4 < p.T_y; c4 += 32) {
-                        const int c = c4 * 4;
-                        uint4 v;
-                        v.x = (c + 0 >= s && c + 0 < e) ? one : 0u;
-                        v.y = (c + 1 >= s && c + 1 < e) ? one : 0u;
-                        v.z = (c + 2 >= s && c + 2 < e) ? one : 0u;
-                        v.w = (c + 3 >= s && c + 3 < e) ? one : 0u;
-                        __stcs(row + c4, v);
+                    for (int c = lane * 4; c < p.T_y; c += 128) {
+                        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                        if (c + 3 >= s && c < e) {
+                            v.x = (c + 0 >= s && c + 0 < e) ? one : 0u;
+                            v.y = (c + 1 >= s && c + 1 < e) ? one : 0u;
+                            v.z = (c + 2 >= s && c + 2 < e) ? one : 0u;
+                            v.w = (c + 3 >= s && c + 3 < e) ? one : 0u;
+                        }
+                        __stcs(row + (c >> 2), v);
                     }
                 }
             } else {
@@ -372,37 +445,51 @@ mas_lengths_kernel(const float *__restrict__ mask, int T_x, int T_y, int *__rest
 namespace mb200 {
 
 struct MasPlan {
-    int R, nstage, txp, n_chunks, multi, use_tma, vec_store;
+    int R, ndp, nstage, txp, n_chunks, use_tma, vec_store, threads, bits_global;
     uint32_t smem;
 };
 
-// Ring depth: enough bytes in flight per CTA (~64 KB) without hogging the SM, so that small
-// shapes co-reside several CTAs per SM; at least 3 stages when they fit.
-static int stage_cap(int R, bool has_mask) {
-    const int stage_bytes = R * kBoxBytes * (has_mask ? 2 : 1);
-    int ns = (64 * 1024) / stage_bytes;
-    if (ns < 3) ns = 3;
-    if (ns > kMaxStages) ns = kMaxStages;
-    return ns;
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
 }
 
-// Picks rows-per-lane R (odd, so the 128B-swizzled LDS.128 pattern is conflict-free) and the
-// pipeline depth that fit 227 KB next to the bit matrix.  Prefers a single row block.
+// Picks rows-per-lane R (odd, so the 128B-swizzled LDS.128 pattern is conflict-free), the
+// number of DP warps and the ring depth that fit 227 KB next to the bit matrix.
+// Tuning overrides (experiments only): MB200_MAS_R, MB200_MAS_NDP_PREF, MB200_MAS_NSTAGE.
 static int mas_make_plan(int T_x, int T_y, bool has_mask, bool aligned16, MasPlan *pl) {
     const int n_chunks = (T_y + kChunk - 1) / kChunk;
-    int r_fit = (T_x + 31) / 32;
-    if ((r_fit & 1) == 0) r_fit += 1;
-    if (r_fit > 13) r_fit = 13;
-    for (int R = r_fit; R >= 1; R -= 2) {
-        const int rb = 32 * R;
-        const int txp = (T_x + rb - 1) / rb * rb;
-        const bool multi = txp > rb;
-        for (int ns = stage_cap(R, has_mask); ns >= 2; --ns) {
-            MasSmem L = mas_smem_layout(R, has_mask, ns, txp, n_chunks, multi);
+    const int g = (T_x + 31) / 32, txp = 32 * g;
+    const int pref = env_int("MB200_MAS_NDP_PREF", 4);
+    int R = env_int("MB200_MAS_R", 0);
+    if (R <= 0) {
+        for (int r = 1; r <= 13 && R <= 0; r += 2)
+            if ((g + r - 1) / r <= pref && (g + r - 1) / r <= max_dp_warps(r)) R = r;
+        for (int r = 13; r >= 1 && R <= 0; r -= 2)
+            if ((g + r - 1) / r <= max_dp_warps(r)) R = r;
+        if (R <= 0) return MB200_ERR_UNSUPPORTED;
+    }
+    if (R < 1 || R > 13 || (R & 1) == 0) return MB200_ERR_INVALID_ARG;
+    const int ndp = (g + R - 1) / R;
+    if (ndp > max_dp_warps(R)) return MB200_ERR_UNSUPPORTED;
+    const int stage_bytes = txp * 128 * (has_mask ? 2 : 1);
+    int cap = (96 * 1024) / stage_bytes;
+    if (cap < 3) cap = 3;
+    if (cap > kMaxStages) cap = kMaxStages;
+    const int forced = env_int("MB200_MAS_NSTAGE", 0);
+    if (forced >= 2 && forced <= kMaxStages) cap = forced;
+    // bits in shared memory with a pipelined ring; then an unpipelined ring; then (huge shapes)
+    // the bit matrix in the utterance's own output region, which must be large enough for it
+    for (int mode = 0; mode < 3; ++mode) {
+        const bool bg = mode == 2;
+        if (bg && (long long)n_chunks * txp > (long long)T_x * T_y) break;
+        const int hi = mode == 1 ? 1 : cap, lo = mode == 0 ? 2 : 1;
+        for (int ns = hi; ns >= lo; --ns) {
+            MasSmem L = mas_smem_layout(has_mask, ndp, ns, txp, n_chunks, bg);
             if (L.total <= (uint32_t)kMaxSmemPerBlock) {
-                pl->R = R; pl->nstage = ns; pl->txp = txp; pl->n_chunks = n_chunks;
-                pl->multi = multi ? 1 : 0; pl->use_tma = aligned16 ? 1 : 0;
-                pl->vec_store = 0; pl->smem = L.total;
+                pl->R = R; pl->ndp = ndp; pl->nstage = ns; pl->txp = txp; pl->n_chunks = n_chunks;
+                pl->use_tma = aligned16 ? 1 : 0; pl->vec_store = 0; pl->smem = L.total;
+                pl->threads = 32 * (ndp + 1 + kWriterWarps); pl->bits_global = bg ? 1 : 0;
                 return MB200_OK;
             }
         }
@@ -430,7 +517,7 @@ static int mas_grid(MasKernelFn fn, const MasPlan &pl, int B, int *ctas_per_sm) 
     int dev = 0, sms = kNumSMsB200, occ = 1;
     if (cudaGetDevice(&dev) == cudaSuccess)
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kThreads, pl.smem) != cudaSuccess || occ < 1)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, pl.threads, pl.smem) != cudaSuccess || occ < 1)
         occ = 1;
     if (ctas_per_sm) *ctas_per_sm = occ;
     long long g = (long long)sms * occ;
@@ -479,11 +566,11 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
     p.t_xs = t_xs_dev; p.t_ys = t_ys_dev; p.status = status_dev;
     p.B = B; p.T_x = T_x; p.T_y = T_y; p.penalty = penalty;
     p.one_bits = (path_dtype == MB200_PATH_F32) ? 0x3f800000u : 1u;
-    p.nstage = pl.nstage; p.txp = pl.txp; p.n_chunks = pl.n_chunks;
-    p.use_tma = pl.use_tma; p.vec_store = pl.vec_store; p.multi = pl.multi;
+    p.ndp = pl.ndp; p.nstage = pl.nstage; p.txp = pl.txp; p.n_chunks = pl.n_chunks;
+    p.use_tma = pl.use_tma; p.vec_store = pl.vec_store; p.bits_global = pl.bits_global;
 
     const int grid = mas_grid(fn, pl, B, nullptr);
-    fn<<<grid, kThreads, pl.smem, (cudaStream_t)stream>>>(tm_v, tm_m, p);
+    fn<<<grid, pl.threads, pl.smem, (cudaStream_t)stream>>>(tm_v, tm_m, p);
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
 }
@@ -501,8 +588,8 @@ extern "C" int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mas
     } else {
         out[0] = mas_grid(fn, pl, B, &occ);
     }
-    out[1] = kThreads; out[2] = (int)pl.smem; out[3] = pl.R; out[4] = pl.nstage;
-    out[5] = pl.use_tma; out[6] = occ; out[7] = pl.multi;
+    out[1] = pl.threads; out[2] = (int)pl.smem; out[3] = pl.R; out[4] = pl.nstage;
+    out[5] = pl.use_tma + 2 * pl.bits_global; out[6] = occ; out[7] = pl.ndp;
     return MB200_OK;
 }
 

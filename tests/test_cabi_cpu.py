@@ -47,20 +47,22 @@ def test_argument_validation_needs_no_gpu(lib):
     assert lib.matcha_b200_mas_maximum_path_host(None, None, None, None, 0, 4, 4, ctypes.c_float(-1e9)) == 0
 
 
-@pytest.mark.parametrize("shape,want_r", [((16, 128, 800), 5), ((64, 400, 2000), 13), ((8, 50, 200), 3),
-                                          ((4, 20, 64), 1), ((2, 450, 520), 13)])
-def test_launch_plan(lib, shape, want_r):
+@pytest.mark.parametrize("shape", [(16, 128, 800), (64, 400, 2000), (8, 50, 200), (4, 20, 64), (2, 450, 520),
+                                   (1024, 200, 1000)])
+@pytest.mark.parametrize("has_mask", [0, 1])
+def test_launch_plan(lib, shape, has_mask):
     out = (ctypes.c_int * 8)()
-    assert lib.matcha_b200_mas_query_launch(*shape, 0, 1, ctypes.byref(out)) == 0
-    block, smem, r, nstage, use_tma = out[1], out[2], out[3], out[4], out[5]
-    assert block == 192 and r == want_r and r % 2 == 1 and 2 <= nstage <= 8 and use_tma == 1
+    assert lib.matcha_b200_mas_query_launch(*shape, has_mask, 1, ctypes.byref(out)) == 0
+    block, smem, r, nstage, use_tma, ndp = out[1], out[2], out[3], out[4], out[5], out[7]
+    assert r % 2 == 1 and 1 <= r <= 13 and 1 <= nstage <= 8 and (use_tma & 1) == 1
+    assert block == 32 * (ndp + 5) and block <= 1024
+    assert 32 * r * ndp >= shape[1], "one wavefront pass must cover every token"
     assert smem <= 232448
-    assert out[7] == (1 if shape[1] > 32 * r else 0)
 
 
 def test_unsupported_shape_is_reported(lib):
     out = (ctypes.c_int * 8)()
-    assert lib.matcha_b200_mas_query_launch(1, 4096, 16384, 0, 1, ctypes.byref(out)) == -2
+    assert lib.matcha_b200_mas_query_launch(1, 1400, 4000, 0, 1, ctypes.byref(out)) == -2
 
 
 def test_no_cpu_fallback_without_cuda():
