@@ -78,6 +78,12 @@ int matcha_b200_mas_maximum_path_host(
     const int *t_xs_host, const int *t_ys_host,
     int B, int T_x, int T_y, float penalty);
 
+/* scores[i] = values[i] * mask[i] (__init__.py:45), for callers whose shape is too large for the
+ * fused-mask variant of the MAS kernel (query_launch with has_mask=1 returns MB200_ERR_UNSUPPORTED):
+ * form the scores here, then call matcha_b200_mas_compute_batch_alignments with mask_dev = NULL. */
+int matcha_b200_mas_apply_mask(float *scores_dev, const float *values_dev, const float *mask_dev,
+                               long long n, void *stream);
+
 /* Launch geometry the MAS kernel would use for a shape (for bench/launch accounting):
  * out[0]=grid, out[1]=block, out[2]=dynamic smem bytes, out[3]=rows per lane (R),
  * out[4]=pipeline stages, out[5]=bit0: TMA path taken, bit1: bit matrix kept in global memory, out[6]=CTAs per SM,

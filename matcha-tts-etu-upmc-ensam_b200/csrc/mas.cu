@@ -75,10 +75,6 @@ __device__ __forceinline__ void rb_chunk_range(int r0, int r1, int tx, int ty, i
     c1 = y_last / kChunk;
 }
 
-__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {
-    while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
-}
-
 // ------------------------------------------------------------------ DP over one chunk
 // `stage` points at this warp's first row inside the stage.  has_prev: lane 0 takes
 // Q[y-1][x0-1] from the boundary slot `bin` written by the previous warp; put_next: lane 31
@@ -111,7 +107,7 @@ __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uin
         }
         const int y0 = y_base + 4 * g;
         float4 upv = make_float4(0.f, 0.f, 0.f, 0.f), outv = upv;
-        if (has_prev && lane == 0) upv = lds128(bin + 16 * g);
+        if (has_prev) upv = lds128(bin + 16 * g);   // all lanes (broadcast): keeps the warp converged
         const uint32_t mg = 1u << (4 * g);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -250,7 +246,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                     const int lo = max(r0, tx + kChunk * c - ty);
                     const int hi = min(r1, kChunk * c + kChunk);
                     const int j0 = (lo - r0) / kBoxRows, j1 = (hi - 1 - r0) / kBoxRows;
-                    if (lane == 0) mbar_wait_sleep(bar_empty + 8u * (w * nstage + s), ph ^ 1u, 20);
+                    if (lane == 0) mbar_wait_parked(bar_empty + 8u * (w * nstage + s), ph ^ 1u, 2000);
                     __syncwarp();
                     if (p.use_tma) {
                         if (lane == 0) {
@@ -318,11 +314,12 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                         const uint32_t bout = base + L.bnd + ((w * kBndDepth + dout) * kBndFloats) * 4u;
 #pragma unroll
                         for (int r = 0; r < R; ++r) bits[r] = 0u;
-                        mbar_wait(bar_full + 8u * (w * nstage + s), ph);
-                        if (in_h && lane == 0)
-                            mbar_wait(bar_bdfull + 8u * ((w - 1) * kBndDepth + din), (hin / kBndDepth) & 1u);
-                        if (out_h && lane == 31)
-                            mbar_wait(bar_bdempty + 8u * (w * kBndDepth + dout), ((hout / kBndDepth) & 1u) ^ 1u);
+                        mbar_wait_parked(bar_full + 8u * (w * nstage + s), ph, 2000);
+                        // every lane waits (warp-uniform control flow keeps the shuffles on the fast path)
+                        if (in_h)
+                            mbar_wait_parked(bar_bdfull + 8u * ((w - 1) * kBndDepth + din), (hin / kBndDepth) & 1u, 2000);
+                        if (out_h)
+                            mbar_wait_parked(bar_bdempty + 8u * (w * kBndDepth + dout), ((hout / kBndDepth) & 1u) ^ 1u, 2000);
                         __syncwarp();
                         if (c <= cd)
                             dp_chunk<R, HAS_MASK, true>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
@@ -348,7 +345,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                 __syncwarp();
                 asm volatile("bar.sync 1, %0;" ::"r"(ndp * 32) : "memory");
                 if (w == 0 && lane == 0) {
-                    mbar_wait_sleep(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 64);
+                    mbar_wait_parked(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
                     // backtrack, core.pyx:87-92: token idx owns frames [cs[idx], cs[idx+1])
                     int idx = tx - 1, y = ty - 1;
                     cs[tx] = ty;
@@ -370,7 +367,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                 __syncwarp();
                 asm volatile("bar.sync 1, %0;" ::"r"(ndp * 32) : "memory");
             } else if (w == 0 && lane == 0) {
-                mbar_wait_sleep(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 64);
+                mbar_wait_parked(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
                 if (p.status != nullptr) atomicAdd(p.status, 1);
                 info_g[buf].tx = 0; info_g[buf].ty = 0; info_g[buf].valid = 0;
                 mbar_arrive(bar_bfull + 8u * buf);
@@ -383,7 +380,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const uint32_t buf = k & 1u;
             const int *cs = cs_g + buf * (p.txp + 4);
-            mbar_wait_sleep(bar_bfull + 8u * buf, (k >> 1) & 1u, 200);
+            mbar_wait_parked(bar_bfull + 8u * buf, (k >> 1) & 1u, 20000);
             const int tx = info_g[buf].valid ? info_g[buf].tx : 0;
             uint32_t *out = p.out + (size_t)b * p.T_x * p.T_y;
             const uint32_t one = p.one_bits;
@@ -437,6 +434,15 @@ mas_lengths_kernel(const float *__restrict__ mask, int T_x, int T_y, int *__rest
         t_xs[blockIdx.x] = (int)(red[0][0] + red[0][1] + red[0][2] + red[0][3]);
         t_ys[blockIdx.x] = (int)(red[1][0] + red[1][1] + red[1][2] + red[1][3]);
     }
+}
+
+// scores = value * mask (__init__.py:45) for shapes whose fused-mask plan does not fit on chip
+__global__ void __launch_bounds__(256)
+mas_apply_mask_kernel(float *__restrict__ out, const float *__restrict__ value,
+                      const float *__restrict__ mask, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        out[i] = __fmul_rn(value[i], mask[i]);
 }
 
 }  // namespace mb200
@@ -599,6 +605,18 @@ extern "C" int matcha_b200_mas_lengths_from_mask(const float *mask_dev, int B, i
     if (B == 0) return MB200_OK;
     if (!mask_dev || !t_xs_dev || !t_ys_dev) return MB200_ERR_INVALID_ARG;
     mas_lengths_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(mask_dev, T_x, T_y, t_xs_dev, t_ys_dev);
+    MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+extern "C" int matcha_b200_mas_apply_mask(float *scores_dev, const float *values_dev, const float *mask_dev,
+                                           long long n, void *stream) {
+    if (n < 0) return MB200_ERR_INVALID_ARG;
+    if (n == 0) return MB200_OK;
+    if (!scores_dev || !values_dev || !mask_dev) return MB200_ERR_INVALID_ARG;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
+    mas_apply_mask_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(scores_dev, values_dev, mask_dev, (size_t)n);
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
 }

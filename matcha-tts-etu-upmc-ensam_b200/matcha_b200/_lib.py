@@ -49,6 +49,8 @@ def load_library():
     lib.matcha_b200_mas_maximum_path_host.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float]
     lib.matcha_b200_mas_query_launch.restype = c_int
     lib.matcha_b200_mas_query_launch.argtypes = [c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int * 8)]
+    lib.matcha_b200_mas_apply_mask.restype = c_int
+    lib.matcha_b200_mas_apply_mask.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_void_p]
     _LIB = lib
     return lib
 
@@ -68,4 +70,5 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_lengths_from_mask",
     "matcha_b200_mas_maximum_path_host",
     "matcha_b200_mas_query_launch",
+    "matcha_b200_mas_apply_mask",
 )

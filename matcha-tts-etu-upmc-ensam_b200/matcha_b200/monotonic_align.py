@@ -31,6 +31,13 @@ def _require_cuda():
         raise RuntimeError("matcha_b200.monotonic_align needs a CUDA device (sm_100a); there is no CPU fallback")
 
 
+def _fused_mask_fits(value):
+    out = (ctypes.c_int * 8)()
+    B, T_x, T_y = value.shape
+    rc = load_library().matcha_b200_mas_query_launch(max(B, 1), T_x, T_y, 1, 1, ctypes.byref(out))
+    return rc == 0
+
+
 def lengths_from_mask(mask):
     """t_x[b] = int(sum_x mask[b,x,0]), t_y[b] = int(sum_y mask[b,0,y]) on the device (__init__.py:52-53)."""
     lib = load_library()
@@ -104,6 +111,14 @@ def maximum_path(value, mask, mask_mode="full", check_lengths=False):
         v = v.contiguous()
         if mask_mode == "full":
             kernel_mask = m.contiguous()
+            if not _fused_mask_fits(v):
+                # shape too large for the fused-mask kernel variant: form value*mask first
+                scores = torch.empty_like(v)
+                with torch.cuda.device(dev):
+                    check(load_library().matcha_b200_mas_apply_mask(
+                        scores.data_ptr(), v.data_ptr(), kernel_mask.data_ptr(), v.numel(), _stream_ptr(dev)),
+                        "mas_apply_mask")
+                v, kernel_mask = scores, None
     else:
         # off the hot path: form value*mask in the caller's dtype exactly as __init__.py:45,48 do
         v = ((v * m) if mask_mode == "full" else v).float().contiguous()
