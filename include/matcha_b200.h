@@ -86,7 +86,7 @@ int matcha_b200_mas_apply_mask(float *scores_dev, const float *values_dev, const
 
 /* Launch geometry the MAS kernel would use for a shape (for bench/launch accounting):
  * out[0]=grid, out[1]=block, out[2]=dynamic smem bytes, out[3]=rows per lane (R),
- * out[4]=pipeline stages, out[5]=bit0: TMA path taken, bit1: bit matrix kept in global memory, out[6]=CTAs per SM,
+ * out[4]=pipeline stages, out[5]=1 if the TMA path is taken, out[6]=CTAs per SM,
  * out[7]=DP warps per CTA. */
 int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int aligned16, int out[8]);
 

@@ -10,14 +10,17 @@
 //           step per mel frame: a single shfl_up brings Q[y-1][x0-1] from lane l-1, the other
 //           R-1 predecessors are registers.  Warp w runs one chunk behind warp w-1 and gets the
 //           boundary row Q[.][32*R*w-1] through a 2-deep shared-memory ring guarded by
-//           mbarriers.  The "came from x-1" bit of every cell is packed 32 frames per word
-//           and kept in shared memory, so the backtrack never leaves the SM.
+//           mbarriers.  The "came from x-1" bit of every cell is packed 32 frames per word and
+//           parked in the utterance's own (not yet written) output region, i.e. in L2.
 //   warp NDP        producer.  Streams the fp32 score rows each DP warp needs for its next
 //           chunk (only rows inside the DP band) into per-warp rings of 128B-swizzled
 //           stages with TMA (cp.async.bulk.tensor, completion on an mbarrier), in the
 //           wavefront's own order; when the tensor breaks TMA's 16-byte rules
 //           (T_y % 4 != 0 or a misaligned base) the same warp fills the same layout with
 //           4-byte cp.async.
+//   warp NDP+1      backtrack.  Walks the bit words of the finished utterance chunk by chunk
+//           (one coalesced 128-byte read per chunk, the next one prefetched) while the DP
+//           warps already run the CTA's next utterance, and emits per-token start frames.
 //   last 4 warps    writers.  Turn the per-token start frames found by the backtrack into
 //           the dense 0/1 alignment with 16-byte streaming stores, overlapping the DP of
 //           the CTA's next utterance.
@@ -38,7 +41,7 @@ constexpr int kBndFloats = 36;    // [0]=Q[32c-1], [1..32]=Q[32c..32c+31], padde
 
 // most DP warps a CTA may carry for a given rows-per-lane (register budget of the SM)
 __host__ __device__ constexpr int max_dp_warps(int R) {
-    return R <= 3 ? 14 : (R <= 5 ? 8 : (R <= 7 ? 6 : (R <= 9 ? 4 : 3)));
+    return R <= 5 ? 8 : (R <= 7 ? 6 : (R <= 9 ? 4 : 3));
 }
 
 struct MasParams {
@@ -53,11 +56,10 @@ struct MasParams {
     uint32_t one_bits;   // bit pattern of "1" in the output element type
     int ndp;             // DP warps in the CTA
     int nstage;          // ring depth per DP warp
-    int txp;             // T_x rounded up to 32: row pitch of the bit matrix and of a stage
+    int txp;             // T_x rounded up to 32: rows of a stage
     int n_chunks;        // ceil(T_y / 32)
     int use_tma;
     int vec_store;       // output rows are 16-byte aligned
-    int bits_global;     // bit matrix too big for shared memory: keep it in the utterance's own output region
 };
 
 struct ItemInfo { int tx, ty, valid, pad; };
@@ -143,43 +145,47 @@ __device__ __forceinline__ void dp_chunk(float (&q)[R], uint32_t (&bits)[R], uin
 // ------------------------------------------------------------------ shared-memory carve-up
 struct MasSmem {
     uint32_t stages;   // nstage stage sets of txp rows x 128 B (x2 with a mask), 1024-aligned
-    uint32_t bits;     // n_chunks * txp words
     uint32_t bnd;      // (ndp-1) * kBndDepth * kBndFloats floats
     uint32_t cs;       // 2 * (txp + 4) ints: start frame of every token (+ end sentinel)
     uint32_t info;     // 2 * ItemInfo
     uint32_t itw;      // ndp ints: producer's per-ring fill counters
-    uint32_t bars;     // full/empty [ndp*nstage], bdfull/bdempty [(ndp-1)*depth], bfull/bempty [2]
+    uint32_t bars;     // full/empty [ndp*nstage], bdfull/bdempty [(ndp-1)*depth],
+                       // bfull/bempty [2], dpdone/btdone [2]
     uint32_t stage_bytes;
     uint32_t total;
 };
 
-__host__ __device__ inline MasSmem mas_smem_layout(bool has_mask, int ndp, int nstage, int txp,
-                                                   int n_chunks, bool bits_global) {
+__host__ __device__ inline MasSmem mas_smem_layout(bool has_mask, int ndp, int nstage, int txp) {
     MasSmem s;
     uint32_t off = 0;
     s.stage_bytes = (uint32_t)txp * 128u * (has_mask ? 2u : 1u);
     s.stages = off; off += (uint32_t)nstage * s.stage_bytes;
-    s.bits = off;   off += bits_global ? 0u : (uint32_t)n_chunks * (uint32_t)txp * 4u;
     s.bnd = off;    off += (uint32_t)(ndp - 1) * kBndDepth * kBndFloats * 4u;
     s.cs = off;     off += 2u * (uint32_t)(txp + 4) * 4u;
     s.info = off;   off += 2u * (uint32_t)sizeof(ItemInfo);
     s.itw = off;    off += ((uint32_t)ndp * 4u + 15u) & ~15u;
     off = (off + 7u) & ~7u;
     s.bars = off;
-    off += (2u * (uint32_t)ndp * (uint32_t)nstage + 2u * (uint32_t)(ndp - 1) * kBndDepth + 4u) * 8u;
+    off += (2u * (uint32_t)ndp * (uint32_t)nstage + 2u * (uint32_t)(ndp - 1) * kBndDepth + 8u) * 8u;
     s.total = off + 1024u;   // slack for the manual 1024-byte alignment of the base
     return s;
 }
 
+// highest set bit of w at or below bit position `pos` (0..31), or -1
+__device__ __forceinline__ int top_bit_upto(uint32_t w, int pos) {
+    w &= 0xffffffffu >> (31 - pos);
+    return 31 - __clz(w);          // __clz(0) == 32 -> -1
+}
+
 // ------------------------------------------------------------------ the kernel
 template <int R, bool HAS_MASK>
-__global__ void __launch_bounds__(32 * (max_dp_warps(R) + 1 + kWriterWarps))
+__global__ void __launch_bounds__(32 * (max_dp_warps(R) + 2 + kWriterWarps), R <= 3 ? 2 : 1)
 mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_m,
            const MasParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-    const MasSmem L = mas_smem_layout(HAS_MASK, p.ndp, p.nstage, p.txp, p.n_chunks, p.bits_global != 0);
+    const MasSmem L = mas_smem_layout(HAS_MASK, p.ndp, p.nstage, p.txp);
     constexpr int RB = 32 * R;
     const int ndp = p.ndp, nstage = p.nstage;
 
@@ -189,9 +195,10 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
     const uint32_t bar_empty = bar_full + 8u * ndp * nstage;               // [w][s]
     const uint32_t bar_bdfull = bar_empty + 8u * ndp * nstage;             // [w][d], w < ndp-1
     const uint32_t bar_bdempty = bar_bdfull + 8u * (ndp - 1) * kBndDepth;  // [w][d]
-    const uint32_t bar_bfull = bar_bdempty + 8u * (ndp - 1) * kBndDepth;   // [2]
-    const uint32_t bar_bempty = bar_bfull + 16u;                           // [2]
-    uint32_t *bits_smem = reinterpret_cast<uint32_t *>(gbase + L.bits);
+    const uint32_t bar_bfull = bar_bdempty + 8u * (ndp - 1) * kBndDepth;   // [2] backtrack -> writers
+    const uint32_t bar_bempty = bar_bfull + 16u;                           // [2] writers -> backtrack
+    const uint32_t bar_dpdone = bar_bempty + 16u;                          // [2] DP warps -> backtrack
+    const uint32_t bar_btdone = bar_dpdone + 16u;                          // [2] backtrack -> DP warps
     int *cs_g = reinterpret_cast<int *>(gbase + L.cs);
     ItemInfo *info_g = reinterpret_cast<ItemInfo *>(gbase + L.info);
     const uint32_t mask_off = (uint32_t)p.txp * 128u;
@@ -208,6 +215,8 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar_bfull + 8u * i, 1u);
             mbar_init(bar_bempty + 8u * i, kWriterWarps);
+            mbar_init(bar_dpdone + 8u * i, (uint32_t)ndp);
+            mbar_init(bar_btdone + 8u * i, 1u);
         }
         mbar_fence_init();
     }
@@ -246,8 +255,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                     const int lo = max(r0, tx + kChunk * c - ty);
                     const int hi = min(r1, kChunk * c + kChunk);
                     const int j0 = (lo - r0) / kBoxRows, j1 = (hi - 1 - r0) / kBoxRows;
-                    if (lane == 0) mbar_wait_parked(bar_empty + 8u * (w * nstage + s), ph ^ 1u, 2000);
-                    __syncwarp();
+                    mbar_wait_parked(bar_empty + 8u * (w * nstage + s), ph ^ 1u, 2000);
                     if (p.use_tma) {
                         if (lane == 0) {
                             mbar_arrive_expect_tx(full, (uint32_t)(j1 - j0 + 1) * kBoxBytes * (HAS_MASK ? 2u : 1u));
@@ -278,21 +286,21 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
             }
         }
     } else if (warp < ndp) {
-        // ============================ DP wavefront + backtrack ============================
+        // ============================ DP wavefront ============================
         const int w = warp;
         uint32_t it = 0, hin = 0, hout = 0, k = 0;
         const int r0 = w * RB;
         const int x0 = r0 + R * lane;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const int tx = p.t_xs[b], ty = p.t_ys[b];
-            const bool valid = lengths_valid(tx, ty, p.T_x, p.T_y);
             const uint32_t buf = k & 1u;
-            int *cs = cs_g + buf * (p.txp + 4);
-            // generic pointer: shared memory, or (fallback) the start of this utterance's output
-            uint32_t *bits_g = p.bits_global ? (p.out + (size_t)b * p.T_x * p.T_y) : bits_smem;
-            if (valid) {
+            // the backtrack warp must have consumed utterance k-2 before dpdone[buf] is re-armed
+            mbar_wait_parked(bar_btdone + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
+            if (lengths_valid(tx, ty, p.T_x, p.T_y)) {
                 const int n_act = (tx + RB - 1) / RB;
                 if (w < n_act) {
+                    // bit words of this utterance: [chunk][token], parked in its own output region
+                    uint32_t *bits_g = p.out + (size_t)b * p.T_x * p.T_y;
                     const int r1 = min(r0 + RB, tx);
                     int c0, c1, c0p = 0, c1p = -1;
                     rb_chunk_range(r0, r1, tx, ty, c0, c1);
@@ -314,8 +322,8 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                         const uint32_t bout = base + L.bnd + ((w * kBndDepth + dout) * kBndFloats) * 4u;
 #pragma unroll
                         for (int r = 0; r < R; ++r) bits[r] = 0u;
-                        mbar_wait_parked(bar_full + 8u * (w * nstage + s), ph, 2000);
                         // every lane waits (warp-uniform control flow keeps the shuffles on the fast path)
+                        mbar_wait_parked(bar_full + 8u * (w * nstage + s), ph, 2000);
                         if (in_h)
                             mbar_wait_parked(bar_bdfull + 8u * ((w - 1) * kBndDepth + din), (hin / kBndDepth) & 1u, 2000);
                         if (out_h)
@@ -327,10 +335,10 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                         else
                             dp_chunk<R, HAS_MASK, false>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
                                                          has_prev, bin, out_h, bout);
-                        uint32_t *wd = bits_g + (size_t)c * p.txp + x0;
+                        uint32_t *wd = bits_g + (size_t)c * p.T_x + x0;
 #pragma unroll
                         for (int r = 0; r < R; ++r)
-                            if (x0 + r < p.txp) wd[r] = bits[r];
+                            if (x0 + r < p.T_x) wd[r] = bits[r];
                         __syncwarp();
                         if (lane == 0) {
                             mbar_arrive(bar_empty + 8u * (w * nstage + s));
@@ -341,41 +349,71 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                         hout += out_h ? 1u : 0u;
                     }
                 }
-                // every DP warp has stored its bits before the backtrack reads them
-                __syncwarp();
-                asm volatile("bar.sync 1, %0;" ::"r"(ndp * 32) : "memory");
-                if (w == 0 && lane == 0) {
-                    mbar_wait_parked(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
-                    // backtrack, core.pyx:87-92: token idx owns frames [cs[idx], cs[idx+1])
-                    int idx = tx - 1, y = ty - 1;
-                    cs[tx] = ty;
-                    while (idx > 0) {
-                        int c = y >> 5;
-                        const volatile uint32_t *bv = bits_g;
-                        uint32_t wv = bv[(size_t)c * p.txp + idx] & (0xffffffffu >> (31 - (y & 31)));
-                        while (wv == 0u) { --c; wv = bv[(size_t)c * p.txp + idx]; }
-                        const int yp = (c << 5) + 31 - __clz(wv);
-                        cs[idx] = yp;
-                        y = yp - 1;
-                        --idx;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_dpdone + 8u * buf);   // release: this warp's bit words are out
+        }
+    } else if (warp == ndp + 1) {
+        // ============================ backtrack ============================
+        uint32_t k = 0;
+        for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
+            const int tx = p.t_xs[b], ty = p.t_ys[b];
+            const bool valid = lengths_valid(tx, ty, p.T_x, p.T_y);
+            const uint32_t buf = k & 1u;
+            int *cs = cs_g + buf * (p.txp + 4);
+            mbar_wait_parked(bar_dpdone + 8u * buf, (k >> 1) & 1u, 5000);
+            mbar_wait_parked(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
+            if (valid) {
+                // core.pyx:87-92: token idx owns frames [cs[idx], cs[idx+1]).  Within one 32-frame
+                // chunk the path descends at most 32 tokens, so lane l holds the word of token
+                // idx_entry - l; the 64 candidate words of the next chunk are prefetched meanwhile.
+                const uint32_t *bits_g = p.out + (size_t)b * p.T_x * p.T_y;
+                int idx = tx - 1, y = ty - 1, c = y >> 5;
+                if (lane == 0) cs[tx] = ty;
+                uint32_t cur = 0u, nxa = 0u, nxb = 0u;
+                if (idx - lane >= 0) cur = __ldcg(bits_g + (size_t)c * p.T_x + (idx - lane));
+                while (idx > 0) {
+                    const int ie = idx;                       // token at chunk entry
+                    if (c > 0) {
+                        const uint32_t *nb = bits_g + (size_t)(c - 1) * p.T_x;
+                        if (ie - lane >= 0) nxa = __ldcg(nb + (ie - lane));
+                        if (ie - 32 - lane >= 0) nxb = __ldcg(nb + (ie - 32 - lane));
                     }
-                    cs[0] = 0;
-                    info_g[buf].tx = tx; info_g[buf].ty = ty; info_g[buf].valid = 1;
-                    mbar_arrive(bar_bfull + 8u * buf);
+                    // walk this chunk: frames (c<<5) .. y
+                    while (idx > 0) {
+                        const uint32_t wv = __shfl_sync(0xffffffffu, cur, ie - idx);
+                        const int tb = top_bit_upto(wv, y & 31);
+                        if (tb < 0) break;                    // token idx continues into chunk c-1
+                        const int yp = (c << 5) + tb;
+                        if (lane == 0) cs[idx] = yp;
+                        --idx;
+                        y = yp - 1;
+                        if (tb == 0) break;                   // next token starts in chunk c-1
+                    }
+                    if (idx > 0) {
+                        --c;
+                        y = (c << 5) + 31;
+                        // re-centre the prefetched words on the new entry token
+                        const int sh = ie - idx;              // 0..32
+                        const uint32_t a = __shfl_sync(0xffffffffu, nxa, (lane + sh) & 31);
+                        const uint32_t bq = __shfl_sync(0xffffffffu, nxb, (lane + sh) & 31);
+                        cur = (lane + sh < 32) ? a : bq;
+                    }
                 }
-                // the next utterance's DP may overwrite the bit matrix only after the backtrack
-                __syncwarp();
-                asm volatile("bar.sync 1, %0;" ::"r"(ndp * 32) : "memory");
-            } else if (w == 0 && lane == 0) {
-                mbar_wait_parked(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
-                if (p.status != nullptr) atomicAdd(p.status, 1);
-                info_g[buf].tx = 0; info_g[buf].ty = 0; info_g[buf].valid = 0;
+                if (lane == 0) cs[0] = 0;
+            } else if (lane == 0 && p.status != nullptr) {
+                atomicAdd(p.status, 1);
+            }
+            __syncwarp();
+            if (lane == 0) {
+                info_g[buf].tx = tx; info_g[buf].ty = ty; info_g[buf].valid = valid ? 1 : 0;
                 mbar_arrive(bar_bfull + 8u * buf);
+                mbar_arrive(bar_btdone + 8u * buf);
             }
         }
     } else {
         // ============================ writers ============================
-        const int ww = warp - ndp - 1;
+        const int ww = warp - ndp - 2;
         uint32_t k = 0;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const uint32_t buf = k & 1u;
@@ -451,7 +489,7 @@ mas_apply_mask_kernel(float *__restrict__ out, const float *__restrict__ value,
 namespace mb200 {
 
 struct MasPlan {
-    int R, ndp, nstage, txp, n_chunks, use_tma, vec_store, threads, bits_global;
+    int R, ndp, nstage, txp, n_chunks, use_tma, vec_store, threads;
     uint32_t smem;
 };
 
@@ -461,17 +499,16 @@ static int env_int(const char *name, int dflt) {
 }
 
 // Picks rows-per-lane R (odd, so the 128B-swizzled LDS.128 pattern is conflict-free), the
-// number of DP warps and the ring depth that fit 227 KB next to the bit matrix.
-// Tuning overrides (experiments only): MB200_MAS_R, MB200_MAS_NDP_PREF, MB200_MAS_NSTAGE.
+// number of DP warps and the ring depth.  Measured on B200: R=3 is the sweet spot (a warp's
+// per-frame instruction count stays near its latency floor), R=1 only for <= 2 row groups.
+// Tuning overrides (experiments only): MB200_MAS_R, MB200_MAS_NSTAGE.
 static int mas_make_plan(int T_x, int T_y, bool has_mask, bool aligned16, MasPlan *pl) {
     const int n_chunks = (T_y + kChunk - 1) / kChunk;
     const int g = (T_x + 31) / 32, txp = 32 * g;
-    const int pref = env_int("MB200_MAS_NDP_PREF", 4);
     int R = env_int("MB200_MAS_R", 0);
     if (R <= 0) {
-        for (int r = 1; r <= 13 && R <= 0; r += 2)
-            if ((g + r - 1) / r <= pref && (g + r - 1) / r <= max_dp_warps(r)) R = r;
-        for (int r = 13; r >= 1 && R <= 0; r -= 2)
+        if (g <= 2) R = 1;
+        for (int r = 3; r <= 13 && R <= 0; r += 2)
             if ((g + r - 1) / r <= max_dp_warps(r)) R = r;
         if (R <= 0) return MB200_ERR_UNSUPPORTED;
     }
@@ -479,25 +516,21 @@ static int mas_make_plan(int T_x, int T_y, bool has_mask, bool aligned16, MasPla
     const int ndp = (g + R - 1) / R;
     if (ndp > max_dp_warps(R)) return MB200_ERR_UNSUPPORTED;
     const int stage_bytes = txp * 128 * (has_mask ? 2 : 1);
-    int cap = (96 * 1024) / stage_bytes;
-    if (cap < 3) cap = 3;
-    if (cap > kMaxStages) cap = kMaxStages;
+    // ring depth: ~64 KB of stages per CTA so that several CTAs share an SM; 3 stages when
+    // two CTAs still fit; whatever fits for very tall inputs
+    int ns = (64 * 1024) / stage_bytes;
+    if (ns > kMaxStages) ns = kMaxStages;
+    if (ns < 2) ns = 2;
+    if (ns < 3 && mas_smem_layout(has_mask, ndp, 3, txp).total + kSmemBlockReserve <= (uint32_t)kSmemPerSM / 2) ns = 3;
     const int forced = env_int("MB200_MAS_NSTAGE", 0);
-    if (forced >= 2 && forced <= kMaxStages) cap = forced;
-    // bits in shared memory with a pipelined ring; then an unpipelined ring; then (huge shapes)
-    // the bit matrix in the utterance's own output region, which must be large enough for it
-    for (int mode = 0; mode < 3; ++mode) {
-        const bool bg = mode == 2;
-        if (bg && (long long)n_chunks * txp > (long long)T_x * T_y) break;
-        const int hi = mode == 1 ? 1 : cap, lo = mode == 0 ? 2 : 1;
-        for (int ns = hi; ns >= lo; --ns) {
-            MasSmem L = mas_smem_layout(has_mask, ndp, ns, txp, n_chunks, bg);
-            if (L.total <= (uint32_t)kMaxSmemPerBlock) {
-                pl->R = R; pl->ndp = ndp; pl->nstage = ns; pl->txp = txp; pl->n_chunks = n_chunks;
-                pl->use_tma = aligned16 ? 1 : 0; pl->vec_store = 0; pl->smem = L.total;
-                pl->threads = 32 * (ndp + 1 + kWriterWarps); pl->bits_global = bg ? 1 : 0;
-                return MB200_OK;
-            }
+    if (forced >= 1 && forced <= kMaxStages) ns = forced;
+    for (; ns >= 1; --ns) {
+        MasSmem L = mas_smem_layout(has_mask, ndp, ns, txp);
+        if (L.total <= (uint32_t)kMaxSmemPerBlock) {
+            pl->R = R; pl->ndp = ndp; pl->nstage = ns; pl->txp = txp; pl->n_chunks = n_chunks;
+            pl->use_tma = aligned16 ? 1 : 0; pl->vec_store = 0; pl->smem = L.total;
+            pl->threads = 32 * (ndp + 2 + kWriterWarps);
+            return MB200_OK;
         }
     }
     return MB200_ERR_UNSUPPORTED;
@@ -573,7 +606,7 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
     p.B = B; p.T_x = T_x; p.T_y = T_y; p.penalty = penalty;
     p.one_bits = (path_dtype == MB200_PATH_F32) ? 0x3f800000u : 1u;
     p.ndp = pl.ndp; p.nstage = pl.nstage; p.txp = pl.txp; p.n_chunks = pl.n_chunks;
-    p.use_tma = pl.use_tma; p.vec_store = pl.vec_store; p.bits_global = pl.bits_global;
+    p.use_tma = pl.use_tma; p.vec_store = pl.vec_store;
 
     const int grid = mas_grid(fn, pl, B, nullptr);
     fn<<<grid, pl.threads, pl.smem, (cudaStream_t)stream>>>(tm_v, tm_m, p);
@@ -595,7 +628,7 @@ extern "C" int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mas
         out[0] = mas_grid(fn, pl, B, &occ);
     }
     out[1] = pl.threads; out[2] = (int)pl.smem; out[3] = pl.R; out[4] = pl.nstage;
-    out[5] = pl.use_tma + 2 * pl.bits_global; out[6] = occ; out[7] = pl.ndp;
+    out[5] = pl.use_tma; out[6] = occ; out[7] = pl.ndp;
     return MB200_OK;
 }
 
