@@ -12,13 +12,13 @@
 //           boundary row Q[.][32*R*w-1] through a 2-deep shared-memory ring guarded by
 //           mbarriers.  The "came from x-1" bit of every cell is packed 32 frames per word and
 //           parked in the utterance's own (not yet written) output region, i.e. in L2.
-//   warp NDP        producer.  Streams the fp32 score rows each DP warp needs for its next
-//           chunk (only rows inside the DP band) into per-warp rings of 128B-swizzled
-//           stages with TMA (cp.async.bulk.tensor, completion on an mbarrier), in the
-//           wavefront's own order; when the tensor breaks TMA's 16-byte rules
-//           (T_y % 4 != 0 or a misaligned base) the same warp fills the same layout with
-//           4-byte cp.async.
-//   warp NDP+1      backtrack.  Walks the bit words of the finished utterance chunk by chunk
+//           Each DP warp also feeds itself: the fp32 score rows it needs for a chunk (only rows
+//           inside the DP band) arrive in its own ring of 128B-swizzled stages by TMA
+//           (cp.async.bulk.tensor, completion on an mbarrier); the stage it has just finished is
+//           re-armed at once with the tile needed nstage chunks later.  When the tensor breaks
+//           TMA's 16-byte rules (T_y % 4 != 0 or a misaligned base) the warp fills the same
+//           layout with 4-byte cp.async instead.
+//   warp NDP        backtrack.  Walks the bit words of the finished utterance chunk by chunk
 //           (one coalesced 128-byte read per chunk, the next one prefetched) while the DP
 //           warps already run the CTA's next utterance, and emits per-token start frames.
 //   last 4 warps    writers.  Turn the per-token start frames found by the backtrack into
@@ -36,7 +36,7 @@ constexpr int kBoxRows = 32;      // tokens per TMA box
 constexpr int kBoxBytes = kBoxRows * kChunk * 4;
 constexpr int kWriterWarps = 4;
 constexpr int kMaxStages = 8;
-constexpr int kBndDepth = 2;      // boundary-row ring depth between neighbouring DP warps
+constexpr int kBndDepth = 8;      // boundary-row ring depth between neighbouring DP warps
 constexpr int kBndFloats = 36;    // [0]=Q[32c-1], [1..32]=Q[32c..32c+31], padded to 16 bytes
 
 // most DP warps a CTA may carry for a given rows-per-lane (register budget of the SM)
@@ -60,9 +60,15 @@ struct MasParams {
     int n_chunks;        // ceil(T_y / 32)
     int use_tma;
     int vec_store;       // output rows are 16-byte aligned
+    int early_zero;      // single-wave launches: zero the slab behind the bit words during the DP
+    int debug;
 };
 
 struct ItemInfo { int tx, ty, valid, pad; };
+
+// profiling aid (MB200_MAS_DEBUG=1): clock64 stamps of CTA 0's first utterance
+__device__ long long g_mas_dbg[32];
+#define MAS_STAMP(i) do { if (p.debug && blockIdx.x == 0 && k == 0 && lane == 0) g_mas_dbg[i] = clock64(); } while (0)
 
 __device__ __forceinline__ bool lengths_valid(int tx, int ty, int T_x, int T_y) {
     return tx >= 1 && ty >= 1 && tx <= ty && tx <= T_x && ty <= T_y;
@@ -148,8 +154,7 @@ struct MasSmem {
     uint32_t bnd;      // (ndp-1) * kBndDepth * kBndFloats floats
     uint32_t cs;       // 2 * (txp + 4) ints: start frame of every token (+ end sentinel)
     uint32_t info;     // 2 * ItemInfo
-    uint32_t itw;      // ndp ints: producer's per-ring fill counters
-    uint32_t bars;     // full/empty [ndp*nstage], bdfull/bdempty [(ndp-1)*depth],
+    uint32_t bars;     // full [ndp*nstage], bdfull/bdempty [(ndp-1)*depth],
                        // bfull/bempty [2], dpdone/btdone [2]
     uint32_t stage_bytes;
     uint32_t total;
@@ -163,10 +168,9 @@ __host__ __device__ inline MasSmem mas_smem_layout(bool has_mask, int ndp, int n
     s.bnd = off;    off += (uint32_t)(ndp - 1) * kBndDepth * kBndFloats * 4u;
     s.cs = off;     off += 2u * (uint32_t)(txp + 4) * 4u;
     s.info = off;   off += 2u * (uint32_t)sizeof(ItemInfo);
-    s.itw = off;    off += ((uint32_t)ndp * 4u + 15u) & ~15u;
     off = (off + 7u) & ~7u;
     s.bars = off;
-    off += (2u * (uint32_t)ndp * (uint32_t)nstage + 2u * (uint32_t)(ndp - 1) * kBndDepth + 8u) * 8u;
+    off += ((uint32_t)ndp * (uint32_t)nstage + 2u * (uint32_t)(ndp - 1) * kBndDepth + 8u) * 8u;
     s.total = off + 1024u;   // slack for the manual 1024-byte alignment of the base
     return s;
 }
@@ -179,7 +183,7 @@ __device__ __forceinline__ int top_bit_upto(uint32_t w, int pos) {
 
 // ------------------------------------------------------------------ the kernel
 template <int R, bool HAS_MASK>
-__global__ void __launch_bounds__(32 * (max_dp_warps(R) + 2 + kWriterWarps), R <= 3 ? 2 : 1)
+__global__ void __launch_bounds__(32 * (max_dp_warps(R) + 1 + kWriterWarps), R <= 3 ? 2 : 1)
 mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_m,
            const MasParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -192,8 +196,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // barrier addresses
     const uint32_t bar_full = base + L.bars;                               // [w][s]
-    const uint32_t bar_empty = bar_full + 8u * ndp * nstage;               // [w][s]
-    const uint32_t bar_bdfull = bar_empty + 8u * ndp * nstage;             // [w][d], w < ndp-1
+    const uint32_t bar_bdfull = bar_full + 8u * ndp * nstage;              // [w][d], w < ndp-1
     const uint32_t bar_bdempty = bar_bdfull + 8u * (ndp - 1) * kBndDepth;  // [w][d]
     const uint32_t bar_bfull = bar_bdempty + 8u * (ndp - 1) * kBndDepth;   // [2] backtrack -> writers
     const uint32_t bar_bempty = bar_bfull + 16u;                           // [2] writers -> backtrack
@@ -206,7 +209,6 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
     if (threadIdx.x == 0) {
         for (int i = 0; i < ndp * nstage; ++i) {
             mbar_init(bar_full + 8u * i, p.use_tma ? 1u : 32u);
-            mbar_init(bar_empty + 8u * i, 1u);
         }
         for (int i = 0; i < (ndp - 1) * kBndDepth; ++i) {
             mbar_init(bar_bdfull + 8u * i, 1u);
@@ -221,139 +223,132 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
         mbar_fence_init();
     }
     __syncthreads();
+    if (p.debug && blockIdx.x == 0 && threadIdx.x == 0) g_mas_dbg[0] = clock64();
 
-    if (warp == ndp) {
-        // ============================ producer ============================
-        if (p.use_tma && lane == 0) {
+    if (warp < ndp) {
+        // ============================ DP wavefront ============================
+        const int w = warp;
+        const int r0 = w * RB;
+        const int x0 = r0 + R * lane;
+        if (p.use_tma && w == 0 && lane == 0) {
             tma_prefetch_desc(&tmap_v);
             if (HAS_MASK) tma_prefetch_desc(&tmap_m);
         }
-        uint32_t *itw = reinterpret_cast<uint32_t *>(gbase + L.itw);
-        if (lane < ndp) itw[lane] = 0u;
-        __syncwarp();
-        for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
-            const int tx = p.t_xs[b], ty = p.t_ys[b];
-            if (!lengths_valid(tx, ty, p.T_x, p.T_y)) continue;
-            const int n_act = (tx + RB - 1) / RB;
-            int cz0, t_end;
-            rb_chunk_range((n_act - 1) * RB, tx, tx, ty, cz0, t_end);
-            t_end += n_act - 1;
-            // wavefront order: DP warp w reaches chunk c at step t = c + w
-            for (int t = 0; t <= t_end; ++t) {
-                const int w_hi = min(n_act - 1, t);
-                for (int w = 0; w <= w_hi; ++w) {
-                    const int c = t - w;
-                    const int r0 = w * RB, r1 = min(r0 + RB, tx);
-                    int c0, c1;
-                    rb_chunk_range(r0, r1, tx, ty, c0, c1);
-                    if (c < c0 || c > c1) continue;
-                    const uint32_t it = itw[w];
-                    const uint32_t s = it % (uint32_t)nstage, ph = (it / (uint32_t)nstage) & 1u;
-                    const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
-                    const uint32_t full = bar_full + 8u * (w * nstage + s);
-                    // rows of this block inside the band over frames [32c, 32c+32)
-                    const int lo = max(r0, tx + kChunk * c - ty);
-                    const int hi = min(r1, kChunk * c + kChunk);
-                    const int j0 = (lo - r0) / kBoxRows, j1 = (hi - 1 - r0) / kBoxRows;
-                    mbar_wait_parked(bar_empty + 8u * (w * nstage + s), ph ^ 1u, 2000);
-                    if (p.use_tma) {
-                        if (lane == 0) {
-                            mbar_arrive_expect_tx(full, (uint32_t)(j1 - j0 + 1) * kBoxBytes * (HAS_MASK ? 2u : 1u));
-                            for (int j = j0; j <= j1; ++j) {
-                                const int row = b * p.T_x + r0 + kBoxRows * j;
-                                tma_load_2d(stage + j * kBoxBytes, &tmap_v, full, kChunk * c, row);
-                                if (HAS_MASK)
-                                    tma_load_2d(stage + mask_off + j * kBoxBytes, &tmap_m, full, kChunk * c, row);
-                            }
-                        }
-                    } else {
-                        const int col = kChunk * c + lane;
-                        if (col < p.T_y) {
-                            const int rho1 = min((j1 + 1) * kBoxRows, r1 - r0);
-                            for (int rho = j0 * kBoxRows; rho < rho1; ++rho) {
-                                const size_t g = ((size_t)b * p.T_x + r0 + rho) * (size_t)p.T_y + col;
-                                const uint32_t d = stage + rho * 128 + ((((uint32_t)lane >> 2) ^ (rho & 7)) << 4) + (lane & 3) * 4;
-                                cp_async_4(d, p.value + g);
-                                if (HAS_MASK) cp_async_4(d + mask_off, p.mask + g);
-                            }
-                        }
-                        cp_async_mbar_arrive_noinc(full);
-                    }
-                    __syncwarp();
-                    if (lane == 0) itw[w] = it + 1u;
-                    __syncwarp();
-                }
+        // Refill cursor: walks the same (utterance, chunk) sequence as the DP loop below, nstage
+        // tiles ahead.  The warp refills its own ring: the stage it has just finished reading is
+        // immediately re-armed with the tile it will need nstage chunks later (possibly the first
+        // tile of the CTA's next utterance), so no producer warp and no "empty" barriers exist.
+        int rb = blockIdx.x - (int)gridDim.x, rtx = 0, rty = 0, rc = 0, rc1 = -1;
+        uint32_t rit = 0;
+        auto refill_one = [&]() {
+            while (rc > rc1) {                                  // next utterance this warp works on
+                rb += gridDim.x;
+                if (rb >= p.B) return;
+                rtx = p.t_xs[rb]; rty = p.t_ys[rb];
+                if (!lengths_valid(rtx, rty, p.T_x, p.T_y) || r0 >= rtx) continue;
+                rb_chunk_range(r0, min(r0 + RB, rtx), rtx, rty, rc, rc1);
             }
-        }
-    } else if (warp < ndp) {
-        // ============================ DP wavefront ============================
-        const int w = warp;
+            const int c = rc++;
+            const int r1 = min(r0 + RB, rtx);
+            const uint32_t s = rit % (uint32_t)nstage;
+            ++rit;
+            const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
+            const uint32_t full = bar_full + 8u * (w * nstage + s);
+            // rows of this block inside the band over frames [32c, 32c+32)
+            const int lo = max(r0, rtx + kChunk * c - rty);
+            const int hi = min(r1, kChunk * c + kChunk);
+            const int j0 = (lo - r0) / kBoxRows, j1 = (hi - 1 - r0) / kBoxRows;
+            if (p.use_tma) {
+                if (lane == 0) {
+                    // order this warp's earlier (generic-proxy) reads of the stage before the async-proxy write
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_arrive_expect_tx(full, (uint32_t)(j1 - j0 + 1) * kBoxBytes * (HAS_MASK ? 2u : 1u));
+                    for (int j = j0; j <= j1; ++j) {
+                        const int row = rb * p.T_x + r0 + kBoxRows * j;
+                        tma_load_2d(stage + j * kBoxBytes, &tmap_v, full, kChunk * c, row);
+                        if (HAS_MASK)
+                            tma_load_2d(stage + mask_off + j * kBoxBytes, &tmap_m, full, kChunk * c, row);
+                    }
+                }
+            } else {
+                const int col = kChunk * c + lane;
+                if (col < p.T_y) {
+                    const int rho1 = min((j1 + 1) * kBoxRows, r1 - r0);
+                    for (int rho = j0 * kBoxRows; rho < rho1; ++rho) {
+                        const size_t g = ((size_t)rb * p.T_x + r0 + rho) * (size_t)p.T_y + col;
+                        const uint32_t d = stage + rho * 128 + ((((uint32_t)lane >> 2) ^ (rho & 7)) << 4) + (lane & 3) * 4;
+                        cp_async_4(d, p.value + g);
+                        if (HAS_MASK) cp_async_4(d + mask_off, p.mask + g);
+                    }
+                }
+                cp_async_mbar_arrive_noinc(full);
+            }
+        };
+        for (int i = 0; i < nstage; ++i) refill_one();
+        __syncwarp();
+
         uint32_t it = 0, hin = 0, hout = 0, k = 0;
-        const int r0 = w * RB;
-        const int x0 = r0 + R * lane;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const int tx = p.t_xs[b], ty = p.t_ys[b];
             const uint32_t buf = k & 1u;
             // the backtrack warp must have consumed utterance k-2 before dpdone[buf] is re-armed
             mbar_wait_parked(bar_btdone + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
-            if (lengths_valid(tx, ty, p.T_x, p.T_y)) {
+            if (lengths_valid(tx, ty, p.T_x, p.T_y) && r0 < tx) {
+                // bit words of this utterance: [chunk][token], parked in its own output region
+                uint32_t *bits_g = p.out + (size_t)b * p.T_x * p.T_y;
                 const int n_act = (tx + RB - 1) / RB;
-                if (w < n_act) {
-                    // bit words of this utterance: [chunk][token], parked in its own output region
-                    uint32_t *bits_g = p.out + (size_t)b * p.T_x * p.T_y;
-                    const int r1 = min(r0 + RB, tx);
-                    int c0, c1, c0p = 0, c1p = -1;
-                    rb_chunk_range(r0, r1, tx, ty, c0, c1);
-                    if (w > 0) rb_chunk_range(r0 - RB, r0, tx, ty, c0p, c1p);
-                    const bool has_prev = w > 0, has_next = (w + 1 < n_act);
-                    const int c0n = (r0 + RB) / kChunk;     // first chunk of the next warp
-                    const int cd = (r1 - 1) / kChunk;       // last chunk that holds a diagonal cell
-                    float q[R];
-                    uint32_t bits[R];
+                const int r1 = min(r0 + RB, tx);
+                int c0, c1, c0p = 0, c1p = -1;
+                rb_chunk_range(r0, r1, tx, ty, c0, c1);
+                if (w > 0) rb_chunk_range(r0 - RB, r0, tx, ty, c0p, c1p);
+                const bool has_prev = w > 0, has_next = (w + 1 < n_act);
+                const int c0n = (r0 + RB) / kChunk;     // first chunk of the next warp
+                const int cd = (r1 - 1) / kChunk;       // last chunk that holds a diagonal cell
+                float q[R];
+                uint32_t bits[R];
 #pragma unroll
-                    for (int r = 0; r < R; ++r) q[r] = p.penalty;      // core.pyx:52-53
-                    for (int c = c0; c <= c1; ++c, ++it) {
-                        const uint32_t s = it % (uint32_t)nstage, ph = (it / (uint32_t)nstage) & 1u;
-                        const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
-                        const bool in_h = has_prev && c <= c1p;
-                        const bool out_h = has_next && c >= c0n;
-                        const uint32_t din = hin % kBndDepth, dout = hout % kBndDepth;
-                        const uint32_t bin = base + L.bnd + (((w - 1) * kBndDepth + din) * kBndFloats) * 4u;
-                        const uint32_t bout = base + L.bnd + ((w * kBndDepth + dout) * kBndFloats) * 4u;
+                for (int r = 0; r < R; ++r) q[r] = p.penalty;      // core.pyx:52-53
+                MAS_STAMP(1 + 2 * w);
+                for (int c = c0; c <= c1; ++c, ++it) {
+                    const uint32_t s = it % (uint32_t)nstage, ph = (it / (uint32_t)nstage) & 1u;
+                    const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
+                    const bool in_h = has_prev && c <= c1p;
+                    const bool out_h = has_next && c >= c0n;
+                    const uint32_t din = hin % kBndDepth, dout = hout % kBndDepth;
+                    const uint32_t bin = base + L.bnd + (((w - 1) * kBndDepth + din) * kBndFloats) * 4u;
+                    const uint32_t bout = base + L.bnd + ((w * kBndDepth + dout) * kBndFloats) * 4u;
 #pragma unroll
-                        for (int r = 0; r < R; ++r) bits[r] = 0u;
-                        // every lane waits (warp-uniform control flow keeps the shuffles on the fast path)
-                        mbar_wait_parked(bar_full + 8u * (w * nstage + s), ph, 2000);
-                        if (in_h)
-                            mbar_wait_parked(bar_bdfull + 8u * ((w - 1) * kBndDepth + din), (hin / kBndDepth) & 1u, 2000);
-                        if (out_h)
-                            mbar_wait_parked(bar_bdempty + 8u * (w * kBndDepth + dout), ((hout / kBndDepth) & 1u) ^ 1u, 2000);
-                        __syncwarp();
-                        if (c <= cd)
-                            dp_chunk<R, HAS_MASK, true>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
-                                                        has_prev, bin, out_h, bout);
-                        else
-                            dp_chunk<R, HAS_MASK, false>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
-                                                         has_prev, bin, out_h, bout);
-                        uint32_t *wd = bits_g + (size_t)c * p.T_x + x0;
+                    for (int r = 0; r < R; ++r) bits[r] = 0u;
+                    // every lane waits (warp-uniform control flow keeps the shuffles on the fast path)
+                    mbar_wait_parked(bar_full + 8u * (w * nstage + s), ph, 2000);
+                    if (in_h)
+                        mbar_wait_parked(bar_bdfull + 8u * ((w - 1) * kBndDepth + din), (hin / kBndDepth) & 1u, 2000);
+                    if (out_h)
+                        mbar_wait_parked(bar_bdempty + 8u * (w * kBndDepth + dout), ((hout / kBndDepth) & 1u) ^ 1u, 2000);
+                    __syncwarp();
+                    if (c <= cd)
+                        dp_chunk<R, HAS_MASK, true>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
+                                                    has_prev, bin, out_h, bout);
+                    else
+                        dp_chunk<R, HAS_MASK, false>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
+                                                     has_prev, bin, out_h, bout);
+                    __syncwarp();                               // all lanes are done reading the stage
+                    if (lane == 0 && in_h) mbar_arrive(bar_bdempty + 8u * ((w - 1) * kBndDepth + din));
+                    if (lane == 31 && out_h) mbar_arrive(bar_bdfull + 8u * (w * kBndDepth + dout));
+                    refill_one();
+                    uint32_t *wd = bits_g + (size_t)c * p.T_x + x0;
 #pragma unroll
-                        for (int r = 0; r < R; ++r)
-                            if (x0 + r < p.T_x) wd[r] = bits[r];
-                        __syncwarp();
-                        if (lane == 0) {
-                            mbar_arrive(bar_empty + 8u * (w * nstage + s));
-                            if (in_h) mbar_arrive(bar_bdempty + 8u * ((w - 1) * kBndDepth + din));
-                        }
-                        if (out_h && lane == 31) mbar_arrive(bar_bdfull + 8u * (w * kBndDepth + dout));
-                        hin += in_h ? 1u : 0u;
-                        hout += out_h ? 1u : 0u;
-                    }
+                    for (int r = 0; r < R; ++r)
+                        if (x0 + r < p.T_x) wd[r] = bits[r];
+                    hin += in_h ? 1u : 0u;
+                    hout += out_h ? 1u : 0u;
                 }
             }
+            MAS_STAMP(2 + 2 * w);
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_dpdone + 8u * buf);   // release: this warp's bit words are out
         }
-    } else if (warp == ndp + 1) {
+    } else if (warp == ndp) {
         // ============================ backtrack ============================
         uint32_t k = 0;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
@@ -363,6 +358,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
             int *cs = cs_g + buf * (p.txp + 4);
             mbar_wait_parked(bar_dpdone + 8u * buf, (k >> 1) & 1u, 5000);
             mbar_wait_parked(bar_bempty + 8u * buf, ((k >> 1) & 1u) ^ 1u, 5000);
+            MAS_STAMP(20);
             if (valid) {
                 // core.pyx:87-92: token idx owns frames [cs[idx], cs[idx+1]).  Within one 32-frame
                 // chunk the path descends at most 32 tokens, so lane l holds the word of token
@@ -404,6 +400,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
             } else if (lane == 0 && p.status != nullptr) {
                 atomicAdd(p.status, 1);
             }
+            MAS_STAMP(21);
             __syncwarp();
             if (lane == 0) {
                 info_g[buf].tx = tx; info_g[buf].ty = ty; info_g[buf].valid = valid ? 1 : 0;
@@ -413,16 +410,56 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
         }
     } else {
         // ============================ writers ============================
-        const int ww = warp - ndp - 2;
+        const int ww = warp - ndp - 1;
         uint32_t k = 0;
+        const int wt = ww * 32 + lane;                           // 0..127
+        constexpr int WT = kWriterWarps * 32;
         for (int b = blockIdx.x; b < p.B; b += gridDim.x, ++k) {
             const uint32_t buf = k & 1u;
             const int *cs = cs_g + buf * (p.txp + 4);
-            mbar_wait_parked(bar_bfull + 8u * buf, (k >> 1) & 1u, 20000);
-            const int tx = info_g[buf].valid ? info_g[buf].tx : 0;
             uint32_t *out = p.out + (size_t)b * p.T_x * p.T_y;
             const uint32_t one = p.one_bits;
-            if (p.vec_store) {
+            const size_t n = (size_t)p.T_x * p.T_y;
+            // The head of the slab holds the utterance's bit words until the backtrack is done;
+            // everything behind it is zeroed right away, overlapping the utterance's own DP.
+            size_t head = (size_t)p.n_chunks * p.T_x;
+            head = (head + 3) & ~(size_t)3;
+            if (head > n) head = n;
+            auto zero_fill = [&](size_t lo, size_t hi) {         // lo, hi multiples of 4 when vec_store
+                if (p.vec_store) {
+                    uint4 *o4 = reinterpret_cast<uint4 *>(out);
+                    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+                    const size_t hi4 = hi >> 2;
+                    size_t i = (lo >> 2) + wt;
+                    for (; i + 3 * WT < hi4; i += 4 * WT) {
+                        __stcs(o4 + i, z);
+                        __stcs(o4 + i + 1 * WT, z);
+                        __stcs(o4 + i + 2 * WT, z);
+                        __stcs(o4 + i + 3 * WT, z);
+                    }
+                    for (; i < hi4; i += WT) __stcs(o4 + i, z);
+                } else {
+                    for (size_t i = lo + wt; i < hi; i += WT) __stcs(out + i, 0u);
+                }
+            };
+            if (ww == 0) MAS_STAMP(22);
+            if (p.early_zero) zero_fill(head, n);
+            if (ww == 0) MAS_STAMP(23);
+            mbar_wait_parked(bar_bfull + 8u * buf, (k >> 1) & 1u, 20000);
+            if (ww == 0) MAS_STAMP(24);
+            const int tx = info_g[buf].valid ? info_g[buf].tx : 0;
+            if (p.early_zero) {
+                zero_fill(0, head);
+                // every zero is ordered before the ones dropped on top of it
+                asm volatile("bar.sync 2, %0;" ::"n"(kWriterWarps * 32) : "memory");
+                for (int x = wt; x < tx; x += WT) {               // one token per lane: its run of frames
+                    const int e = cs[x + 1];
+                    uint32_t *row = out + (size_t)x * p.T_y;
+                    for (int c = cs[x]; c < e; ++c) __stcs(row + c, one);
+                }
+            } else if (p.vec_store) {
+                // steady state (many utterances per CTA): one pass, row by row, paced by the
+                // memory system while the DP warps run the next utterance
                 for (int x = ww; x < p.T_x; x += kWriterWarps) {
                     int s = 0, e = 0;
                     if (x < tx) { s = cs[x]; e = cs[x + 1]; }
@@ -447,6 +484,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                         __stcs(row + c, (c >= s && c < e) ? one : 0u);
                 }
             }
+            if (ww == 0) MAS_STAMP(25);
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_bempty + 8u * buf);
         }
@@ -489,7 +527,7 @@ mas_apply_mask_kernel(float *__restrict__ out, const float *__restrict__ value,
 namespace mb200 {
 
 struct MasPlan {
-    int R, ndp, nstage, txp, n_chunks, use_tma, vec_store, threads;
+    int R, ndp, nstage, txp, n_chunks, use_tma, vec_store, threads, early_zero;
     uint32_t smem;
 };
 
@@ -502,7 +540,7 @@ static int env_int(const char *name, int dflt) {
 // number of DP warps and the ring depth.  Measured on B200: R=3 is the sweet spot (a warp's
 // per-frame instruction count stays near its latency floor), R=1 only for <= 2 row groups.
 // Tuning overrides (experiments only): MB200_MAS_R, MB200_MAS_NSTAGE.
-static int mas_make_plan(int T_x, int T_y, bool has_mask, bool aligned16, MasPlan *pl) {
+static int mas_make_plan(int B, int T_x, int T_y, bool has_mask, bool aligned16, MasPlan *pl) {
     const int n_chunks = (T_y + kChunk - 1) / kChunk;
     const int g = (T_x + 31) / 32, txp = 32 * g;
     int R = env_int("MB200_MAS_R", 0);
@@ -522,6 +560,9 @@ static int mas_make_plan(int T_x, int T_y, bool has_mask, bool aligned16, MasPla
     if (ns > kMaxStages) ns = kMaxStages;
     if (ns < 2) ns = 2;
     if (ns < 3 && mas_smem_layout(has_mask, ndp, 3, txp).total + kSmemBlockReserve <= (uint32_t)kSmemPerSM / 2) ns = 3;
+    // at most one utterance per SM: nothing to co-schedule, spend the shared memory on ring depth
+    const bool single_wave = env_int("MB200_MAS_SINGLE_WAVE", B <= kNumSMsB200 ? 1 : 0) != 0;
+    if (single_wave) { ns = (200 * 1024) / stage_bytes; if (ns > 6) ns = 6; if (ns < 2) ns = 2; }
     const int forced = env_int("MB200_MAS_NSTAGE", 0);
     if (forced >= 1 && forced <= kMaxStages) ns = forced;
     for (; ns >= 1; --ns) {
@@ -529,7 +570,8 @@ static int mas_make_plan(int T_x, int T_y, bool has_mask, bool aligned16, MasPla
         if (L.total <= (uint32_t)kMaxSmemPerBlock) {
             pl->R = R; pl->ndp = ndp; pl->nstage = ns; pl->txp = txp; pl->n_chunks = n_chunks;
             pl->use_tma = aligned16 ? 1 : 0; pl->vec_store = 0; pl->smem = L.total;
-            pl->threads = 32 * (ndp + 2 + kWriterWarps);
+            pl->threads = 32 * (ndp + 1 + kWriterWarps);
+            pl->early_zero = env_int("MB200_MAS_EARLY_ZERO", single_wave ? 1 : 0);
             return MB200_OK;
         }
     }
@@ -581,7 +623,7 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
     const bool aligned16 = (T_y % 4 == 0) && ((uintptr_t)values_dev % 16 == 0) &&
                            (!has_mask || (uintptr_t)mask_dev % 16 == 0);
     MasPlan pl;
-    int rc = mas_make_plan(T_x, T_y, has_mask, aligned16, &pl);
+    int rc = mas_make_plan(B, T_x, T_y, has_mask, aligned16, &pl);
     if (rc != MB200_OK) return rc;
     pl.vec_store = (T_y % 4 == 0) && ((uintptr_t)paths_dev % 16 == 0);
 
@@ -606,7 +648,8 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
     p.B = B; p.T_x = T_x; p.T_y = T_y; p.penalty = penalty;
     p.one_bits = (path_dtype == MB200_PATH_F32) ? 0x3f800000u : 1u;
     p.ndp = pl.ndp; p.nstage = pl.nstage; p.txp = pl.txp; p.n_chunks = pl.n_chunks;
-    p.use_tma = pl.use_tma; p.vec_store = pl.vec_store;
+    p.use_tma = pl.use_tma; p.vec_store = pl.vec_store; p.early_zero = pl.early_zero;
+    p.debug = env_int("MB200_MAS_DEBUG", 0);
 
     const int grid = mas_grid(fn, pl, B, nullptr);
     fn<<<grid, pl.threads, pl.smem, (cudaStream_t)stream>>>(tm_v, tm_m, p);
@@ -617,7 +660,7 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
 extern "C" int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int aligned16, int out[8]) {
     if (B <= 0 || T_x <= 0 || T_y <= 0 || !out) return MB200_ERR_INVALID_ARG;
     MasPlan pl;
-    int rc = mas_make_plan(T_x, T_y, has_mask != 0, aligned16 != 0, &pl);
+    int rc = mas_make_plan(B, T_x, T_y, has_mask != 0, aligned16 != 0, &pl);
     if (rc != MB200_OK) return rc;
     MasKernelFn fn = has_mask ? mas_pick_kernel<true>(pl.R) : mas_pick_kernel<false>(pl.R);
     int occ = 0;
@@ -651,5 +694,11 @@ extern "C" int matcha_b200_mas_apply_mask(float *scores_dev, const float *values
     if (blocks > 148LL * 16) blocks = 148LL * 16;
     mas_apply_mask_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(scores_dev, values_dev, mask_dev, (size_t)n);
     MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+// profiling aid, not part of the public header: copies the clock64 stamps out
+extern "C" int matcha_b200_mas_debug_read(long long *out32) {
+    MB200_CUDA_TRY(cudaMemcpyFromSymbol(out32, mb200::g_mas_dbg, sizeof(long long) * 32));
     return MB200_OK;
 }

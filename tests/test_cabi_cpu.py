@@ -55,7 +55,7 @@ def test_launch_plan(lib, shape, has_mask):
     assert lib.matcha_b200_mas_query_launch(*shape, has_mask, 1, ctypes.byref(out)) == 0
     block, smem, r, nstage, use_tma, ndp = out[1], out[2], out[3], out[4], out[5], out[7]
     assert r % 2 == 1 and 1 <= r <= 13 and 1 <= nstage <= 8 and (use_tma & 1) == 1
-    assert block == 32 * (ndp + 6) and block <= 1024
+    assert block == 32 * (ndp + 5) and block <= 1024
     assert 32 * r * ndp >= shape[1], "one wavefront pass must cover every token"
     assert smem <= 232448
 
