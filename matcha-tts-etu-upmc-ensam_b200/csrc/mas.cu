@@ -36,7 +36,7 @@ constexpr int kBoxRows = 32;      // tokens per TMA box
 constexpr int kBoxBytes = kBoxRows * kChunk * 4;
 constexpr int kWriterWarps = 4;
 constexpr int kMaxStages = 8;
-constexpr int kBndDepth = 8;      // boundary-row ring depth between neighbouring DP warps
+constexpr int kBndDepth = 4;      // boundary-row ring depth between neighbouring DP warps
 constexpr int kBndFloats = 36;    // [0]=Q[32c-1], [1..32]=Q[32c..32c+31], padded to 16 bytes
 
 // most DP warps a CTA may carry for a given rows-per-lane (register budget of the SM)
