@@ -1,0 +1,273 @@
+// decoder.cu -- host orchestration and C ABI of the CFM decoder path (fp32 mode).
+//
+// Replaces, behind the reference's own interfaces (paths under
+// /root/reference/matcha/models/components/):
+//   matcha_b200_decoder_forward   <- Decoder.forward(x, mask, mu, t)          decoder.py:271-371
+//   matcha_b200_cfm_solve_euler   <- BaseConditionalFlowMatching.solve_ode_euler
+//                                                                        flow_matching.py:67-104
+// Activations live channels-last [B][T][C] in a caller-provided workspace; the twelve
+// "b c t <-> b t c" rearranges of decoder.py:298-352 disappear, the channel concats of
+// decoder.py:288,341 and the nearest-neighbour resample of :338-339 become addressing inside the
+// implicit-GEMM loader.
+#include "decoder_kernels.cuh"
+
+namespace mb200 {
+
+// ---------------------------------------------------------------- packed weights
+// Order and shapes must match matcha_b200/decoder.py::pack_weights.
+struct StageW {
+    const float *wt, *bt;                   // Resnet1D.mlp[1]            [256][1024], [256]
+    const float *wc1, *bc1, *g1, *be1;      // block1 conv [256][3][Cin], bias, GN gamma/beta
+    const float *wc2, *bc2, *g2, *be2;      // block2 conv [256][3][256]
+    const float *wr, *br;                   // res_conv [256][Cin]
+    const float *ln1g, *ln1b, *wqkv;        // norm1, [768][256] = to_q | to_k | to_v
+    const float *wo, *bo;                   // to_out.0
+    const float *ln3g, *ln3b, *w1, *b1, *w2, *b2;   // norm3, ff.net.0.proj [1024][256], ff.net.2 [256][1024]
+    const float *wtail, *wtail2, *btail;    // down/up conv: [256][3][256]; ConvTranspose: even/odd [256][2][256]
+    int cin;
+};
+struct DecW {
+    const float *freq, *tw1, *tb1, *tw2, *tb2;
+    StageW st[6];
+    const float *wf, *bf, *gf, *bef, *wp, *bp;
+};
+
+static const int kStageCin[6] = {kInCh, kC, kC, kC, 2 * kC, 2 * kC};
+
+static long long build_weights(const float *blob, DecW *w) {
+    long long off = 0;
+    auto take = [&](long long n) { const float *p = blob ? blob + off : nullptr; off += n; return p; };
+    DecW d;
+    d.freq = take(80);
+    d.tw1 = take(1024LL * kInCh); d.tb1 = take(1024);
+    d.tw2 = take(1024LL * 1024); d.tb2 = take(1024);
+    for (int i = 0; i < 6; ++i) {
+        StageW &s = d.st[i];
+        s.cin = kStageCin[i];
+        s.wt = take(256LL * 1024); s.bt = take(256);
+        s.wc1 = take(256LL * 3 * s.cin); s.bc1 = take(256); s.g1 = take(256); s.be1 = take(256);
+        s.wc2 = take(256LL * 3 * 256); s.bc2 = take(256); s.g2 = take(256); s.be2 = take(256);
+        s.wr = take(256LL * s.cin); s.br = take(256);
+        s.ln1g = take(256); s.ln1b = take(256); s.wqkv = take(768LL * 256);
+        s.wo = take(256LL * 256); s.bo = take(256);
+        s.ln3g = take(256); s.ln3b = take(256);
+        s.w1 = take(1024LL * 256); s.b1 = take(1024); s.w2 = take(256LL * 1024); s.b2 = take(256);
+        s.wtail = s.wtail2 = s.btail = nullptr;
+        if (i == 0 || i == 1 || i == 5) { s.wtail = take(256LL * 3 * 256); s.btail = take(256); }
+        if (i == 4) { s.wtail = take(256LL * 2 * 256); s.wtail2 = take(256LL * 2 * 256); s.btail = take(256); }
+    }
+    d.wf = take(256LL * 3 * 256); d.bf = take(256); d.gf = take(256); d.bef = take(256);
+    d.wp = take((long long)kMel * 256); d.bp = take(kMel);
+    if (w) *w = d;
+    return off;
+}
+
+// ---------------------------------------------------------------- workspace
+struct DecWs {
+    float *tb, *x0, *h, *a, *g, *x1, *ln, *qkv, *att, *x2, *f1, *x3, *s0, *s1, *d, *stats;
+};
+
+static long long carve_workspace(float *base, int B, int T, int n_rows, DecWs *ws) {
+    const long long M = (long long)B * T, Mu = (long long)B * (T + 1);
+    long long off = 0;
+    auto take = [&](long long n) { float *p = base ? base + off : nullptr; off += (n + 3) & ~3LL; return p; };
+    DecWs w;
+    w.tb = take(6LL * n_rows * kC);
+    w.x0 = take(M * kInCh);
+    w.h = take(M * kC); w.a = take(M * kC); w.g = take(M * kC); w.x1 = take(M * kC); w.ln = take(M * kC);
+    w.qkv = take(M * 3 * kC); w.att = take(M * kC); w.x2 = take(M * kC); w.f1 = take(M * 4 * kC); w.x3 = take(M * kC);
+    w.s0 = take(M * kC); w.s1 = take(M * kC); w.d = take(Mu * kC);
+    w.stats = take((long long)B * kGroups * 2);
+    if (ws) *ws = w;
+    return off * (long long)sizeof(float);
+}
+
+// ---------------------------------------------------------------- launch helpers
+struct Ctx {
+    cudaStream_t st;
+    const float *mask;   // [B][T] float 0/1, pitch T at every U-Net level (prefix truncation)
+    int B, T;
+    DecWs ws;
+    int launches;
+};
+
+static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int c1, bool masked, int ntaps,
+                 const int *taps, int stride, int Tin, int Tout, const float *w, const float *bias, int N, int act,
+                 const float *res, float *out, int out_T, int out_stride, int out_off) {
+    GemmArgs g;
+    g.a0 = a0; g.a1 = a1; g.c0 = c0; g.c1 = c1; g.Ta0 = Ta0;
+    g.mask = masked ? c.mask : nullptr; g.mask_T = c.T;
+    g.ntaps = ntaps;
+    for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
+    g.stride = stride; g.B = c.B; g.Tin = Tin; g.Tout = Tout;
+    g.w = w; g.bias = bias; g.N = N; g.K = ntaps * (c0 + c1); g.act = act; g.res = res; g.out = out;
+    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off;
+    const int M = c.B * Tout;
+    dim3 grid((M + kBM - 1) / kBM, N / kBN);
+    gemm_f32_kernel<<<grid, 256, 0, c.st>>>(g);
+    c.launches++;
+}
+static void linear(Ctx &c, const float *a, int K, int T, const float *w, const float *bias, int N, int act,
+                   const float *res, float *out) {
+    static const int tap0[1] = {0};
+    gemm(c, a, K, T, nullptr, 0, false, 1, tap0, 1, T, T, w, bias, N, act, res, out, T, 1, 0);
+}
+static void gn_stats(Ctx &c, const float *h, int T) {
+    gn_stats_kernel<<<c.B * kGroups, 256, 0, c.st>>>(h, T, c.ws.stats);
+    c.launches++;
+}
+static void gn_mish(Ctx &c, const float *h, const float *gamma, const float *beta, const float *tb, int per_sample,
+                    float *out, int T) {
+    const long long n4 = (long long)c.B * T * (kC / 4);
+    int blocks = (int)((n4 + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, c.B, T);
+    c.launches++;
+}
+static void layernorm(Ctx &c, const float *x, const float *g, const float *b, float *out, int T) {
+    const size_t rows = (size_t)c.B * T;
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(x, g, b, out, rows);
+    c.launches++;
+}
+
+// Resnet1D + BasicTransformerBlock of one U-Net stage (decoder.py:80-86, transformer.py:316-368).
+// `out` may alias a0: the input is last read by the res_conv GEMM.
+static void run_stage(Ctx &c, const StageW &s, const float *a0, int c0, int Ta0, const float *a1, int c1, int T,
+                      const float *tb, int tb_per_sample, float *out) {
+    static const int taps3[3] = {-1, 0, 1};
+    static const int tap0[1] = {0};
+    DecWs &w = c.ws;
+    gemm(c, a0, c0, Ta0, a1, c1, true, 3, taps3, 1, T, T, s.wc1, s.bc1, kC, 0, nullptr, w.h, T, 1, 0);
+    gn_stats(c, w.h, T);
+    gn_mish(c, w.h, s.g1, s.be1, tb, tb_per_sample, w.a, T);                 // Mish(GN(.))*mask + time bias
+    gemm(c, w.a, kC, T, nullptr, 0, true, 3, taps3, 1, T, T, s.wc2, s.bc2, kC, 0, nullptr, w.h, T, 1, 0);
+    gn_stats(c, w.h, T);
+    gn_mish(c, w.h, s.g2, s.be2, nullptr, 0, w.g, T);
+    gemm(c, a0, c0, Ta0, a1, c1, true, 1, tap0, 1, T, T, s.wr, s.br, kC, 0, w.g, w.x1, T, 1, 0);   // h + res_conv(x*mask)
+    layernorm(c, w.x1, s.ln1g, s.ln1b, w.ln, T);
+    linear(c, w.ln, kC, T, s.wqkv, nullptr, 3 * kC, 0, nullptr, w.qkv);
+    dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
+    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, w.att, T);
+    c.launches++;
+    linear(c, w.att, kC, T, s.wo, s.bo, kC, 0, w.x1, w.x2);
+    layernorm(c, w.x2, s.ln3g, s.ln3b, w.ln, T);
+    linear(c, w.ln, kC, T, s.w1, s.b1, 4 * kC, 1, nullptr, w.f1);
+    linear(c, w.f1, 4 * kC, T, s.w2, s.b2, kC, 0, w.x2, out);
+}
+
+// One estimator call: velocity (x_in == nullptr) or Euler update out = x_in + dt * v.
+static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu, const float *tb_rows, int n_rows,
+                         int tb_per_sample, const float *x_in, float dt, float *out) {
+    static const int taps3[3] = {-1, 0, 1};
+    static const int taps_even[2] = {0, -1};    // ConvTranspose1d(4,2,1): out[2s]   = W[..,1] in[s]   + W[..,3] in[s-1]
+    static const int taps_odd[2] = {1, 0};      //                         out[2s+1] = W[..,0] in[s+1] + W[..,2] in[s]
+    DecWs &w = c.ws;
+    const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
+    auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
+    dim3 pgrid((T + 31) / 32, kInCh / 32, c.B);
+    pack_input_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, w.x0, c.B, T);
+    c.launches++;
+    run_stage(c, W.st[0], w.x0, kInCh, T, nullptr, 0, T, tb(0), tb_per_sample, w.s0);
+    gemm(c, w.s0, kC, T, nullptr, 0, true, 3, taps3, 2, T, T2, W.st[0].wtail, W.st[0].btail, kC, 0, nullptr, w.d, T2, 1, 0);
+    run_stage(c, W.st[1], w.d, kC, T2, nullptr, 0, T2, tb(1), tb_per_sample, w.s1);
+    gemm(c, w.s1, kC, T2, nullptr, 0, true, 3, taps3, 1, T2, T2, W.st[1].wtail, W.st[1].btail, kC, 0, nullptr, w.d, T2, 1, 0);
+    run_stage(c, W.st[2], w.d, kC, T2, nullptr, 0, T2, tb(2), tb_per_sample, w.d);
+    run_stage(c, W.st[3], w.d, kC, T2, nullptr, 0, T2, tb(3), tb_per_sample, w.d);
+    run_stage(c, W.st[4], w.d, kC, T2, w.s1, kC, T2, tb(4), tb_per_sample, w.x3);
+    gemm(c, w.x3, kC, T2, nullptr, 0, true, 2, taps_even, 1, T2, T2, W.st[4].wtail, W.st[4].btail, kC, 0, nullptr, w.d, Tu, 2, 0);
+    gemm(c, w.x3, kC, T2, nullptr, 0, true, 2, taps_odd, 1, T2, T2, W.st[4].wtail2, W.st[4].btail, kC, 0, nullptr, w.d, Tu, 2, 1);
+    run_stage(c, W.st[5], w.d, kC, Tu, w.s0, kC, T, tb(5), tb_per_sample, w.x3);
+    gemm(c, w.x3, kC, T, nullptr, 0, true, 3, taps3, 1, T, T, W.st[5].wtail, W.st[5].btail, kC, 0, nullptr, w.d, T, 1, 0);
+    gemm(c, w.d, kC, T, nullptr, 0, true, 3, taps3, 1, T, T, W.wf, W.bf, kC, 0, nullptr, w.h, T, 1, 0);
+    gn_stats(c, w.h, T);
+    dim3 fgrid((T + 31) / 32, c.B);
+    final_proj_kernel<<<fgrid, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, W.wp, W.bp, x_in, dt, out, T);
+    c.launches++;
+}
+
+static TimeWeights time_weights(const DecW &W) {
+    TimeWeights t;
+    t.freq = W.freq; t.w1 = W.tw1; t.b1 = W.tb1; t.w2 = W.tw2; t.b2 = W.tb2;
+    for (int i = 0; i < 6; ++i) { t.wt[i] = W.st[i].wt; t.bt[i] = W.st[i].bt; }
+    return t;
+}
+
+}  // namespace mb200
+
+using namespace mb200;
+
+namespace {
+struct TimeVals { float v[64]; };
+__global__ void stage_times_kernel(TimeVals tv, int n, float *out) {
+    if (threadIdx.x < n) out[threadIdx.x] = tv.v[threadIdx.x];
+}
+
+int check_common(const void *a, const void *b, const void *c, const void *d, const void *e, const void *f, int B, int T) {
+    if (B <= 0 || T <= 0) return MB200_ERR_INVALID_ARG;
+    if (!a || !b || !c || !d || !e || !f) return MB200_ERR_INVALID_ARG;
+    if (T < 2) return MB200_ERR_UNSUPPORTED;
+    return MB200_OK;
+}
+int prepare(Ctx &c, DecW &W, const float *blob, void *ws, long long ws_bytes, const float *mask, int B, int T,
+            int n_rows, void *stream) {
+    build_weights(blob, &W);
+    if (ws_bytes < carve_workspace(nullptr, B, T, n_rows, nullptr)) return MB200_ERR_INVALID_ARG;
+    if ((uintptr_t)ws % 16 != 0 || (uintptr_t)blob % 16 != 0) return MB200_ERR_INVALID_ARG;
+    carve_workspace((float *)ws, B, T, n_rows, &c.ws);
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
+        attr_set = true;
+    }
+    return MB200_OK;
+}
+}  // namespace
+
+extern "C" long long matcha_b200_decoder_blob_floats(void) { return build_weights(nullptr, nullptr); }
+
+extern "C" long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows) {
+    if (B <= 0 || T <= 0 || n_rows <= 0) return MB200_ERR_INVALID_ARG;
+    return carve_workspace(nullptr, B, T, n_rows, nullptr);
+}
+
+extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_dev, const float *mask_dev,
+                                            const float *t_dev, int n_t, float *out_dev, const float *blob_dev,
+                                            void *ws_dev, long long ws_bytes, int B, int T, int precision,
+                                            void *stream) {
+    int rc = check_common(x_dev, mu_dev, mask_dev, t_dev, out_dev, blob_dev, B, T);
+    if (rc != MB200_OK) return rc;
+    if (!ws_dev || (n_t != 1 && n_t != B)) return MB200_ERR_INVALID_ARG;
+    if (precision != MB200_PREC_F32) return MB200_ERR_UNSUPPORTED;
+    Ctx c; DecW W;
+    rc = prepare(c, W, blob_dev, ws_dev, ws_bytes, mask_dev, B, T, n_t, stream);
+    if (rc != MB200_OK) return rc;
+    time_embed_kernel<<<n_t, 256, 0, c.st>>>(time_weights(W), t_dev, n_t, c.ws.tb);
+    decoder_eval(c, W, x_dev, mu_dev, c.ws.tb, n_t, n_t == B && B > 1 ? 1 : 0, nullptr, 0.f, out_dev);
+    MB200_CUDA_TRY(cudaGetLastError());
+    return c.launches + 1;
+}
+
+extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,
+                                            float *out_dev, const float *t_host, const float *dt_host, int n_steps,
+                                            const float *blob_dev, void *ws_dev, long long ws_bytes, int B, int T,
+                                            int precision, void *stream) {
+    int rc = check_common(x0_dev, mu_dev, mask_dev, out_dev, blob_dev, t_host, B, T);
+    if (rc != MB200_OK) return rc;
+    if (!ws_dev || !dt_host || n_steps < 1 || n_steps > 64) return MB200_ERR_INVALID_ARG;
+    if (precision != MB200_PREC_F32) return MB200_ERR_UNSUPPORTED;
+    Ctx c; DecW W;
+    rc = prepare(c, W, blob_dev, ws_dev, ws_bytes, mask_dev, B, T, n_steps, stream);
+    if (rc != MB200_OK) return rc;
+    // all time embeddings and per-Resnet time biases of the grid in one launch
+    TimeVals tv;
+    for (int i = 0; i < n_steps; ++i) tv.v[i] = t_host[i];
+    float *t_stage = c.ws.h;          // free until the first conv writes it
+    stage_times_kernel<<<1, 64, 0, c.st>>>(tv, n_steps, t_stage);
+    time_embed_kernel<<<n_steps, 256, 0, c.st>>>(time_weights(W), t_stage, n_steps, c.ws.tb);
+    for (int k = 0; k < n_steps; ++k)
+        decoder_eval(c, W, k == 0 ? x0_dev : out_dev, mu_dev, c.ws.tb + (size_t)k * kC, n_steps, 0,
+                     k == 0 ? x0_dev : out_dev, dt_host[k], out_dev);
+    MB200_CUDA_TRY(cudaGetLastError());
+    return c.launches + 2;
+}

@@ -1,0 +1,448 @@
+// decoder_kernels.cuh -- fp32 building blocks of the CFM decoder (channels-last [B][T][C]).
+//
+// Reference arithmetic restated here (paths under /root/reference/matcha/models/components/):
+//   time_embed_kernel   <- SinusoidalPosEmb + TimeStepEmbeddingNet + the six Resnet1D.mlp
+//                          projections                     decoder.py:22-31, 44-49, 75, 82
+//   pack_input_kernel   <- pack([x, mu], "b * t")           decoder.py:288 (to channels-last)
+//   gemm_f32_kernel     <- every nn.Conv1d / nn.ConvTranspose1d / nn.Linear of the path as an
+//                          implicit GEMM (taps gathered on load, x*mask applied on load)
+//                                                           decoder.py:59,78,95,112,192,239,248,251
+//   gn_stats_kernel, gn_mish_kernel <- GroupNorm(8) + Mish + mask (+ time bias)
+//                                                           decoder.py:60-61,66,83
+//   layernorm_kernel    <- nn.LayerNorm(256)                transformer.py:250,285
+//   attention_f32_kernel<- diffusers Attention / SDPA with the additive 0/1 key mask
+//   final_proj_kernel   <- final_norm + Mish + final_proj + masks + the Euler update
+//                                                           decoder.py:367-371, flow_matching.py:95
+#pragma once
+#include "common.cuh"
+
+namespace mb200 {
+
+constexpr int kC = 256;        // decoder width
+constexpr int kHeads = 4, kDHead = 64;
+constexpr int kTimeDim = 1024;
+constexpr int kInCh = 160, kMel = 80;
+constexpr int kGroups = 8, kGroupCh = 32;
+
+// torch: softplus with threshold 20, then x * tanh(.)   (nn.Mish)
+__device__ __forceinline__ float mish_f(float x) {
+    const float sp = (x > 20.0f) ? x : log1pf(expf(x));
+    return x * tanhf(sp);
+}
+__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
+__device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+
+// ------------------------------------------------------------------ time embedding
+// One block per time row (n_rows = Euler steps, or batch items for per-sample t).
+// out_tb[stage][row][256] = Linear_stage(Mish(time_mlp(sinusoidal(t[row]))))
+struct TimeWeights {
+    const float *freq;            // [80], built on the host exactly as decoder.py:26-27 does
+    const float *w1, *b1;         // [1024][160], [1024]
+    const float *w2, *b2;         // [1024][1024], [1024]
+    const float *wt[6], *bt[6];   // [256][1024], [256]
+};
+
+__global__ void __launch_bounds__(256)
+time_embed_kernel(TimeWeights w, const float *__restrict__ t, int n_rows, float *__restrict__ out_tb) {
+    __shared__ float emb[kInCh];
+    __shared__ float h1[kTimeDim];
+    __shared__ float h2[kTimeDim];
+    const int row = blockIdx.x, tid = threadIdx.x;
+    const float tv = t[row];
+    if (tid < 80) {
+        const float a = (1000.0f * tv) * w.freq[tid];           // scale * x * emb, decoder.py:28
+        emb[tid] = sinf(a);
+        emb[80 + tid] = cosf(a);
+    }
+    __syncthreads();
+    for (int o = tid; o < kTimeDim; o += 256) {
+        const float *wr = w.w1 + (size_t)o * kInCh;
+        float acc = 0.f;
+        for (int i = 0; i < kInCh; ++i) acc = fmaf(wr[i], emb[i], acc);
+        h1[o] = silu_f(acc + w.b1[o]);
+    }
+    __syncthreads();
+    // 1024x1024: one warp per output, lanes stride the input (coalesced weight rows)
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int o = warp; o < kTimeDim; o += 8) {
+        const float *wr = w.w2 + (size_t)o * kTimeDim;
+        float acc = 0.f;
+        for (int i = lane; i < kTimeDim; i += 32) acc = fmaf(wr[i], h1[i], acc);
+        for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+        if (lane == 0) h2[o] = mish_f(acc + w.b2[o]);          // Mish of Resnet1D.mlp[0] applied once here
+    }
+    __syncthreads();
+    for (int st = 0; st < 6; ++st) {
+        for (int o = warp; o < kC; o += 8) {
+            const float *wr = w.wt[st] + (size_t)o * kTimeDim;
+            float acc = 0.f;
+            for (int i = lane; i < kTimeDim; i += 32) acc = fmaf(wr[i], h2[i], acc);
+            for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+            if (lane == 0) out_tb[((size_t)st * n_rows + row) * kC + o] = acc + w.bt[st][o];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ input packing
+// X0[b][t][0:80] = x[b][:, t], X0[b][t][80:160] = mu[b][:, t]   (channels-first -> channels-last)
+__global__ void __launch_bounds__(256)
+pack_input_kernel(const float *__restrict__ x, const float *__restrict__ mu, float *__restrict__ out,
+                  int B, int T) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 160 channels
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;                  // 32 x 8
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i, t = t0 + tx;
+        float v = 0.f;
+        if (t < T) v = (c < kMel) ? x[((size_t)b * kMel + c) * T + t] : mu[((size_t)b * kMel + (c - kMel)) * T + t];
+        tile[i][tx] = v;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int t = t0 + i, c = c0 + tx;
+        if (t < T) out[((size_t)b * T + t) * kInCh + c] = tile[tx][i];
+    }
+}
+
+// ------------------------------------------------------------------ implicit-GEMM (fp32 SIMT)
+// out[(b, t*out_stride + out_off)][n] = act(sum_k A[(b,t)][k] * W[n][k] + bias[n]) + res[...][n]
+// A[(b,t)][tap*Ct + c] = src(c)[b][t*stride + tap_off[tap]][c] * mask[b][t_in]   (0 outside [0,Tin))
+// src 0 holds channels [0,c0) (time length Ta0, nearest-resampled to Tin when they differ,
+// decoder.py:338-339), src 1 channels [c0, c0+c1) -- the skip concat of decoder.py:341.
+struct GemmArgs {
+    const float *a0, *a1;
+    int c0, c1, Ta0;
+    const float *mask; int mask_T;
+    int ntaps, tap_off[4], stride;
+    int B, Tin, Tout;
+    const float *w, *bias;
+    int N, K;
+    int act;                      // 0 none, 1 erf-GELU
+    const float *res;             // same indexing as out, or nullptr
+    float *out;
+    int out_T, out_stride, out_off;
+};
+
+constexpr int kBM = 128, kBN = 64, kBK = 16;
+
+__global__ void __launch_bounds__(256)
+gemm_f32_kernel(const GemmArgs g) {
+    __shared__ __align__(16) float As[kBK][kBM + 4];
+    __shared__ __align__(16) float Bs[kBK][kBN + 4];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
+    const int M = g.B * g.Tout, Ct = g.c0 + g.c1;
+
+    // loader coordinates
+    const int lrow = tid >> 1, lkq = (tid & 1) * 2;
+    const int lm = m0 + lrow;
+    const bool lvalid = lm < M;
+    const int lb = lvalid ? lm / g.Tout : 0, lt = lvalid ? lm % g.Tout : 0;
+    const float nn_scale = (float)g.Ta0 / (float)g.Tin;
+    const int wn = tid >> 2, wkq = tid & 3;
+
+    float4 ra[2], rb;
+    auto load_tile = [&](int k0) {
+        const int tap = k0 / Ct, cc = k0 - tap * Ct;
+        const int tin = lt * g.stride + g.tap_off[tap];
+        const bool ok = lvalid && tin >= 0 && tin < g.Tin;
+        float mk = 1.0f;
+        if (ok && g.mask) mk = g.mask[(size_t)lb * g.mask_T + tin];
+        const float *p = nullptr;
+        if (ok) {
+            if (cc < g.c0) {
+                int ts = tin;
+                if (g.Ta0 != g.Tin) { ts = (int)floorf((float)tin * nn_scale); if (ts > g.Ta0 - 1) ts = g.Ta0 - 1; }
+                p = g.a0 + ((size_t)lb * g.Ta0 + ts) * g.c0 + cc;
+            } else {
+                p = g.a1 + ((size_t)lb * g.Tin + tin) * g.c1 + (cc - g.c0);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok) v = *reinterpret_cast<const float4 *>(p + (lkq + i) * 4);
+            v.x *= mk; v.y *= mk; v.z *= mk; v.w *= mk;
+            ra[i] = v;
+        }
+        rb = *reinterpret_cast<const float4 *>(g.w + (size_t)(n0 + wn) * g.K + k0 + wkq * 4);
+    };
+    auto store_tile = [&]() {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int k = (lkq + i) * 4;
+            As[k + 0][lrow] = ra[i].x; As[k + 1][lrow] = ra[i].y; As[k + 2][lrow] = ra[i].z; As[k + 3][lrow] = ra[i].w;
+        }
+        const int k = wkq * 4;
+        Bs[k + 0][wn] = rb.x; Bs[k + 1][wn] = rb.y; Bs[k + 2][wn] = rb.z; Bs[k + 3][wn] = rb.w;
+    };
+
+    const int ty = tid >> 4, tx = tid & 15;
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    load_tile(0);
+    for (int k0 = 0; k0 < g.K; k0 += kBK) {
+        store_tile();
+        __syncthreads();
+        if (k0 + kBK < g.K) load_tile(k0 + kBK);
+#pragma unroll
+        for (int k = 0; k < kBK; ++k) {
+            const float4 a_lo = *reinterpret_cast<const float4 *>(&As[k][ty * 8]);
+            const float4 a_hi = *reinterpret_cast<const float4 *>(&As[k][ty * 8 + 4]);
+            const float4 bv = *reinterpret_cast<const float4 *>(&Bs[k][tx * 4]);
+            const float a[8] = {a_lo.x, a_lo.y, a_lo.z, a_lo.w, a_hi.x, a_hi.y, a_hi.z, a_hi.w};
+            const float b[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+
+    const int n = n0 + tx * 4;
+    float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int m = m0 + ty * 8 + i;
+        if (m >= M) continue;
+        const int b = m / g.Tout, t = m - b * g.Tout;
+        const size_t o = ((size_t)b * g.out_T + (size_t)t * g.out_stride + g.out_off) * g.N + n;
+        float4 v = make_float4(acc[i][0] + bias.x, acc[i][1] + bias.y, acc[i][2] + bias.z, acc[i][3] + bias.w);
+        if (g.act == 1) { v.x = gelu_erf_f(v.x); v.y = gelu_erf_f(v.y); v.z = gelu_erf_f(v.z); v.w = gelu_erf_f(v.w); }
+        if (g.res) {
+            const float4 r = *reinterpret_cast<const float4 *>(g.res + o);
+            v.x += r.x; v.y += r.y; v.z += r.z; v.w += r.w;
+        }
+        *reinterpret_cast<float4 *>(g.out + o) = v;
+    }
+}
+
+// ------------------------------------------------------------------ GroupNorm(8, 256)
+// stats[(b*8+g)*2] = mean, [..+1] = rstd over 32 channels x T frames (biased variance, eps 1e-5;
+// the statistics run over the full padded T).
+__global__ void __launch_bounds__(256)
+gn_stats_kernel(const float *__restrict__ h, int T, float *__restrict__ stats) {
+    const int b = blockIdx.x / kGroups, grp = blockIdx.x % kGroups;
+    const float *p = h + (size_t)b * T * kC + grp * kGroupCh;
+    double s = 0.0, ss = 0.0;
+    const int n4 = T * (kGroupCh / 4);
+    for (int i = threadIdx.x; i < n4; i += 256) {
+        const int t = i >> 3, c4 = i & 7;
+        const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)t * kC + c4 * 4);
+        s += (double)v.x + (double)v.y + (double)v.z + (double)v.w;
+        ss += (double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z + (double)v.w * v.w;
+    }
+    __shared__ double rs[8], rss[8];
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    }
+    if ((threadIdx.x & 31) == 0) { rs[threadIdx.x >> 5] = s; rss[threadIdx.x >> 5] = ss; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, q = 0.0;
+        for (int i = 0; i < 8; ++i) { a += rs[i]; q += rss[i]; }
+        const double n = (double)T * kGroupCh;
+        const double mean = a / n;
+        double var = q / n - mean * mean;
+        if (var < 0.0) var = 0.0;
+        stats[blockIdx.x * 2] = (float)mean;
+        stats[blockIdx.x * 2 + 1] = (float)(1.0 / sqrt(var + 1e-5));
+    }
+}
+
+// out = Mish(GN(h)) * mask (+ tb[row_b][c])          Block1D, decoder.py:60-61,66 (+ :83)
+__global__ void __launch_bounds__(256)
+gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, const float *__restrict__ gamma,
+               const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
+               const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out, int B, int T) {
+    const size_t n4 = (size_t)B * T * (kC / 4);
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        const int c = (int)(i % (kC / 4)) * 4;
+        const size_t row = i / (kC / 4);
+        const int b = (int)(row / T), t = (int)(row % T);
+        const float mean = stats[(b * kGroups + c / kGroupCh) * 2], rstd = stats[(b * kGroups + c / kGroupCh) * 2 + 1];
+        const float mk = mask[(size_t)b * mask_T + t];
+        const float4 v = *reinterpret_cast<const float4 *>(h + i * 4);
+        const float4 ga = *reinterpret_cast<const float4 *>(gamma + c), be = *reinterpret_cast<const float4 *>(beta + c);
+        float4 o;
+        o.x = mish_f((v.x - mean) * rstd * ga.x + be.x) * mk;
+        o.y = mish_f((v.y - mean) * rstd * ga.y + be.y) * mk;
+        o.z = mish_f((v.z - mean) * rstd * ga.z + be.z) * mk;
+        o.w = mish_f((v.w - mean) * rstd * ga.w + be.w) * mk;
+        if (tb) {
+            const float4 tv = *reinterpret_cast<const float4 *>(tb + (size_t)(tb_per_sample ? b : 0) * kC + c);
+            o.x += tv.x; o.y += tv.y; o.z += tv.z; o.w += tv.w;
+        }
+        *reinterpret_cast<float4 *>(out + i * 4) = o;
+    }
+}
+
+// ------------------------------------------------------------------ LayerNorm(256), eps 1e-5
+// one warp per row
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta,
+                 float *__restrict__ out, size_t rows) {
+    const int lane = threadIdx.x & 31;
+    const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const float *p = x + row * kC;
+    const float4 a = *reinterpret_cast<const float4 *>(p + lane * 4);
+    const float4 b = *reinterpret_cast<const float4 *>(p + 128 + lane * 4);
+    float s = a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s * (1.0f / kC);
+    float d[8] = {a.x - mean, a.y - mean, a.z - mean, a.w - mean, b.x - mean, b.y - mean, b.z - mean, b.w - mean};
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) q = fmaf(d[i], d[i], q);
+    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = rsqrtf(q * (1.0f / kC) + 1e-5f);
+    const float4 g0 = *reinterpret_cast<const float4 *>(gamma + lane * 4), g1 = *reinterpret_cast<const float4 *>(gamma + 128 + lane * 4);
+    const float4 b0 = *reinterpret_cast<const float4 *>(beta + lane * 4), b1 = *reinterpret_cast<const float4 *>(beta + 128 + lane * 4);
+    float4 o0 = make_float4(d[0] * rstd * g0.x + b0.x, d[1] * rstd * g0.y + b0.y, d[2] * rstd * g0.z + b0.z, d[3] * rstd * g0.w + b0.w);
+    float4 o1 = make_float4(d[4] * rstd * g1.x + b1.x, d[5] * rstd * g1.y + b1.y, d[6] * rstd * g1.z + b1.z, d[7] * rstd * g1.w + b1.w);
+    *reinterpret_cast<float4 *>(out + row * kC + lane * 4) = o0;
+    *reinterpret_cast<float4 *>(out + row * kC + 128 + lane * 4) = o1;
+}
+
+// ------------------------------------------------------------------ attention (fp32 SIMT)
+// softmax_j(q_i . k_j / 8 + mask01[b][j]) v_j per head; qkv rows are [q(256) | k(256) | v(256)],
+// head h at columns h*64.  The float 0/1 key mask is ADDED to the logits: padded keys
+// are not excluded, only frames beyond T are.
+constexpr int kAttBQ = 64, kAttBK = 64, kAttPitch = 68;
+constexpr int kAttSmemBytes = (2 * kAttBK * kAttPitch + kAttBQ * kAttPitch) * 4;
+
+__global__ void __launch_bounds__(128)
+attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ mask, int mask_T,
+                     float *__restrict__ out, int T) {
+    extern __shared__ __align__(16) float att_smem[];
+    float (*Ks)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem);
+    float (*Vs)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem + kAttBK * kAttPitch);
+    float (*Ps)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem + 2 * kAttBK * kAttPitch);
+    const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * kAttBQ;
+    const int tid = threadIdx.x, r = tid >> 1, half = tid & 1;
+    const int tq = q0 + r;
+    const float *base = qkv + (size_t)b * T * (3 * kC) + h * kDHead;
+
+    float q[kDHead];
+#pragma unroll
+    for (int d = 0; d < kDHead; d += 4) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tq < T) v = *reinterpret_cast<const float4 *>(base + (size_t)tq * (3 * kC) + d);
+        q[d] = v.x; q[d + 1] = v.y; q[d + 2] = v.z; q[d + 3] = v.w;
+    }
+    float o[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) o[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+
+    for (int k0 = 0; k0 < T; k0 += kAttBK) {
+        __syncthreads();
+        for (int i = tid; i < kAttBK * (kDHead / 4); i += 128) {
+            const int j = i >> 4, d4 = (i & 15) * 4;
+            float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
+            if (k0 + j < T) {
+                const float *p = base + (size_t)(k0 + j) * (3 * kC);
+                kv = *reinterpret_cast<const float4 *>(p + kC + d4);
+                vv = *reinterpret_cast<const float4 *>(p + 2 * kC + d4);
+            }
+            *reinterpret_cast<float4 *>(&Ks[j][d4]) = kv;
+            *reinterpret_cast<float4 *>(&Vs[j][d4]) = vv;
+        }
+        __syncthreads();
+        float s[32];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) {
+            const int j = half * 32 + jj;
+            float acc = 0.f;
+#pragma unroll
+            for (int d = 0; d < kDHead; d += 4) {
+                const float4 kv = *reinterpret_cast<const float4 *>(&Ks[j][d]);
+                acc = fmaf(q[d], kv.x, acc); acc = fmaf(q[d + 1], kv.y, acc);
+                acc = fmaf(q[d + 2], kv.z, acc); acc = fmaf(q[d + 3], kv.w, acc);
+            }
+            const int tk = k0 + j;
+            s[jj] = (tk < T) ? fmaf(acc, 0.125f, mask[(size_t)b * mask_T + tk]) : -INFINITY;
+            mx = fmaxf(mx, s[jj]);
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        const float m_new = fmaxf(m_run, mx);
+        const float corr = expf(m_run - m_new);          // first block: exp(-inf) = 0
+        float ps = 0.f;
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) {
+            const float pv = expf(s[jj] - m_new);
+            ps += pv;
+            Ps[r][half * 32 + jj] = pv;
+        }
+        ps += __shfl_xor_sync(0xffffffffu, ps, 1);
+        l_run = l_run * corr + ps;
+        m_run = m_new;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] *= corr;
+        __syncwarp();
+        for (int j = 0; j < kAttBK; ++j) {
+            const float pv = Ps[r][j];
+#pragma unroll
+            for (int d = 0; d < 32; d += 4) {
+                const float4 vv = *reinterpret_cast<const float4 *>(&Vs[j][half * 32 + d]);
+                o[d] = fmaf(pv, vv.x, o[d]); o[d + 1] = fmaf(pv, vv.y, o[d + 1]);
+                o[d + 2] = fmaf(pv, vv.z, o[d + 2]); o[d + 3] = fmaf(pv, vv.w, o[d + 3]);
+            }
+        }
+    }
+    if (tq < T) {
+        const float inv = 1.0f / l_run;
+        float *po = out + ((size_t)b * T + tq) * kC + h * kDHead + half * 32;
+#pragma unroll
+        for (int d = 0; d < 32; d += 4)
+            *reinterpret_cast<float4 *>(po + d) = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
+    }
+}
+
+// ------------------------------------------------------------------ final norm + proj + Euler
+// v[b][n][t] = (sum_c Mish(GN(hf))[b][t][c]*mask * Wp[n][c] + bp[n]) * mask     decoder.py:367-371
+// out = x_in + dt * v  (flow_matching.py:95) when x_in != nullptr, else out = v.  Channels-first out.
+__global__ void __launch_bounds__(256)
+final_proj_kernel(const float *__restrict__ hf, const float *__restrict__ stats, const float *__restrict__ gamma,
+                  const float *__restrict__ beta, const float *__restrict__ mask, const float *__restrict__ wp,
+                  const float *__restrict__ bp, const float *__restrict__ x_in, float dt,
+                  float *__restrict__ out, int T) {
+    __shared__ float A[32][kC + 1];
+    const int b = blockIdx.y, t0 = blockIdx.x * 32, tid = threadIdx.x;
+    for (int i = tid; i < 32 * kC; i += 256) {
+        const int tt = i >> 8, c = i & 255;
+        const int t = t0 + tt;
+        float v = 0.f;
+        if (t < T) {
+            const float mean = stats[(b * kGroups + c / kGroupCh) * 2], rstd = stats[(b * kGroups + c / kGroupCh) * 2 + 1];
+            v = mish_f((hf[((size_t)b * T + t) * kC + c] - mean) * rstd * gamma[c] + beta[c]) * mask[(size_t)b * T + t];
+        }
+        A[tt][c] = v;
+    }
+    __syncthreads();
+    const int lane = tid & 31, warp = tid >> 5;
+    const int t = t0 + lane;
+    const float mk = (t < T) ? mask[(size_t)b * T + t] : 0.f;
+    for (int n = warp * 10; n < warp * 10 + 10; ++n) {
+        const float *wr = wp + (size_t)n * kC;
+        float acc = 0.f;
+#pragma unroll 8
+        for (int c = 0; c < kC; ++c) acc = fmaf(A[lane][c], __ldg(wr + c), acc);
+        if (t < T) {
+            const float v = (acc + bp[n]) * mk;
+            const size_t o = ((size_t)b * kMel + n) * T + t;
+            out[o] = x_in ? __fadd_rn(x_in[o], __fmul_rn(dt, v)) : v;   // x + dt * v, two roundings as in torch
+        }
+    }
+}
+
+}  // namespace mb200

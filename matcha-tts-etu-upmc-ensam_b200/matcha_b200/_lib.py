@@ -51,6 +51,16 @@ def load_library():
     lib.matcha_b200_mas_query_launch.argtypes = [c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int * 8)]
     lib.matcha_b200_mas_apply_mask.restype = c_int
     lib.matcha_b200_mas_apply_mask.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_void_p]
+    ll = ctypes.c_longlong
+    lib.matcha_b200_decoder_blob_floats.restype = ll
+    lib.matcha_b200_decoder_workspace_bytes.restype = ll
+    lib.matcha_b200_decoder_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.matcha_b200_decoder_forward.restype = c_int
+    lib.matcha_b200_decoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                                c_void_p, ll, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_cfm_solve_euler.restype = c_int
+    lib.matcha_b200_cfm_solve_euler.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                                c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
     _LIB = lib
     return lib
 
@@ -71,4 +81,8 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_maximum_path_host",
     "matcha_b200_mas_query_launch",
     "matcha_b200_mas_apply_mask",
+    "matcha_b200_decoder_blob_floats",
+    "matcha_b200_decoder_workspace_bytes",
+    "matcha_b200_decoder_forward",
+    "matcha_b200_cfm_solve_euler",
 )

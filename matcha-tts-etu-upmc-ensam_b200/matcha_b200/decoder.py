@@ -1,0 +1,210 @@
+"""Drop-in for ``matcha.models.components.decoder.Decoder`` backed by the sm_100a decoder kernels.
+
+Mirrors /root/reference/matcha/models/components/decoder.py:118-371:
+  ``Decoder(in_channels=160, out_channels=80, channels=(256,256), ...).forward(x, mask, mu, t, cond=None)``
+with the reference's ``state_dict`` names (SURVEY.md §8 b-names), so a Lightning checkpoint
+(``decoder.estimator.*``) or a freshly built reference module can be copied over 1:1 with
+``load_state_dict``.  Inference only (the reference runs it under ``torch.inference_mode``); all
+arithmetic happens in ``lib/libmatcha_b200.so`` -- no CPU fallback.
+"""
+import ctypes
+import math
+from collections import OrderedDict
+
+import torch
+
+from ._lib import check, load_library
+
+PREC_F32, PREC_BF16 = 0, 1
+_PRECISIONS = {"fp32": PREC_F32, "f32": PREC_F32, "bf16": PREC_BF16}
+
+C, TIME_DIM, IN_CH, OUT_CH = 256, 1024, 160, 80
+_STAGES = ("Downsampling_Blocks.0", "Downsampling_Blocks.1", "Mid_Blocks.0", "Mid_Blocks.1",
+           "Upsampling_Blocks.0", "Upsampling_Blocks.1")
+_STAGE_CIN = (IN_CH, C, C, C, 2 * C, 2 * C)
+
+
+def _stream_ptr(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def expected_keys():
+    """The reference's state_dict keys and shapes for the configured decoder."""
+    s = OrderedDict()
+    s["time_mlp.linear_1.weight"] = (TIME_DIM, IN_CH); s["time_mlp.linear_1.bias"] = (TIME_DIM,)
+    s["time_mlp.linear_2.weight"] = (TIME_DIM, TIME_DIM); s["time_mlp.linear_2.bias"] = (TIME_DIM,)
+    for p, cin in zip(_STAGES, _STAGE_CIN):
+        r, t = p + ".0", p + ".1.0"
+        s[r + ".mlp.1.weight"] = (C, TIME_DIM); s[r + ".mlp.1.bias"] = (C,)
+        s[r + ".block1.block.0.weight"] = (C, cin, 3); s[r + ".block1.block.0.bias"] = (C,)
+        s[r + ".block1.block.1.weight"] = (C,); s[r + ".block1.block.1.bias"] = (C,)
+        s[r + ".block2.block.0.weight"] = (C, C, 3); s[r + ".block2.block.0.bias"] = (C,)
+        s[r + ".block2.block.1.weight"] = (C,); s[r + ".block2.block.1.bias"] = (C,)
+        s[r + ".res_conv.weight"] = (C, cin, 1); s[r + ".res_conv.bias"] = (C,)
+        s[t + ".norm1.weight"] = (C,); s[t + ".norm1.bias"] = (C,)
+        for n in ("to_q", "to_k", "to_v"):
+            s[t + f".attn1.{n}.weight"] = (C, C)
+        s[t + ".attn1.to_out.0.weight"] = (C, C); s[t + ".attn1.to_out.0.bias"] = (C,)
+        s[t + ".norm3.weight"] = (C,); s[t + ".norm3.bias"] = (C,)
+        s[t + ".ff.net.0.proj.weight"] = (4 * C, C); s[t + ".ff.net.0.proj.bias"] = (4 * C,)
+        s[t + ".ff.net.2.weight"] = (C, 4 * C); s[t + ".ff.net.2.bias"] = (C,)
+    s["Downsampling_Blocks.0.2.conv.weight"] = (C, C, 3); s["Downsampling_Blocks.0.2.conv.bias"] = (C,)
+    s["Downsampling_Blocks.1.2.weight"] = (C, C, 3); s["Downsampling_Blocks.1.2.bias"] = (C,)
+    s["Upsampling_Blocks.0.2.conv.weight"] = (C, C, 4); s["Upsampling_Blocks.0.2.conv.bias"] = (C,)
+    s["Upsampling_Blocks.1.2.weight"] = (C, C, 3); s["Upsampling_Blocks.1.2.bias"] = (C,)
+    s["final_conv.weight"] = (C, C, 3); s["final_conv.bias"] = (C,)
+    s["final_norm.weight"] = (C,); s["final_norm.bias"] = (C,)
+    s["final_proj.weight"] = (OUT_CH, C, 1); s["final_proj.bias"] = (OUT_CH,)
+    return s
+
+
+def _conv_taps_major(w):
+    """Conv1d weight [out, cin, k] -> [out, k, cin]: GEMM K index = tap * cin + channel."""
+    return w.permute(0, 2, 1).contiguous()
+
+
+def pack_weights(sd):
+    """Packs a reference state_dict (fp32, any device) into the flat fp32 blob the C ABI expects.
+    Order must match csrc/decoder.cu::build_weights."""
+    w = {k: v.detach().to("cpu", torch.float32) for k, v in sd.items()}
+    parts = []
+    half = IN_CH // 2
+    freq = torch.log(torch.tensor(10000.0)) / (half - 1)                       # decoder.py:26
+    parts.append(torch.exp(torch.arange(half, dtype=torch.float32) * -freq))   # decoder.py:27
+    for n in ("time_mlp.linear_1", "time_mlp.linear_2"):
+        parts += [w[n + ".weight"], w[n + ".bias"]]
+    for i, p in enumerate(_STAGES):
+        r, t = p + ".0", p + ".1.0"
+        parts += [w[r + ".mlp.1.weight"], w[r + ".mlp.1.bias"]]
+        parts += [_conv_taps_major(w[r + ".block1.block.0.weight"]), w[r + ".block1.block.0.bias"],
+                  w[r + ".block1.block.1.weight"], w[r + ".block1.block.1.bias"]]
+        parts += [_conv_taps_major(w[r + ".block2.block.0.weight"]), w[r + ".block2.block.0.bias"],
+                  w[r + ".block2.block.1.weight"], w[r + ".block2.block.1.bias"]]
+        parts += [w[r + ".res_conv.weight"][:, :, 0], w[r + ".res_conv.bias"]]
+        parts += [w[t + ".norm1.weight"], w[t + ".norm1.bias"],
+                  torch.cat([w[t + ".attn1.to_q.weight"], w[t + ".attn1.to_k.weight"], w[t + ".attn1.to_v.weight"]], 0)]
+        parts += [w[t + ".attn1.to_out.0.weight"], w[t + ".attn1.to_out.0.bias"]]
+        parts += [w[t + ".norm3.weight"], w[t + ".norm3.bias"], w[t + ".ff.net.0.proj.weight"], w[t + ".ff.net.0.proj.bias"],
+                  w[t + ".ff.net.2.weight"], w[t + ".ff.net.2.bias"]]
+        if i == 0:
+            parts += [_conv_taps_major(w[p + ".2.conv.weight"]), w[p + ".2.conv.bias"]]
+        elif i in (1, 5):
+            parts += [_conv_taps_major(w[p + ".2.weight"]), w[p + ".2.bias"]]
+        elif i == 4:
+            wt = w[p + ".2.conv.weight"]                  # ConvTranspose1d: [cin, cout, 4]
+            even = torch.stack([wt[:, :, 1].t(), wt[:, :, 3].t()], 1)      # [cout][2][cin]: taps in[s], in[s-1]
+            odd = torch.stack([wt[:, :, 0].t(), wt[:, :, 2].t()], 1)       #                  taps in[s+1], in[s]
+            parts += [even, odd, w[p + ".2.conv.bias"]]
+    parts += [_conv_taps_major(w["final_conv.weight"]), w["final_conv.bias"], w["final_norm.weight"], w["final_norm.bias"],
+              w["final_proj.weight"][:, :, 0], w["final_proj.bias"]]
+    blob = torch.cat([p.contiguous().reshape(-1) for p in parts])
+    n = int(load_library().matcha_b200_decoder_blob_floats())
+    assert blob.numel() == n, f"packed {blob.numel()} floats, library expects {n}"
+    return blob
+
+
+class Decoder(torch.nn.Module):
+    """Same constructor signature and ``forward`` as the reference Decoder (decoder.py:149-159, 271)."""
+
+    def __init__(self, in_channels=IN_CH, out_channels=OUT_CH, channels=(256, 256), dropout=0.05,
+                 attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=4, precision="fp32"):
+        super().__init__()
+        if (in_channels, out_channels, tuple(channels), attention_head_dim, n_blocks, num_mid_blocks, num_heads) != \
+                (IN_CH, OUT_CH, (256, 256), 64, 1, 2, 4):
+            raise NotImplementedError("matcha_b200.Decoder implements the reference's configured architecture only "
+                                      "(matcha_tts.py:146-153, 167-172)")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.precision = precision
+        self._weights = None          # reference-named fp32 tensors (CPU)
+        self._blob = {}               # device -> packed blob
+        self._ws = {}                 # (device, B, T, rows) -> workspace
+
+    # -- weights ----------------------------------------------------------------------------
+    def load_state_dict(self, state_dict, strict=True):
+        sd = OrderedDict()
+        for k, v in state_dict.items():
+            for prefix in ("decoder.estimator.", "estimator."):
+                if k.startswith(prefix):
+                    k = k[len(prefix):]
+            sd[k] = v
+        exp = expected_keys()
+        missing = [k for k in exp if k not in sd]
+        bad = [k for k in exp if k in sd and tuple(sd[k].shape) != exp[k]]
+        if missing or bad:
+            raise KeyError(f"state_dict mismatch: missing {missing[:4]}..., wrong shape {bad[:4]}...")
+        self._weights = OrderedDict((k, sd[k].detach().to("cpu", torch.float32).clone()) for k in exp)
+        self._blob.clear()
+        return self
+
+    def state_dict(self, *a, **k):
+        return OrderedDict(self._weights or {})
+
+    def _blob_on(self, device):
+        if self._weights is None:
+            raise RuntimeError("matcha_b200.Decoder has no weights: call load_state_dict first")
+        key = str(device)
+        if key not in self._blob:
+            self._blob[key] = pack_weights(self._weights).to(device)
+        return self._blob[key]
+
+    def _workspace(self, device, B, T, rows):
+        key = (str(device), B, T, rows)
+        if key not in self._ws:
+            n = int(load_library().matcha_b200_decoder_workspace_bytes(B, T, rows))
+            self._ws = {key: torch.empty(n, dtype=torch.uint8, device=device)}      # keep one shape alive
+        return self._ws[key]
+
+    # -- forward ----------------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, x, mask, mu, t, cond=None):
+        """x, mu [B,80,T]; mask [B,1,T] float; t 0-d or [B].  Returns the velocity [B,80,T] (fp32)."""
+        if not x.is_cuda:
+            raise RuntimeError("matcha_b200.Decoder needs CUDA tensors (sm_100a); there is no CPU fallback")
+        lib = load_library()
+        B, _, T = x.shape
+        dev = x.device
+        xf, muf = x.float().contiguous(), mu.float().contiguous()
+        mf = mask.float().reshape(B, T).contiguous()
+        tf = t.detach().to(dev, torch.float32).reshape(-1).contiguous()
+        assert tf.numel() in (1, B)
+        out = torch.empty_like(xf)
+        blob, ws = self._blob_on(dev), self._workspace(dev, B, T, tf.numel())
+        with torch.cuda.device(dev):
+            check(lib.matcha_b200_decoder_forward(xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), tf.data_ptr(), tf.numel(),
+                                                  out.data_ptr(), blob.data_ptr(), ws.data_ptr(), ws.numel(), B, T,
+                                                  _PRECISIONS[self.precision], _stream_ptr(dev)), "decoder_forward")
+        return out.to(x.dtype)
+
+    @torch.no_grad()
+    def solve_euler(self, x, t_span, mu, mask):
+        """The whole Euler loop of flow_matching.py:67-104 in one C call."""
+        lib = load_library()
+        B, _, T = x.shape
+        dev = x.device
+        ts, dts = euler_time_grid(t_span.detach().to("cpu", torch.float32))
+        n = len(ts)
+        xf, muf = x.float().contiguous(), mu.float().contiguous()
+        mf = mask.float().reshape(B, T).contiguous()
+        out = torch.empty_like(xf)
+        blob, ws = self._blob_on(dev), self._workspace(dev, B, T, n)
+        t_arr = (ctypes.c_float * n)(*[float(v) for v in ts])
+        dt_arr = (ctypes.c_float * n)(*[float(v) for v in dts])
+        with torch.cuda.device(dev):
+            self.last_launches = check(lib.matcha_b200_cfm_solve_euler(
+                xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), out.data_ptr(), t_arr, dt_arr, n, blob.data_ptr(),
+                ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision], _stream_ptr(dev)), "cfm_solve_euler")
+        return out.to(x.dtype)
+
+
+def euler_time_grid(t_span):
+    """(t_k, dt_k) exactly as the reference loop produces them in fp32 (flow_matching.py:85-102)."""
+    ts, dts = [], []
+    t = t_span[0]
+    dt = t_span[1] - t_span[0]
+    n = len(t_span) - 1
+    for step in range(1, n + 1):
+        ts.append(t.clone()); dts.append(dt.clone())
+        t = t + dt
+        if step < n:
+            dt = t_span[step + 1] - t
+    return ts, dts
