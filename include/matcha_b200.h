@@ -96,26 +96,31 @@ int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int alig
  *   matcha_b200_cfm_solve_euler  <- BaseConditionalFlowMatching.solve_ode_euler   flow_matching.py:67-104
  * x, mu, out: [B][80][T] fp32 channels-first, as the Python API delivers them; mask: [B][T] (= [B][1][T])
  * fp32 0/1.  blob: the packed weights (matcha_b200.decoder.pack_weights, matcha_b200_decoder_blob_floats()
- * floats, 16-byte aligned).  ws: caller-provided scratch of matcha_b200_decoder_workspace_bytes(B, T, n_rows)
+ * floats, 16-byte aligned).  ws: caller-provided scratch of matcha_b200_decoder_workspace_bytes(B, T, n_rows, precision)
  * bytes, n_rows = number of distinct time rows (n_t, or n_steps).  Nothing is allocated inside.
  * Both return the number of kernels launched (> 0) or a negative error.                           */
 #define MB200_PREC_F32   0   /* fp32 SIMT arithmetic: rel-L2 <= 1e-5 against the fp32 reference */
 #define MB200_PREC_BF16  1   /* bf16 tensor-core GEMMs, fp32 residual stream and statistics     */
 
 long long matcha_b200_decoder_blob_floats(void);
-long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows);
+/* bf16 mode: GEMM weights re-packed as bf16 (input channels padded to 64) by matcha_b200_decoder_pack_bf16 into a
+ * caller-provided buffer of matcha_b200_decoder_blob_bf16_bytes() bytes; pass NULL in fp32 mode. */
+long long matcha_b200_decoder_blob_bf16_bytes(void);
+int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_bf16_dev, void *stream);
+long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows, int precision);
 
 /* t_dev: n_t = 1 (one time for the whole batch, as in the Euler loop) or n_t = B (compute_loss) */
 int matcha_b200_decoder_forward(const float *x_dev, const float *mu_dev, const float *mask_dev,
                                 const float *t_dev, int n_t, float *out_dev, const float *blob_dev,
-                                void *ws_dev, long long ws_bytes, int B, int T, int precision, void *stream);
+                                const void *blob_bf16_dev, void *ws_dev, long long ws_bytes, int B, int T,
+                                int precision, void *stream);
 
 /* t_host/dt_host: the n_steps (t_k, dt_k) pairs the reference loop produces in fp32
  * (flow_matching.py:85-102); out_dev may not alias x0_dev.  n_steps <= 64. */
 int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,
                                 float *out_dev, const float *t_host, const float *dt_host, int n_steps,
-                                const float *blob_dev, void *ws_dev, long long ws_bytes, int B, int T,
-                                int precision, void *stream);
+                                const float *blob_dev, const void *blob_bf16_dev, void *ws_dev, long long ws_bytes,
+                                int B, int T, int precision, void *stream);
 
 #ifdef __cplusplus
 }

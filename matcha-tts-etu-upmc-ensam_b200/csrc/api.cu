@@ -44,6 +44,25 @@ int encode_tmap_2d_f32(CUtensorMap *map, const void *base, uint64_t rows, uint64
     return MB200_OK;
 }
 
+// bf16 tensor map (2-D or 3-D), 128B swizzle, zero fill outside the tensor.
+int encode_tmap_bf16(CUtensorMap *map, const void *base, int ndim, const uint64_t *dims,
+                     const uint64_t *strides_bytes, const uint32_t *box) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return MB200_ERR_NO_DEVICE;
+    cuuint64_t d[3], st[2];
+    cuuint32_t bx[3], es[3] = {1, 1, 1};
+    for (int i = 0; i < ndim; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
+    for (int i = 0; i + 1 < ndim; ++i) st[i] = strides_bytes[i];
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)ndim, const_cast<void *>(base), d, st, bx, es,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        g_last_cuda_error = (int)r;
+        return MB200_ERR_CUDA;
+    }
+    return MB200_OK;
+}
+
 }  // namespace mb200
 
 using namespace mb200;

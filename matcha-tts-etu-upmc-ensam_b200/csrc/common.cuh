@@ -33,6 +33,9 @@ constexpr int kSmemBlockReserve = 1024;    // per-CTA system reservation
 int encode_tmap_2d_f32(CUtensorMap *map, const void *base, uint64_t rows, uint64_t cols,
                        uint32_t box_rows, uint32_t box_cols);
 
+int encode_tmap_bf16(CUtensorMap *map, const void *base, int ndim, const uint64_t *dims,
+                     const uint64_t *strides_bytes, const uint32_t *box);
+
 // ---------------------------------------------------------------- device side
 #ifdef __CUDACC__
 

@@ -9,7 +9,9 @@
 // "b c t <-> b t c" rearranges of decoder.py:298-352 disappear, the channel concats of
 // decoder.py:288,341 and the nearest-neighbour resample of :338-339 become addressing inside the
 // implicit-GEMM loader.
-#include "decoder_kernels.cuh"
+#include <vector>
+
+#include "gemm_bf16.cuh"
 
 namespace mb200 {
 
@@ -65,9 +67,10 @@ static long long build_weights(const float *blob, DecW *w) {
 // ---------------------------------------------------------------- workspace
 struct DecWs {
     float *tb, *x0, *h, *a, *g, *x1, *ln, *qkv, *att, *x2, *f1, *x3, *s0, *s1, *d, *stats;
+    __nv_bfloat16 *x0b, *a1b, *lnb, *attb, *f1b, *inb, *s0b, *s1b, *upb;   // bf16 mode only
 };
 
-static long long carve_workspace(float *base, int B, int T, int n_rows, DecWs *ws) {
+static long long carve_workspace(float *base, int B, int T, int n_rows, int precision, DecWs *ws) {
     const long long M = (long long)B * T, Mu = (long long)B * (T + 1);
     long long off = 0;
     auto take = [&](long long n) { float *p = base ? base + off : nullptr; off += (n + 3) & ~3LL; return p; };
@@ -78,17 +81,27 @@ static long long carve_workspace(float *base, int B, int T, int n_rows, DecWs *w
     w.qkv = take(M * 3 * kC); w.att = take(M * kC); w.x2 = take(M * kC); w.f1 = take(M * 4 * kC); w.x3 = take(M * kC);
     w.s0 = take(M * kC); w.s1 = take(M * kC); w.d = take(Mu * kC);
     w.stats = take((long long)B * kGroups * 2);
+    w.x0b = w.a1b = w.lnb = w.attb = w.f1b = w.inb = w.s0b = w.s1b = w.upb = nullptr;
+    if (precision == MB200_PREC_BF16) {
+        auto take_h = [&](long long n) { return reinterpret_cast<__nv_bfloat16 *>(take((n + 1) / 2)); };
+        w.x0b = take_h(M * kInChPad); w.a1b = take_h(M * kC); w.lnb = take_h(M * kC); w.attb = take_h(M * kC);
+        w.f1b = take_h(M * 4 * kC); w.inb = take_h(M * kC); w.s0b = take_h(M * kC); w.s1b = take_h(M * kC);
+        w.upb = take_h(M * kC);
+    }
     if (ws) *ws = w;
     return off * (long long)sizeof(float);
 }
 
 // ---------------------------------------------------------------- launch helpers
+struct TmapEntry { const void *base; uint64_t d0, d1; CUtensorMap map; };
 struct Ctx {
     cudaStream_t st;
     const float *mask;   // [B][T] float 0/1, pitch T at every U-Net level (prefix truncation)
     int B, T;
     DecWs ws;
     int launches;
+    int err;
+    std::vector<TmapEntry> tmaps;   // tensor maps of this call's bf16 tensors
 };
 
 static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int c1, bool masked, int ntaps,
@@ -101,7 +114,7 @@ static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int 
     for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
     g.stride = stride; g.B = c.B; g.Tin = Tin; g.Tout = Tout;
     g.w = w; g.bias = bias; g.N = N; g.K = ntaps * (c0 + c1); g.act = act; g.res = res; g.out = out;
-    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off;
+    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off; g.out_bf16 = nullptr; g.omask = nullptr;
     const int M = c.B * Tout;
     dim3 grid((M + kBM - 1) / kBM, N / kBN);
     gemm_f32_kernel<<<grid, 256, 0, c.st>>>(g);
@@ -121,12 +134,12 @@ static void gn_mish(Ctx &c, const float *h, const float *gamma, const float *bet
     const long long n4 = (long long)c.B * T * (kC / 4);
     int blocks = (int)((n4 + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, c.B, T);
+    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, c.B, T);
     c.launches++;
 }
 static void layernorm(Ctx &c, const float *x, const float *g, const float *b, float *out, int T) {
     const size_t rows = (size_t)c.B * T;
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(x, g, b, out, rows);
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(x, g, b, out, nullptr, rows);
     c.launches++;
 }
 
@@ -147,7 +160,7 @@ static void run_stage(Ctx &c, const StageW &s, const float *a0, int c0, int Ta0,
     layernorm(c, w.x1, s.ln1g, s.ln1b, w.ln, T);
     linear(c, w.ln, kC, T, s.wqkv, nullptr, 3 * kC, 0, nullptr, w.qkv);
     dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
-    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, w.att, T);
+    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, w.att, nullptr, T);
     c.launches++;
     linear(c, w.att, kC, T, s.wo, s.bo, kC, 0, w.x1, w.x2);
     layernorm(c, w.x2, s.ln3g, s.ln3b, w.ln, T);
@@ -185,6 +198,143 @@ static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu,
     c.launches++;
 }
 
+
+// ================================================================== bf16 mode (tcgen05 GEMMs)
+typedef __nv_bfloat16 bf16;
+struct StageWb { const bf16 *wc1, *wc2, *wr, *wqkv, *wo, *w1, *w2, *wtail; int cin_pad; };
+struct DecWb { StageWb st[6]; const bf16 *wf; };
+static const int kStageCinPad[6] = {kInChPad, kC, kC, kC, 2 * kC, 2 * kC};
+
+// Order must match pack_bf16 below.
+static long long build_weights_bf16(const bf16 *blob, DecWb *w) {
+    long long off = 0;
+    auto take = [&](long long n) { const bf16 *p = blob ? blob + off : nullptr; off += (n + 7) & ~7LL; return p; };
+    DecWb d;
+    for (int i = 0; i < 6; ++i) {
+        StageWb &s = d.st[i];
+        s.cin_pad = kStageCinPad[i];
+        s.wc1 = take(256LL * 3 * s.cin_pad); s.wc2 = take(256LL * 3 * 256); s.wr = take(256LL * s.cin_pad);
+        s.wqkv = take(768LL * 256); s.wo = take(256LL * 256); s.w1 = take(1024LL * 256); s.w2 = take(256LL * 1024);
+        s.wtail = (i == 1 || i == 5) ? take(256LL * 3 * 256) : nullptr;
+    }
+    d.wf = take(256LL * 3 * 256);
+    if (w) *w = d;
+    return off;
+}
+
+static bool tmap_for(Ctx &c, const bf16 *base, int ndim, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t b0,
+                     uint32_t b1, CUtensorMap *out) {
+    for (auto &e : c.tmaps)
+        if (e.base == base && e.d0 == d0 && e.d1 == d1) { *out = e.map; return true; }
+    TmapEntry e;
+    e.base = base; e.d0 = d0; e.d1 = d1;
+    const uint64_t dims[3] = {d0, d1, d2};
+    const uint64_t strides[2] = {d0 * 2, d0 * d1 * 2};
+    const uint32_t box[3] = {b0, b1, 1};
+    const int rc = encode_tmap_bf16(&e.map, base, ndim, dims, strides, box);
+    if (rc != MB200_OK) { c.err = rc; return false; }
+    c.tmaps.push_back(e);
+    *out = e.map;
+    return true;
+}
+
+// out = act(A W^T + bias) + res on the tensor cores.  a0/a1: bf16 [B][T][c0|c1] (already x*mask where the
+// reference multiplies), w: bf16 [N][ntaps*(c0+c1)].
+static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
+                   const bf16 *w, int N, const float *bias, int act, const float *res, float *out_f32,
+                   bf16 *out_b16, bool omask) {
+    if (c.err) return;
+    CUtensorMap ma0, ma1, mb;
+    if (!tmap_for(c, a0, 3, (uint64_t)c0, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma0)) return;
+    ma1 = ma0;
+    if (a1 && !tmap_for(c, a1, 3, (uint64_t)c1, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma1)) return;
+    if (!tmap_for(c, w, 2, (uint64_t)ntaps * (c0 + c1), (uint64_t)N, 1, kGK, kGN, &mb)) return;
+    GemmBf16Args g;
+    g.B = c.B; g.Tout = T; g.tiles_per_sample = (T + kGM - 1) / kGM;
+    g.ntaps = ntaps;
+    for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
+    g.c0_chunks = c0 / kGK; g.c1_chunks = c1 / kGK;
+    g.bias = bias; g.act = act; g.res = res; g.out_f32 = out_f32; g.out_bf16 = out_b16;
+    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.N = N;
+    dim3 grid(g.tiles_per_sample * c.B, N / kGN);
+    gemm_bf16_kernel<<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
+    c.launches++;
+}
+
+static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf16 *in0, int c0, const bf16 *in1,
+                           int c1, int T, const float *tb, int tb_per_sample, float *out_f32, bf16 *out_b16) {
+    static const int taps3[3] = {-1, 0, 1};
+    static const int tap0[1] = {0};
+    DecWs &w = c.ws;
+    const long long n4 = (long long)c.B * T * (kC / 4);
+    int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
+    const size_t rows = (size_t)c.B * T;
+    gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false);
+    gn_stats(c, w.h, T);
+    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.B, T);
+    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false);
+    gn_stats(c, w.h, T);
+    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, c.B, T);
+    gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, rows);
+    gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, w.qkv, nullptr, false);
+    dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
+    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, nullptr, w.attb, T);
+    gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, rows);
+    gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
+    gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
+    c.launches += 5;
+}
+
+static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const float *x, const float *mu,
+                              const float *tb_rows, int n_rows, int tb_per_sample, const float *x_in, float dt,
+                              float *out) {
+    static const int taps3[3] = {-1, 0, 1};
+    static const int taps_even[2] = {0, -1};
+    static const int taps_odd[2] = {1, 0};
+    DecWs &w = c.ws;
+    const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
+    auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
+    dim3 pgrid((T + 31) / 32, kInChPad / 32, c.B);
+    pack_input_bf16_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, c.mask, w.x0b, c.B, T);
+    c.launches++;
+    // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
+    run_stage_bf16(c, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, w.s0, w.s0b);
+    {
+        GemmArgs g;
+        g.a0 = w.s0; g.a1 = nullptr; g.c0 = kC; g.c1 = 0; g.Ta0 = T; g.mask = c.mask; g.mask_T = c.T;
+        g.ntaps = 3; g.tap_off[0] = -1; g.tap_off[1] = 0; g.tap_off[2] = 1; g.tap_off[3] = 0; g.stride = 2;
+        g.B = c.B; g.Tin = T; g.Tout = T2; g.w = W.st[0].wtail; g.bias = W.st[0].btail; g.N = kC; g.K = 3 * kC;
+        g.act = 0; g.res = nullptr; g.out = nullptr; g.out_T = T2; g.out_stride = 1; g.out_off = 0;
+        g.out_bf16 = w.inb; g.omask = c.mask;
+        gemm_f32_kernel<<<dim3((c.B * T2 + kBM - 1) / kBM, kC / kBN), 256, 0, c.st>>>(g);
+        c.launches++;
+    }
+    run_stage_bf16(c, W.st[1], Wb.st[1], w.inb, kC, nullptr, 0, T2, tb(1), tb_per_sample, nullptr, w.s1b);
+    gemm_b(c, w.s1b, kC, nullptr, 0, 3, taps3, T2, Wb.st[1].wtail, kC, W.st[1].btail, 0, nullptr, nullptr, w.inb, true);
+    run_stage_bf16(c, W.st[2], Wb.st[2], w.inb, kC, nullptr, 0, T2, tb(2), tb_per_sample, nullptr, w.upb);
+    run_stage_bf16(c, W.st[3], Wb.st[3], w.upb, kC, nullptr, 0, T2, tb(3), tb_per_sample, nullptr, w.inb);
+    run_stage_bf16(c, W.st[4], Wb.st[4], w.inb, kC, w.s1b, kC, T2, tb(4), tb_per_sample, w.x3, nullptr);
+    // ConvTranspose1d(4,2,1) (decoder.py:112) as two phase GEMMs on the fp32 kernel, then the nearest
+    // resample (odd T) + x*mask into the bf16 operand of the last Resnet1D
+    gemm(c, w.x3, kC, T2, nullptr, 0, true, 2, taps_even, 1, T2, T2, W.st[4].wtail, W.st[4].btail, kC, 0, nullptr, w.d, Tu, 2, 0);
+    gemm(c, w.x3, kC, T2, nullptr, 0, true, 2, taps_odd, 1, T2, T2, W.st[4].wtail2, W.st[4].btail, kC, 0, nullptr, w.d, Tu, 2, 1);
+    {
+        const long long n4 = (long long)c.B * T * (kC / 4);
+        int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
+        resample_mask_bf16_kernel<<<eb, 256, 0, c.st>>>(w.d, Tu, c.mask, w.upb, c.B, T);
+        c.launches++;
+    }
+    run_stage_bf16(c, W.st[5], Wb.st[5], w.upb, kC, w.s0b, kC, T, tb(5), tb_per_sample, nullptr, w.inb);
+    gemm_b(c, w.inb, kC, nullptr, 0, 3, taps3, T, Wb.st[5].wtail, kC, W.st[5].btail, 0, nullptr, nullptr, w.a1b, true);
+    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, Wb.wf, kC, W.bf, 0, nullptr, w.h, nullptr, false);
+    gn_stats(c, w.h, T);
+    dim3 fgrid((T + 31) / 32, c.B);
+    final_proj_kernel<<<fgrid, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, W.wp, W.bp, x_in, dt, out, T);
+    c.launches++;
+}
+
 static TimeWeights time_weights(const DecW &W) {
     TimeWeights t;
     t.freq = W.freq; t.w1 = W.tw1; t.b1 = W.tb1; t.w2 = W.tw2; t.b2 = W.tb2;
@@ -208,56 +358,90 @@ int check_common(const void *a, const void *b, const void *c, const void *d, con
     if (T < 2) return MB200_ERR_UNSUPPORTED;
     return MB200_OK;
 }
-int prepare(Ctx &c, DecW &W, const float *blob, void *ws, long long ws_bytes, const float *mask, int B, int T,
-            int n_rows, void *stream) {
+int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16, void *ws, long long ws_bytes,
+            const float *mask, int B, int T, int n_rows, int precision, void *stream) {
+    if (precision != MB200_PREC_F32 && precision != MB200_PREC_BF16) return MB200_ERR_INVALID_ARG;
+    if (precision == MB200_PREC_BF16 && !blob_bf16) return MB200_ERR_INVALID_ARG;
     build_weights(blob, &W);
-    if (ws_bytes < carve_workspace(nullptr, B, T, n_rows, nullptr)) return MB200_ERR_INVALID_ARG;
-    if ((uintptr_t)ws % 16 != 0 || (uintptr_t)blob % 16 != 0) return MB200_ERR_INVALID_ARG;
-    carve_workspace((float *)ws, B, T, n_rows, &c.ws);
-    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0;
+    build_weights_bf16(reinterpret_cast<const bf16 *>(blob_bf16), &Wb);
+    if (ws_bytes < carve_workspace(nullptr, B, T, n_rows, precision, nullptr)) return MB200_ERR_INVALID_ARG;
+    if ((uintptr_t)ws % 16 != 0 || (uintptr_t)blob % 16 != 0 || (uintptr_t)blob_bf16 % 16 != 0) return MB200_ERR_INVALID_ARG;
+    carve_workspace((float *)ws, B, T, n_rows, precision, &c.ws);
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0;
     static bool attr_set = false;
     if (!attr_set) {
         MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
         attr_set = true;
     }
     return MB200_OK;
 }
+void eval_any(Ctx &c, const DecW &W, const DecWb &Wb, int precision, const float *x, const float *mu,
+              const float *tb_rows, int n_rows, int per_sample, const float *x_in, float dt, float *out) {
+    if (precision == MB200_PREC_BF16) decoder_eval_bf16(c, W, Wb, x, mu, tb_rows, n_rows, per_sample, x_in, dt, out);
+    else decoder_eval(c, W, x, mu, tb_rows, n_rows, per_sample, x_in, dt, out);
+}
 }  // namespace
 
 extern "C" long long matcha_b200_decoder_blob_floats(void) { return build_weights(nullptr, nullptr); }
+extern "C" long long matcha_b200_decoder_blob_bf16_bytes(void) { return build_weights_bf16(nullptr, nullptr) * 2; }
 
-extern "C" long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows) {
+extern "C" long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows, int precision) {
     if (B <= 0 || T <= 0 || n_rows <= 0) return MB200_ERR_INVALID_ARG;
-    return carve_workspace(nullptr, B, T, n_rows, nullptr);
+    return carve_workspace(nullptr, B, T, n_rows, precision, nullptr);
+}
+
+extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_bf16_dev, void *stream) {
+    if (!blob_dev || !blob_bf16_dev) return MB200_ERR_INVALID_ARG;
+    DecW W; DecWb Wb;
+    build_weights(blob_dev, &W);
+    build_weights_bf16(reinterpret_cast<bf16 *>(blob_bf16_dev), &Wb);
+    cudaStream_t st = (cudaStream_t)stream;
+    auto pack = [&](const float *src, const bf16 *dst, int rows, int cin, int cin_pad) {
+        pack_weight_bf16_kernel<<<256, 256, 0, st>>>(src, const_cast<bf16 *>(dst), rows, cin, cin_pad);
+    };
+    for (int i = 0; i < 6; ++i) {
+        const StageW &s = W.st[i]; const StageWb &b = Wb.st[i];
+        pack(s.wc1, b.wc1, 256 * 3, s.cin, b.cin_pad);
+        pack(s.wc2, b.wc2, 256 * 3, 256, 256);
+        pack(s.wr, b.wr, 256, s.cin, b.cin_pad);
+        pack(s.wqkv, b.wqkv, 768, 256, 256);
+        pack(s.wo, b.wo, 256, 256, 256);
+        pack(s.w1, b.w1, 1024, 256, 256);
+        pack(s.w2, b.w2, 256, 1024, 1024);
+        if (b.wtail) pack(s.wtail, b.wtail, 256 * 3, 256, 256);
+    }
+    pack(W.wf, Wb.wf, 256 * 3, 256, 256);
+    MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
 }
 
 extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_dev, const float *mask_dev,
                                             const float *t_dev, int n_t, float *out_dev, const float *blob_dev,
-                                            void *ws_dev, long long ws_bytes, int B, int T, int precision,
-                                            void *stream) {
+                                            const void *blob_bf16_dev, void *ws_dev, long long ws_bytes, int B, int T,
+                                            int precision, void *stream) {
     int rc = check_common(x_dev, mu_dev, mask_dev, t_dev, out_dev, blob_dev, B, T);
     if (rc != MB200_OK) return rc;
     if (!ws_dev || (n_t != 1 && n_t != B)) return MB200_ERR_INVALID_ARG;
-    if (precision != MB200_PREC_F32) return MB200_ERR_UNSUPPORTED;
-    Ctx c; DecW W;
-    rc = prepare(c, W, blob_dev, ws_dev, ws_bytes, mask_dev, B, T, n_t, stream);
+    Ctx c; DecW W; DecWb Wb;
+    rc = prepare(c, W, Wb, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, mask_dev, B, T, n_t, precision, stream);
     if (rc != MB200_OK) return rc;
     time_embed_kernel<<<n_t, 256, 0, c.st>>>(time_weights(W), t_dev, n_t, c.ws.tb);
-    decoder_eval(c, W, x_dev, mu_dev, c.ws.tb, n_t, n_t == B && B > 1 ? 1 : 0, nullptr, 0.f, out_dev);
+    eval_any(c, W, Wb, precision, x_dev, mu_dev, c.ws.tb, n_t, n_t == B && B > 1 ? 1 : 0, nullptr, 0.f, out_dev);
+    if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return c.launches + 1;
 }
 
 extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,
                                             float *out_dev, const float *t_host, const float *dt_host, int n_steps,
-                                            const float *blob_dev, void *ws_dev, long long ws_bytes, int B, int T,
-                                            int precision, void *stream) {
+                                            const float *blob_dev, const void *blob_bf16_dev, void *ws_dev,
+                                            long long ws_bytes, int B, int T, int precision, void *stream) {
     int rc = check_common(x0_dev, mu_dev, mask_dev, out_dev, blob_dev, t_host, B, T);
     if (rc != MB200_OK) return rc;
     if (!ws_dev || !dt_host || n_steps < 1 || n_steps > 64) return MB200_ERR_INVALID_ARG;
-    if (precision != MB200_PREC_F32) return MB200_ERR_UNSUPPORTED;
-    Ctx c; DecW W;
-    rc = prepare(c, W, blob_dev, ws_dev, ws_bytes, mask_dev, B, T, n_steps, stream);
+    Ctx c; DecW W; DecWb Wb;
+    rc = prepare(c, W, Wb, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, mask_dev, B, T, n_steps, precision, stream);
     if (rc != MB200_OK) return rc;
     // all time embeddings and per-Resnet time biases of the grid in one launch
     TimeVals tv;
@@ -266,8 +450,24 @@ extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_
     stage_times_kernel<<<1, 64, 0, c.st>>>(tv, n_steps, t_stage);
     time_embed_kernel<<<n_steps, 256, 0, c.st>>>(time_weights(W), t_stage, n_steps, c.ws.tb);
     for (int k = 0; k < n_steps; ++k)
-        decoder_eval(c, W, k == 0 ? x0_dev : out_dev, mu_dev, c.ws.tb + (size_t)k * kC, n_steps, 0,
-                     k == 0 ? x0_dev : out_dev, dt_host[k], out_dev);
+        eval_any(c, W, Wb, precision, k == 0 ? x0_dev : out_dev, mu_dev, c.ws.tb + (size_t)k * kC, n_steps, 0,
+                 k == 0 ? x0_dev : out_dev, dt_host[k], out_dev);
+    if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return c.launches + 2;
+}
+
+// test aid, not part of the public header: one tcgen05 implicit GEMM on caller-provided bf16 operands
+extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a1, int c1, int ntaps, const int *taps,
+                                            int B, int T, const void *w, int N, const float *bias, int act,
+                                            const float *res, float *out_f32, void *out_bf16, const float *mask,
+                                            void *stream) {
+    Ctx c;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0;
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+    gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
+           (bf16 *)out_bf16, mask != nullptr);
+    if (c.err) return c.err;
+    MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
 }

@@ -14,6 +14,8 @@
 //   final_proj_kernel   <- final_norm + Mish + final_proj + masks + the Euler update
 //                                                           decoder.py:367-371, flow_matching.py:95
 #pragma once
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace mb200 {
@@ -119,8 +121,10 @@ struct GemmArgs {
     int N, K;
     int act;                      // 0 none, 1 erf-GELU
     const float *res;             // same indexing as out, or nullptr
-    float *out;
+    float *out;                   // fp32 output or nullptr
     int out_T, out_stride, out_off;
+    __nv_bfloat16 *out_bf16;      // optional bf16 copy, multiplied by omask[b][out row] (pitch mask_T)
+    const float *omask;
 };
 
 constexpr int kBM = 128, kBN = 64, kBK = 16;
@@ -219,7 +223,13 @@ gemm_f32_kernel(const GemmArgs g) {
             const float4 r = *reinterpret_cast<const float4 *>(g.res + o);
             v.x += r.x; v.y += r.y; v.z += r.z; v.w += r.w;
         }
-        *reinterpret_cast<float4 *>(g.out + o) = v;
+        if (g.out) *reinterpret_cast<float4 *>(g.out + o) = v;
+        if (g.out_bf16) {
+            const float mk = g.omask ? g.omask[(size_t)b * g.mask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * mk, v.y * mk), hi = __floats2bfloat162_rn(v.z * mk, v.w * mk);
+            uint2 pk = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+            *reinterpret_cast<uint2 *>(g.out_bf16 + o) = pk;
+        }
     }
 }
 
@@ -261,7 +271,8 @@ gn_stats_kernel(const float *__restrict__ h, int T, float *__restrict__ stats) {
 __global__ void __launch_bounds__(256)
 gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, const float *__restrict__ gamma,
                const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
-               const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out, int B, int T) {
+               const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out,
+               __nv_bfloat16 *__restrict__ out_bf16, int B, int T) {
     const size_t n4 = (size_t)B * T * (kC / 4);
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
         const int c = (int)(i % (kC / 4)) * 4;
@@ -280,7 +291,11 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
             const float4 tv = *reinterpret_cast<const float4 *>(tb + (size_t)(tb_per_sample ? b : 0) * kC + c);
             o.x += tv.x; o.y += tv.y; o.z += tv.z; o.w += tv.w;
         }
-        *reinterpret_cast<float4 *>(out + i * 4) = o;
+        if (out) *reinterpret_cast<float4 *>(out + i * 4) = o;
+        if (out_bf16) {     // the bf16 copy is the next conv's operand: x*mask applied here (decoder.py:65)
+            __nv_bfloat162 lo = __floats2bfloat162_rn(o.x * mk, o.y * mk), hi = __floats2bfloat162_rn(o.z * mk, o.w * mk);
+            *reinterpret_cast<uint2 *>(out_bf16 + i * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+        }
     }
 }
 
@@ -288,7 +303,7 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
 // one warp per row
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta,
-                 float *__restrict__ out, size_t rows) {
+                 float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, size_t rows) {
     const int lane = threadIdx.x & 31;
     const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -308,8 +323,16 @@ layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, c
     const float4 b0 = *reinterpret_cast<const float4 *>(beta + lane * 4), b1 = *reinterpret_cast<const float4 *>(beta + 128 + lane * 4);
     float4 o0 = make_float4(d[0] * rstd * g0.x + b0.x, d[1] * rstd * g0.y + b0.y, d[2] * rstd * g0.z + b0.z, d[3] * rstd * g0.w + b0.w);
     float4 o1 = make_float4(d[4] * rstd * g1.x + b1.x, d[5] * rstd * g1.y + b1.y, d[6] * rstd * g1.z + b1.z, d[7] * rstd * g1.w + b1.w);
-    *reinterpret_cast<float4 *>(out + row * kC + lane * 4) = o0;
-    *reinterpret_cast<float4 *>(out + row * kC + 128 + lane * 4) = o1;
+    if (out) {
+        *reinterpret_cast<float4 *>(out + row * kC + lane * 4) = o0;
+        *reinterpret_cast<float4 *>(out + row * kC + 128 + lane * 4) = o1;
+    }
+    if (out_bf16) {
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(o0.x, o0.y), p1 = __floats2bfloat162_rn(o0.z, o0.w);
+        __nv_bfloat162 p2 = __floats2bfloat162_rn(o1.x, o1.y), p3 = __floats2bfloat162_rn(o1.z, o1.w);
+        *reinterpret_cast<uint2 *>(out_bf16 + row * kC + lane * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&p0), *reinterpret_cast<uint32_t *>(&p1));
+        *reinterpret_cast<uint2 *>(out_bf16 + row * kC + 128 + lane * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&p2), *reinterpret_cast<uint32_t *>(&p3));
+    }
 }
 
 // ------------------------------------------------------------------ attention (fp32 SIMT)
@@ -321,7 +344,7 @@ constexpr int kAttSmemBytes = (2 * kAttBK * kAttPitch + kAttBQ * kAttPitch) * 4;
 
 __global__ void __launch_bounds__(128)
 attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ mask, int mask_T,
-                     float *__restrict__ out, int T) {
+                     float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int T) {
     extern __shared__ __align__(16) float att_smem[];
     float (*Ks)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem);
     float (*Vs)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem + kAttBK * kAttPitch);
@@ -401,10 +424,15 @@ attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ ma
     }
     if (tq < T) {
         const float inv = 1.0f / l_run;
-        float *po = out + ((size_t)b * T + tq) * kC + h * kDHead + half * 32;
+        const size_t oo = ((size_t)b * T + tq) * kC + h * kDHead + half * 32;
 #pragma unroll
-        for (int d = 0; d < 32; d += 4)
-            *reinterpret_cast<float4 *>(po + d) = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
+        for (int d = 0; d < 32; d += 4) {
+            if (out) *reinterpret_cast<float4 *>(out + oo + d) = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
+            if (out_bf16) {
+                __nv_bfloat162 lo = __floats2bfloat162_rn(o[d] * inv, o[d + 1] * inv), hi = __floats2bfloat162_rn(o[d + 2] * inv, o[d + 3] * inv);
+                *reinterpret_cast<uint2 *>(out_bf16 + oo + d) = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+            }
+        }
     }
 }
 
@@ -442,6 +470,61 @@ final_proj_kernel(const float *__restrict__ hf, const float *__restrict__ stats,
             const size_t o = ((size_t)b * kMel + n) * T + t;
             out[o] = x_in ? __fadd_rn(x_in[o], __fmul_rn(dt, v)) : v;   // x + dt * v, two roundings as in torch
         }
+    }
+}
+
+// ------------------------------------------------------------------ bf16-mode helpers
+constexpr int kInChPad = 192;      // 160 input channels padded to three 64-wide K chunks
+
+// X0b[b][t][0:80] = x*mask, [80:160] = mu*mask, [160:192] = 0   (decoder.py:288 + the x*mask of :65,85)
+__global__ void __launch_bounds__(256)
+pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
+                       __nv_bfloat16 *__restrict__ out, int B, int T) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 192 channels
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i, t = t0 + tx;
+        float v = 0.f;
+        if (t < T && c < kInCh)
+            v = ((c < kMel) ? x[((size_t)b * kMel + c) * T + t] : mu[((size_t)b * kMel + (c - kMel)) * T + t]) * mask[(size_t)b * T + t];
+        tile[i][tx] = v;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int t = t0 + i, c = c0 + tx;
+        if (t < T) out[((size_t)b * T + t) * kInChPad + c] = __float2bfloat16_rn(tile[tx][i]);
+    }
+}
+
+// out[b][t][:] = bf16(in[b][nearest(t)][:] * mask[b][t]): F.interpolate(mode="nearest") of decoder.py:338-339
+// (identity when Tin == T) followed by the x*mask of the next Resnet1D.
+__global__ void __launch_bounds__(256)
+resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__restrict__ mask,
+                          __nv_bfloat16 *__restrict__ out, int B, int T) {
+    const size_t n4 = (size_t)B * T * (kC / 4);
+    const float scale = (float)Tin / (float)T;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        const int c = (int)(i % (kC / 4)) * 4;
+        const size_t row = i / (kC / 4);
+        const int b = (int)(row / T), t = (int)(row % T);
+        int ts = t;
+        if (Tin != T) { ts = (int)floorf((float)t * scale); if (ts > Tin - 1) ts = Tin - 1; }
+        const float mk = mask[(size_t)b * T + t];
+        const float4 v = *reinterpret_cast<const float4 *>(in + ((size_t)b * Tin + ts) * kC + c);
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * mk, v.y * mk), hi = __floats2bfloat162_rn(v.z * mk, v.w * mk);
+        *reinterpret_cast<uint2 *>(out + i * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+    }
+}
+
+// dst[n][tap][0:cin_pad] = bf16(src[n][tap][0:cin]) zero-padded: GEMM weights for the tcgen05 path
+__global__ void __launch_bounds__(256)
+pack_weight_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int rows, int cin, int cin_pad) {
+    const size_t n = (size_t)rows * cin_pad;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+        const size_t r = i / cin_pad;
+        const int c = (int)(i % cin_pad);
+        dst[i] = __float2bfloat16_rn(c < cin ? src[r * cin + c] : 0.f);
     }
 }
 

@@ -1,0 +1,188 @@
+// gemm_bf16.cuh -- tcgen05/TMEM implicit-GEMM for the decoder's convolutions and projections.
+//
+// D[128 x 256] (fp32, TMEM) = sum over (tap, 64-channel chunk) of A[128 x 64] * W[256 x 64]^T, bf16
+// operands staged in shared memory by TMA in the 128B-swizzled K-major layout both TMA and the
+// UMMA shared-memory descriptor understand.  One CTA per output tile:
+//   warp 0      TMA producer: A boxes from a 3-D map over the bf16 activation [B][T][C] (the conv
+//               taps are row offsets; rows outside [0,T) come back as zeros, which is the conv's
+//               zero padding, decoder.py:59), W boxes from a 2-D map over [N][K].
+//   warp 1      allocates 256 TMEM columns and issues tcgen05.mma (one elected lane), releasing
+//               stages with tcgen05.commit.
+//   warps 2..5  epilogue: tcgen05.ld (lane = output row), transpose through shared memory so that
+//               global accesses are row-contiguous, then bias / erf-GELU / residual / row mask and
+//               fp32 and/or bf16 stores.
+// Reference arithmetic: nn.Conv1d / nn.Linear of decoder.py:59,78,192,239,248 and the diffusers
+// Attention / FeedForward projections (transformer.py:251-259,156,180).
+#pragma once
+#include <cuda_bf16.h>
+
+#include "decoder_kernels.cuh"
+
+namespace mb200 {
+
+constexpr int kGM = 128, kGN = 256, kGK = 64;          // CTA tile; UMMA 128 x 256 x 16
+constexpr int kGStages = 4;
+constexpr int kGStageA = kGM * kGK * 2, kGStageB = kGN * kGK * 2;
+constexpr int kGStageBytes = kGStageA + kGStageB;      // 48 KB
+constexpr int kGEpiBytes = 4 * 32 * 33 * 4;            // per-warp transpose buffers
+constexpr int kGSmemBytes = kGStages * kGStageBytes + kGEpiBytes + 256 + 1024;
+constexpr int kGThreads = 192;
+
+struct GemmBf16Args {
+    int B, Tout, tiles_per_sample;
+    int ntaps, tap_off[4];
+    int c0_chunks, c1_chunks;          // 64-channel chunks of source 0 / source 1 (concat)
+    const float *bias;                 // [N] or nullptr
+    int act;                           // 0 none, 1 erf-GELU
+    const float *res;                  // fp32 [B][Tout][N] or nullptr
+    float *out_f32;                    // fp32 [B][Tout][N] or nullptr
+    __nv_bfloat16 *out_bf16;           // bf16 [B][Tout][N] or nullptr
+    const float *omask; int omask_T;   // multiplies the bf16 output rows (x*mask for the next conv)
+    int N;
+};
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+// K-major, 128B swizzle, 8-row atoms 1024 B apart (SBO), version 1 (sm_100)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// kind::f16, A/B bf16 K-major, fp32 accumulate, M=128, N=256
+constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kGN >> 3) << 17) | ((uint32_t)(kGM >> 4) << 24);
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(kGThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                 const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
+    extern __shared__ uint8_t gsm_raw[];
+    const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
+    uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
+    const uint32_t epi_off = kGStages * kGStageBytes;
+    const uint32_t bar_full = base + epi_off + kGEpiBytes;          // [kGStages]
+    const uint32_t bar_empty = bar_full + 8u * kGStages;            // [kGStages]
+    const uint32_t bar_acc = bar_empty + 8u * kGStages;             // accumulator ready
+    const uint32_t tmem_slot = bar_acc + 8u;                        // u32 written by tcgen05.alloc
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + epi_off + kGEpiBytes + 16 * kGStages + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x % g.tiles_per_sample) * kGM;
+    const int n0 = blockIdx.y * kGN;
+    const int chunks = g.c0_chunks + g.c1_chunks;
+    const int n_kb = g.ntaps * chunks;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kGStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
+        mbar_init(bar_acc, 1u);
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(kGN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = *tmem_slot_p;
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0) {
+            tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmB);
+            if (g.c1_chunks) tma_prefetch_desc(&tmA1);
+            for (int kb = 0; kb < n_kb; ++kb) {
+                const int s = kb % kGStages;
+                mbar_wait_parked(bar_empty + 8u * s, ((kb / kGStages) & 1) ^ 1, 1000);
+                const int tap = kb / chunks, ch = kb - tap * chunks;
+                const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
+                mbar_arrive_expect_tx(bar_full + 8u * s, kGStageBytes);
+                if (ch < g.c0_chunks) tma_load_3d(sa, &tmA0, bar_full + 8u * s, ch * kGK, t0 + g.tap_off[tap], b);
+                else tma_load_3d(sa, &tmA1, bar_full + 8u * s, (ch - g.c0_chunks) * kGK, t0 + g.tap_off[tap], b);
+                tma_load_2d(sb, &tmB, bar_full + 8u * s, kb * kGK, n0);
+            }
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ============================
+        if (lane == 0) {
+            for (int kb = 0; kb < n_kb; ++kb) {
+                const int s = kb % kGStages;
+                mbar_wait_parked(bar_full + 8u * s, (kb / kGStages) & 1, 1000);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
+                const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sb);
+#pragma unroll
+                for (int k = 0; k < kGK / 16; ++k)     // 32 bytes along K per UMMA_K=16 step: +2 in 16-byte units
+                    umma_bf16(tmem_d, da + 2u * k, db + 2u * k, kIdescBf16, (kb | k) != 0 ? 1u : 0u);
+                umma_commit(bar_empty + 8u * s);        // frees the stage when these MMAs have read it
+            }
+            umma_commit(bar_acc);                       // accumulator complete
+        }
+    } else {
+        // ============================ epilogue ============================
+        const int q = warp & 3;                         // TMEM lane quarter this warp may touch
+        float *tb = reinterpret_cast<float *>(gbase + epi_off) + (warp - 2) * (32 * 33);
+        mbar_wait_parked(bar_acc, 0, 2000);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int trow0 = t0 + 32 * q;
+        for (int j = 0; j < kGN / 32; ++j) {
+            uint32_t v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) tb[lane * 33 + i] = __uint_as_float(v[i]);
+            __syncwarp();
+            const int n = n0 + 32 * j + lane;
+            const float bias = g.bias ? g.bias[n] : 0.f;
+            for (int r = 0; r < 32; ++r) {
+                const int t = trow0 + r;
+                if (t >= g.Tout) break;
+                float x = tb[r * 33 + lane] + bias;
+                if (g.act == 1) x = gelu_erf_f(x);
+                const size_t o = ((size_t)b * g.Tout + t) * g.N + n;
+                if (g.res) x += g.res[o];
+                if (g.out_f32) g.out_f32[o] = x;
+                if (g.out_bf16) {
+                    const float mk = g.omask ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
+                    g.out_bf16[o] = __float2bfloat16_rn(x * mk);
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(kGN) : "memory");
+    }
+}
+
+}  // namespace mb200

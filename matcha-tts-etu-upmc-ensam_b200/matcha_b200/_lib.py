@@ -54,13 +54,19 @@ def load_library():
     ll = ctypes.c_longlong
     lib.matcha_b200_decoder_blob_floats.restype = ll
     lib.matcha_b200_decoder_workspace_bytes.restype = ll
-    lib.matcha_b200_decoder_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.matcha_b200_decoder_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
+    lib.matcha_b200_decoder_blob_bf16_bytes.restype = ll
+    lib.matcha_b200_decoder_pack_bf16.restype = c_int
+    lib.matcha_b200_decoder_pack_bf16.argtypes = [c_void_p, c_void_p, c_void_p]
     lib.matcha_b200_decoder_forward.restype = c_int
-    lib.matcha_b200_decoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+    lib.matcha_b200_decoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                                 c_void_p, ll, c_int, c_int, c_int, c_void_p]
     lib.matcha_b200_cfm_solve_euler.restype = c_int
     lib.matcha_b200_cfm_solve_euler.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
-                                                c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
+                                                c_void_p, c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_debug_gemm_bf16.restype = c_int
+    lib.matcha_b200_debug_gemm_bf16.argtypes = [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p,
+                                                c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     _LIB = lib
     return lib
 
@@ -83,6 +89,8 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_apply_mask",
     "matcha_b200_decoder_blob_floats",
     "matcha_b200_decoder_workspace_bytes",
+    "matcha_b200_decoder_blob_bf16_bytes",
+    "matcha_b200_decoder_pack_bf16",
     "matcha_b200_decoder_forward",
     "matcha_b200_cfm_solve_euler",
 )

@@ -116,7 +116,8 @@ class Decoder(torch.nn.Module):
         self.in_channels, self.out_channels = in_channels, out_channels
         self.precision = precision
         self._weights = None          # reference-named fp32 tensors (CPU)
-        self._blob = {}               # device -> packed blob
+        self._blob = {}               # device -> packed fp32 blob
+        self._blob16 = {}             # device -> bf16 GEMM weights (bf16 mode)
         self._ws = {}                 # (device, B, T, rows) -> workspace
 
     # -- weights ----------------------------------------------------------------------------
@@ -134,6 +135,7 @@ class Decoder(torch.nn.Module):
             raise KeyError(f"state_dict mismatch: missing {missing[:4]}..., wrong shape {bad[:4]}...")
         self._weights = OrderedDict((k, sd[k].detach().to("cpu", torch.float32).clone()) for k in exp)
         self._blob.clear()
+        self._blob16.clear()
         return self
 
     def state_dict(self, *a, **k):
@@ -147,10 +149,24 @@ class Decoder(torch.nn.Module):
             self._blob[key] = pack_weights(self._weights).to(device)
         return self._blob[key]
 
+    def _blob16_on(self, device):
+        """bf16 GEMM weights for the tcgen05 path (None in fp32 mode)."""
+        if _PRECISIONS[self.precision] != PREC_BF16:
+            return None
+        key = str(device)
+        if key not in self._blob16:
+            lib = load_library()
+            buf = torch.empty(int(lib.matcha_b200_decoder_blob_bf16_bytes()), dtype=torch.uint8, device=device)
+            with torch.cuda.device(device):
+                check(lib.matcha_b200_decoder_pack_bf16(self._blob_on(device).data_ptr(), buf.data_ptr(), _stream_ptr(device)),
+                      "decoder_pack_bf16")
+            self._blob16[key] = buf
+        return self._blob16[key]
+
     def _workspace(self, device, B, T, rows):
-        key = (str(device), B, T, rows)
+        key = (str(device), B, T, rows, self.precision)
         if key not in self._ws:
-            n = int(load_library().matcha_b200_decoder_workspace_bytes(B, T, rows))
+            n = int(load_library().matcha_b200_decoder_workspace_bytes(B, T, rows, _PRECISIONS[self.precision]))
             self._ws = {key: torch.empty(n, dtype=torch.uint8, device=device)}      # keep one shape alive
         return self._ws[key]
 
@@ -168,10 +184,11 @@ class Decoder(torch.nn.Module):
         tf = t.detach().to(dev, torch.float32).reshape(-1).contiguous()
         assert tf.numel() in (1, B)
         out = torch.empty_like(xf)
-        blob, ws = self._blob_on(dev), self._workspace(dev, B, T, tf.numel())
+        blob, b16, ws = self._blob_on(dev), self._blob16_on(dev), self._workspace(dev, B, T, tf.numel())
         with torch.cuda.device(dev):
             check(lib.matcha_b200_decoder_forward(xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), tf.data_ptr(), tf.numel(),
-                                                  out.data_ptr(), blob.data_ptr(), ws.data_ptr(), ws.numel(), B, T,
+                                                  out.data_ptr(), blob.data_ptr(), b16.data_ptr() if b16 is not None else None,
+                                                  ws.data_ptr(), ws.numel(), B, T,
                                                   _PRECISIONS[self.precision], _stream_ptr(dev)), "decoder_forward")
         return out.to(x.dtype)
 
@@ -186,13 +203,13 @@ class Decoder(torch.nn.Module):
         xf, muf = x.float().contiguous(), mu.float().contiguous()
         mf = mask.float().reshape(B, T).contiguous()
         out = torch.empty_like(xf)
-        blob, ws = self._blob_on(dev), self._workspace(dev, B, T, n)
+        blob, b16, ws = self._blob_on(dev), self._blob16_on(dev), self._workspace(dev, B, T, n)
         t_arr = (ctypes.c_float * n)(*[float(v) for v in ts])
         dt_arr = (ctypes.c_float * n)(*[float(v) for v in dts])
         with torch.cuda.device(dev):
             self.last_launches = check(lib.matcha_b200_cfm_solve_euler(
                 xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), out.data_ptr(), t_arr, dt_arr, n, blob.data_ptr(),
-                ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision], _stream_ptr(dev)), "cfm_solve_euler")
+                b16.data_ptr() if b16 is not None else None, ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision], _stream_ptr(dev)), "cfm_solve_euler")
         return out.to(x.dtype)
 
 
