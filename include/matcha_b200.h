@@ -101,12 +101,13 @@ int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int alig
  * Both return the number of kernels launched (> 0) or a negative error.                           */
 #define MB200_PREC_F32   0   /* fp32 SIMT arithmetic: rel-L2 <= 1e-5 against the fp32 reference */
 #define MB200_PREC_BF16  1   /* bf16 tensor-core GEMMs, fp32 residual stream and statistics     */
+#define MB200_PREC_F16   2   /* same kernels with IEEE fp16 operands (3 more mantissa bits)     */
 
 long long matcha_b200_decoder_blob_floats(void);
 /* bf16 mode: GEMM weights re-packed as bf16 (input channels padded to 64) by matcha_b200_decoder_pack_bf16 into a
  * caller-provided buffer of matcha_b200_decoder_blob_bf16_bytes() bytes; pass NULL in fp32 mode. */
 long long matcha_b200_decoder_blob_bf16_bytes(void);
-int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_bf16_dev, void *stream);
+int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_bf16_dev, int precision, void *stream);
 long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows, int precision);
 
 /* t_dev: n_t = 1 (one time for the whole batch, as in the Euler loop) or n_t = B (compute_loss) */

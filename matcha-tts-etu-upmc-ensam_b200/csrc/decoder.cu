@@ -82,7 +82,7 @@ static long long carve_workspace(float *base, int B, int T, int n_rows, int prec
     w.s0 = take(M * kC); w.s1 = take(M * kC); w.d = take(Mu * kC);
     w.stats = take((long long)B * kGroups * 2);
     w.x0b = w.a1b = w.lnb = w.attb = w.f1b = w.inb = w.s0b = w.s1b = w.upb = nullptr;
-    if (precision == MB200_PREC_BF16) {
+    if (precision != MB200_PREC_F32) {
         auto take_h = [&](long long n) { return reinterpret_cast<__nv_bfloat16 *>(take((n + 1) / 2)); };
         w.x0b = take_h(M * kInChPad); w.a1b = take_h(M * kC); w.lnb = take_h(M * kC); w.attb = take_h(M * kC);
         w.f1b = take_h(M * 4 * kC); w.inb = take_h(M * kC); w.s0b = take_h(M * kC); w.s1b = take_h(M * kC);
@@ -101,6 +101,7 @@ struct Ctx {
     DecWs ws;
     int launches;
     int err;
+    int f16;             // 16-bit operand format of the tensor-core mode: 0 bf16, 1 fp16
     std::vector<TmapEntry> tmaps;   // tensor maps of this call's bf16 tensors
 };
 
@@ -114,7 +115,7 @@ static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int 
     for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
     g.stride = stride; g.B = c.B; g.Tin = Tin; g.Tout = Tout;
     g.w = w; g.bias = bias; g.N = N; g.K = ntaps * (c0 + c1); g.act = act; g.res = res; g.out = out;
-    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off; g.out_bf16 = nullptr; g.omask = nullptr;
+    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off; g.out_bf16 = nullptr; g.omask = nullptr; g.f16 = 0;
     const int M = c.B * Tout;
     dim3 grid((M + kBM - 1) / kBM, N / kBN);
     gemm_f32_kernel<<<grid, 256, 0, c.st>>>(g);
@@ -134,12 +135,12 @@ static void gn_mish(Ctx &c, const float *h, const float *gamma, const float *bet
     const long long n4 = (long long)c.B * T * (kC / 4);
     int blocks = (int)((n4 + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, c.B, T);
+    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, c.B, T);
     c.launches++;
 }
 static void layernorm(Ctx &c, const float *x, const float *g, const float *b, float *out, int T) {
     const size_t rows = (size_t)c.B * T;
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(x, g, b, out, nullptr, rows);
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(x, g, b, out, nullptr, 0, rows);
     c.launches++;
 }
 
@@ -160,7 +161,7 @@ static void run_stage(Ctx &c, const StageW &s, const float *a0, int c0, int Ta0,
     layernorm(c, w.x1, s.ln1g, s.ln1b, w.ln, T);
     linear(c, w.ln, kC, T, s.wqkv, nullptr, 3 * kC, 0, nullptr, w.qkv);
     dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
-    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, w.att, nullptr, T);
+    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, w.att, nullptr, 0, T);
     c.launches++;
     linear(c, w.att, kC, T, s.wo, s.bo, kC, 0, w.x1, w.x2);
     layernorm(c, w.x2, s.ln3g, s.ln3b, w.ln, T);
@@ -255,7 +256,7 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
     g.c0_chunks = c0 / kGK; g.c1_chunks = c1 / kGK;
     g.bias = bias; g.act = act; g.res = res; g.out_f32 = out_f32; g.out_bf16 = out_b16;
-    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.N = N;
+    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.N = N; g.f16 = c.f16;
     dim3 grid(g.tiles_per_sample * c.B, N / kGN);
     gemm_bf16_kernel<<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
     c.launches++;
@@ -271,17 +272,17 @@ static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf1
     const size_t rows = (size_t)c.B * T;
     gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.B, T);
+    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, c.B, T);
     gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, c.B, T);
+    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, c.B, T);
     gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, rows);
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, w.qkv, nullptr, false);
     dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
-    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, nullptr, w.attb, T);
+    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, nullptr, w.attb, c.f16, T);
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, rows);
+    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
     gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
     c.launches += 5;
@@ -297,7 +298,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
     auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
     dim3 pgrid((T + 31) / 32, kInChPad / 32, c.B);
-    pack_input_bf16_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, c.mask, w.x0b, c.B, T);
+    pack_input_bf16_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, c.mask, w.x0b, c.f16, c.B, T);
     c.launches++;
     // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
     run_stage_bf16(c, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, w.s0, w.s0b);
@@ -307,7 +308,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         g.ntaps = 3; g.tap_off[0] = -1; g.tap_off[1] = 0; g.tap_off[2] = 1; g.tap_off[3] = 0; g.stride = 2;
         g.B = c.B; g.Tin = T; g.Tout = T2; g.w = W.st[0].wtail; g.bias = W.st[0].btail; g.N = kC; g.K = 3 * kC;
         g.act = 0; g.res = nullptr; g.out = nullptr; g.out_T = T2; g.out_stride = 1; g.out_off = 0;
-        g.out_bf16 = w.inb; g.omask = c.mask;
+        g.out_bf16 = w.inb; g.omask = c.mask; g.f16 = c.f16;
         gemm_f32_kernel<<<dim3((c.B * T2 + kBM - 1) / kBM, kC / kBN), 256, 0, c.st>>>(g);
         c.launches++;
     }
@@ -323,7 +324,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     {
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        resample_mask_bf16_kernel<<<eb, 256, 0, c.st>>>(w.d, Tu, c.mask, w.upb, c.B, T);
+        resample_mask_bf16_kernel<<<eb, 256, 0, c.st>>>(w.d, Tu, c.mask, w.upb, c.f16, c.B, T);
         c.launches++;
     }
     run_stage_bf16(c, W.st[5], Wb.st[5], w.upb, kC, w.s0b, kC, T, tb(5), tb_per_sample, nullptr, w.inb);
@@ -360,14 +361,14 @@ int check_common(const void *a, const void *b, const void *c, const void *d, con
 }
 int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16, void *ws, long long ws_bytes,
             const float *mask, int B, int T, int n_rows, int precision, void *stream) {
-    if (precision != MB200_PREC_F32 && precision != MB200_PREC_BF16) return MB200_ERR_INVALID_ARG;
-    if (precision == MB200_PREC_BF16 && !blob_bf16) return MB200_ERR_INVALID_ARG;
+    if (precision != MB200_PREC_F32 && precision != MB200_PREC_BF16 && precision != MB200_PREC_F16) return MB200_ERR_INVALID_ARG;
+    if (precision != MB200_PREC_F32 && !blob_bf16) return MB200_ERR_INVALID_ARG;
     build_weights(blob, &W);
     build_weights_bf16(reinterpret_cast<const bf16 *>(blob_bf16), &Wb);
     if (ws_bytes < carve_workspace(nullptr, B, T, n_rows, precision, nullptr)) return MB200_ERR_INVALID_ARG;
     if ((uintptr_t)ws % 16 != 0 || (uintptr_t)blob % 16 != 0 || (uintptr_t)blob_bf16 % 16 != 0) return MB200_ERR_INVALID_ARG;
     carve_workspace((float *)ws, B, T, n_rows, precision, &c.ws);
-    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = precision == MB200_PREC_F16 ? 1 : 0;
     static bool attr_set = false;
     if (!attr_set) {
         MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
@@ -378,7 +379,7 @@ int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16
 }
 void eval_any(Ctx &c, const DecW &W, const DecWb &Wb, int precision, const float *x, const float *mu,
               const float *tb_rows, int n_rows, int per_sample, const float *x_in, float dt, float *out) {
-    if (precision == MB200_PREC_BF16) decoder_eval_bf16(c, W, Wb, x, mu, tb_rows, n_rows, per_sample, x_in, dt, out);
+    if (precision != MB200_PREC_F32) decoder_eval_bf16(c, W, Wb, x, mu, tb_rows, n_rows, per_sample, x_in, dt, out);
     else decoder_eval(c, W, x, mu, tb_rows, n_rows, per_sample, x_in, dt, out);
 }
 }  // namespace
@@ -391,14 +392,16 @@ extern "C" long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_row
     return carve_workspace(nullptr, B, T, n_rows, precision, nullptr);
 }
 
-extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_bf16_dev, void *stream) {
+extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_bf16_dev, int precision, void *stream) {
     if (!blob_dev || !blob_bf16_dev) return MB200_ERR_INVALID_ARG;
+    if (precision != MB200_PREC_BF16 && precision != MB200_PREC_F16) return MB200_ERR_INVALID_ARG;
+    const int f16 = precision == MB200_PREC_F16 ? 1 : 0;
     DecW W; DecWb Wb;
     build_weights(blob_dev, &W);
     build_weights_bf16(reinterpret_cast<bf16 *>(blob_bf16_dev), &Wb);
     cudaStream_t st = (cudaStream_t)stream;
     auto pack = [&](const float *src, const bf16 *dst, int rows, int cin, int cin_pad) {
-        pack_weight_bf16_kernel<<<256, 256, 0, st>>>(src, const_cast<bf16 *>(dst), rows, cin, cin_pad);
+        pack_weight_bf16_kernel<<<256, 256, 0, st>>>(src, const_cast<bf16 *>(dst), rows, cin, cin_pad, f16);
     };
     for (int i = 0; i < 6; ++i) {
         const StageW &s = W.st[i]; const StageWb &b = Wb.st[i];
@@ -463,7 +466,7 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
                                             const float *res, float *out_f32, void *out_bf16, const float *mask,
                                             void *stream) {
     Ctx c;
-    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0;
     MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
     gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);

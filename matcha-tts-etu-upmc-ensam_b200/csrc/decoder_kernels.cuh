@@ -15,6 +15,7 @@
 //                                                           decoder.py:367-371, flow_matching.py:95
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "common.cuh"
 
@@ -30,6 +31,16 @@ constexpr int kGroups = 8, kGroupCh = 32;
 __device__ __forceinline__ float mish_f(float x) {
     const float sp = (x > 20.0f) ? x : log1pf(expf(x));
     return x * tanhf(sp);
+}
+// 16-bit GEMM operands: bf16 (f16 == 0) or IEEE fp16 (f16 == 1); both travel as __nv_bfloat16-typed storage
+__device__ __forceinline__ uint32_t pack16x2(float a, float b, int f16) {
+    if (f16) { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t *>(&h); }
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+__device__ __forceinline__ __nv_bfloat16 pack16(float a, int f16) {
+    if (f16) { __half h = __float2half_rn(a); return *reinterpret_cast<__nv_bfloat16 *>(&h); }
+    return __float2bfloat16_rn(a);
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 __device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
@@ -125,6 +136,7 @@ struct GemmArgs {
     int out_T, out_stride, out_off;
     __nv_bfloat16 *out_bf16;      // optional bf16 copy, multiplied by omask[b][out row] (pitch mask_T)
     const float *omask;
+    int f16;
 };
 
 constexpr int kBM = 128, kBN = 64, kBK = 16;
@@ -226,9 +238,7 @@ gemm_f32_kernel(const GemmArgs g) {
         if (g.out) *reinterpret_cast<float4 *>(g.out + o) = v;
         if (g.out_bf16) {
             const float mk = g.omask ? g.omask[(size_t)b * g.mask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
-            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * mk, v.y * mk), hi = __floats2bfloat162_rn(v.z * mk, v.w * mk);
-            uint2 pk = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
-            *reinterpret_cast<uint2 *>(g.out_bf16 + o) = pk;
+            *reinterpret_cast<uint2 *>(g.out_bf16 + o) = make_uint2(pack16x2(v.x * mk, v.y * mk, g.f16), pack16x2(v.z * mk, v.w * mk, g.f16));
         }
     }
 }
@@ -272,7 +282,7 @@ __global__ void __launch_bounds__(256)
 gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, const float *__restrict__ gamma,
                const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
                const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out,
-               __nv_bfloat16 *__restrict__ out_bf16, int B, int T) {
+               __nv_bfloat16 *__restrict__ out_bf16, int f16, int B, int T) {
     const size_t n4 = (size_t)B * T * (kC / 4);
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
         const int c = (int)(i % (kC / 4)) * 4;
@@ -293,8 +303,7 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
         }
         if (out) *reinterpret_cast<float4 *>(out + i * 4) = o;
         if (out_bf16) {     // the bf16 copy is the next conv's operand: x*mask applied here (decoder.py:65)
-            __nv_bfloat162 lo = __floats2bfloat162_rn(o.x * mk, o.y * mk), hi = __floats2bfloat162_rn(o.z * mk, o.w * mk);
-            *reinterpret_cast<uint2 *>(out_bf16 + i * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+            *reinterpret_cast<uint2 *>(out_bf16 + i * 4) = make_uint2(pack16x2(o.x * mk, o.y * mk, f16), pack16x2(o.z * mk, o.w * mk, f16));
         }
     }
 }
@@ -303,7 +312,7 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
 // one warp per row
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta,
-                 float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, size_t rows) {
+                 float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int f16, size_t rows) {
     const int lane = threadIdx.x & 31;
     const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -328,10 +337,8 @@ layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, c
         *reinterpret_cast<float4 *>(out + row * kC + 128 + lane * 4) = o1;
     }
     if (out_bf16) {
-        __nv_bfloat162 p0 = __floats2bfloat162_rn(o0.x, o0.y), p1 = __floats2bfloat162_rn(o0.z, o0.w);
-        __nv_bfloat162 p2 = __floats2bfloat162_rn(o1.x, o1.y), p3 = __floats2bfloat162_rn(o1.z, o1.w);
-        *reinterpret_cast<uint2 *>(out_bf16 + row * kC + lane * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&p0), *reinterpret_cast<uint32_t *>(&p1));
-        *reinterpret_cast<uint2 *>(out_bf16 + row * kC + 128 + lane * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&p2), *reinterpret_cast<uint32_t *>(&p3));
+        *reinterpret_cast<uint2 *>(out_bf16 + row * kC + lane * 4) = make_uint2(pack16x2(o0.x, o0.y, f16), pack16x2(o0.z, o0.w, f16));
+        *reinterpret_cast<uint2 *>(out_bf16 + row * kC + 128 + lane * 4) = make_uint2(pack16x2(o1.x, o1.y, f16), pack16x2(o1.z, o1.w, f16));
     }
 }
 
@@ -344,7 +351,7 @@ constexpr int kAttSmemBytes = (2 * kAttBK * kAttPitch + kAttBQ * kAttPitch) * 4;
 
 __global__ void __launch_bounds__(128)
 attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ mask, int mask_T,
-                     float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int T) {
+                     float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int f16, int T) {
     extern __shared__ __align__(16) float att_smem[];
     float (*Ks)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem);
     float (*Vs)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem + kAttBK * kAttPitch);
@@ -429,8 +436,7 @@ attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ ma
         for (int d = 0; d < 32; d += 4) {
             if (out) *reinterpret_cast<float4 *>(out + oo + d) = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
             if (out_bf16) {
-                __nv_bfloat162 lo = __floats2bfloat162_rn(o[d] * inv, o[d + 1] * inv), hi = __floats2bfloat162_rn(o[d + 2] * inv, o[d + 3] * inv);
-                *reinterpret_cast<uint2 *>(out_bf16 + oo + d) = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+                *reinterpret_cast<uint2 *>(out_bf16 + oo + d) = make_uint2(pack16x2(o[d] * inv, o[d + 1] * inv, f16), pack16x2(o[d + 2] * inv, o[d + 3] * inv, f16));
             }
         }
     }
@@ -479,7 +485,7 @@ constexpr int kInChPad = 192;      // 160 input channels padded to three 64-wide
 // X0b[b][t][0:80] = x*mask, [80:160] = mu*mask, [160:192] = 0   (decoder.py:288 + the x*mask of :65,85)
 __global__ void __launch_bounds__(256)
 pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
-                       __nv_bfloat16 *__restrict__ out, int B, int T) {
+                       __nv_bfloat16 *__restrict__ out, int f16, int B, int T) {
     __shared__ float tile[32][33];
     const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 192 channels
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -493,7 +499,7 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
     __syncthreads();
     for (int i = ty; i < 32; i += 8) {
         const int t = t0 + i, c = c0 + tx;
-        if (t < T) out[((size_t)b * T + t) * kInChPad + c] = __float2bfloat16_rn(tile[tx][i]);
+        if (t < T) out[((size_t)b * T + t) * kInChPad + c] = pack16(tile[tx][i], f16);
     }
 }
 
@@ -501,7 +507,7 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
 // (identity when Tin == T) followed by the x*mask of the next Resnet1D.
 __global__ void __launch_bounds__(256)
 resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__restrict__ mask,
-                          __nv_bfloat16 *__restrict__ out, int B, int T) {
+                          __nv_bfloat16 *__restrict__ out, int f16, int B, int T) {
     const size_t n4 = (size_t)B * T * (kC / 4);
     const float scale = (float)Tin / (float)T;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
@@ -512,19 +518,18 @@ resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__
         if (Tin != T) { ts = (int)floorf((float)t * scale); if (ts > Tin - 1) ts = Tin - 1; }
         const float mk = mask[(size_t)b * T + t];
         const float4 v = *reinterpret_cast<const float4 *>(in + ((size_t)b * Tin + ts) * kC + c);
-        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * mk, v.y * mk), hi = __floats2bfloat162_rn(v.z * mk, v.w * mk);
-        *reinterpret_cast<uint2 *>(out + i * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+        *reinterpret_cast<uint2 *>(out + i * 4) = make_uint2(pack16x2(v.x * mk, v.y * mk, f16), pack16x2(v.z * mk, v.w * mk, f16));
     }
 }
 
 // dst[n][tap][0:cin_pad] = bf16(src[n][tap][0:cin]) zero-padded: GEMM weights for the tcgen05 path
 __global__ void __launch_bounds__(256)
-pack_weight_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int rows, int cin, int cin_pad) {
+pack_weight_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int rows, int cin, int cin_pad, int f16) {
     const size_t n = (size_t)rows * cin_pad;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
         const size_t r = i / cin_pad;
         const int c = (int)(i % cin_pad);
-        dst[i] = __float2bfloat16_rn(c < cin ? src[r * cin + c] : 0.f);
+        dst[i] = pack16(c < cin ? src[r * cin + c] : 0.f, f16);
     }
 }
 

@@ -39,6 +39,7 @@ struct GemmBf16Args {
     __nv_bfloat16 *out_bf16;           // bf16 [B][Tout][N] or nullptr
     const float *omask; int omask_T;   // multiplies the bf16 output rows (x*mask for the next conv)
     int N;
+    int f16;                           // operands are IEEE fp16 instead of bf16
 };
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
@@ -56,8 +57,9 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
-// kind::f16, A/B bf16 K-major, fp32 accumulate, M=128, N=256
-constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kGN >> 3) << 17) | ((uint32_t)(kGM >> 4) << 24);
+// kind::f16, A/B bf16 (format 1) or fp16 (format 0) K-major, fp32 accumulate, M=128, N=256
+constexpr uint32_t kIdescF16 = (1u << 4) | ((uint32_t)(kGN >> 3) << 17) | ((uint32_t)(kGM >> 4) << 24);
+constexpr uint32_t kIdescBf16 = kIdescF16 | (1u << 7) | (1u << 10);
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -141,7 +143,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sb);
 #pragma unroll
                 for (int k = 0; k < kGK / 16; ++k)     // 32 bytes along K per UMMA_K=16 step: +2 in 16-byte units
-                    umma_bf16(tmem_d, da + 2u * k, db + 2u * k, kIdescBf16, (kb | k) != 0 ? 1u : 0u);
+                    umma_bf16(tmem_d, da + 2u * k, db + 2u * k, g.f16 ? kIdescF16 : kIdescBf16, (kb | k) != 0 ? 1u : 0u);
                 umma_commit(bar_empty + 8u * s);        // frees the stage when these MMAs have read it
             }
             umma_commit(bar_acc);                       // accumulator complete
@@ -172,7 +174,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 if (g.out_f32) g.out_f32[o] = x;
                 if (g.out_bf16) {
                     const float mk = g.omask ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
-                    g.out_bf16[o] = __float2bfloat16_rn(x * mk);
+                    g.out_bf16[o] = pack16(x * mk, g.f16);
                 }
             }
         }

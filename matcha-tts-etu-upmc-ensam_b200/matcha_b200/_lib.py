@@ -57,7 +57,7 @@ def load_library():
     lib.matcha_b200_decoder_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
     lib.matcha_b200_decoder_blob_bf16_bytes.restype = ll
     lib.matcha_b200_decoder_pack_bf16.restype = c_int
-    lib.matcha_b200_decoder_pack_bf16.argtypes = [c_void_p, c_void_p, c_void_p]
+    lib.matcha_b200_decoder_pack_bf16.argtypes = [c_void_p, c_void_p, c_int, c_void_p]
     lib.matcha_b200_decoder_forward.restype = c_int
     lib.matcha_b200_decoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                                 c_void_p, ll, c_int, c_int, c_int, c_void_p]

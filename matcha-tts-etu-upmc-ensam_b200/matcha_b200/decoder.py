@@ -15,8 +15,8 @@ import torch
 
 from ._lib import check, load_library
 
-PREC_F32, PREC_BF16 = 0, 1
-_PRECISIONS = {"fp32": PREC_F32, "f32": PREC_F32, "bf16": PREC_BF16}
+PREC_F32, PREC_BF16, PREC_F16 = 0, 1, 2
+_PRECISIONS = {"fp32": PREC_F32, "f32": PREC_F32, "bf16": PREC_BF16, "fp16": PREC_F16, "f16": PREC_F16}
 
 C, TIME_DIM, IN_CH, OUT_CH = 256, 1024, 160, 80
 _STAGES = ("Downsampling_Blocks.0", "Downsampling_Blocks.1", "Mid_Blocks.0", "Mid_Blocks.1",
@@ -151,14 +151,15 @@ class Decoder(torch.nn.Module):
 
     def _blob16_on(self, device):
         """bf16 GEMM weights for the tcgen05 path (None in fp32 mode)."""
-        if _PRECISIONS[self.precision] != PREC_BF16:
+        if _PRECISIONS[self.precision] == PREC_F32:
             return None
         key = str(device)
         if key not in self._blob16:
             lib = load_library()
             buf = torch.empty(int(lib.matcha_b200_decoder_blob_bf16_bytes()), dtype=torch.uint8, device=device)
             with torch.cuda.device(device):
-                check(lib.matcha_b200_decoder_pack_bf16(self._blob_on(device).data_ptr(), buf.data_ptr(), _stream_ptr(device)),
+                check(lib.matcha_b200_decoder_pack_bf16(self._blob_on(device).data_ptr(), buf.data_ptr(),
+                                                        _PRECISIONS[self.precision], _stream_ptr(device)),
                       "decoder_pack_bf16")
             self._blob16[key] = buf
         return self._blob16[key]
