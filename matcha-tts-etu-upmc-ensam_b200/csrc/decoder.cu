@@ -11,6 +11,7 @@
 // implicit-GEMM loader.
 #include <vector>
 
+#include "attention_mma.cuh"
 #include "gemm_bf16.cuh"
 
 namespace mb200 {
@@ -278,9 +279,11 @@ static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf1
     gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, c.B, T);
     gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
     layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
-    gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, w.qkv, nullptr, false);
-    dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
-    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, nullptr, w.attb, c.f16, T);
+    bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
+    gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
+    dim3 agrid((T + kFaBQ - 1) / kFaBQ, kHeads, c.B);
+    if (c.f16) attention_mma_kernel<true><<<agrid, 128, kFaSmemBytes, c.st>>>(qkvb, c.mask, c.T, w.attb, T);
+    else attention_mma_kernel<false><<<agrid, 128, kFaSmemBytes, c.st>>>(qkvb, c.mask, c.T, w.attb, T);
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
     layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);

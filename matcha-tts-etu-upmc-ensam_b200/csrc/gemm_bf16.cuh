@@ -164,17 +164,28 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             __syncwarp();
             const int n = n0 + 32 * j + lane;
             const float bias = g.bias ? g.bias[n] : 0.f;
-            for (int r = 0; r < 32; ++r) {
-                const int t = trow0 + r;
-                if (t >= g.Tout) break;
-                float x = tb[r * 33 + lane] + bias;
-                if (g.act == 1) x = gelu_erf_f(x);
-                const size_t o = ((size_t)b * g.Tout + t) * g.N + n;
-                if (g.res) x += g.res[o];
-                if (g.out_f32) g.out_f32[o] = x;
-                if (g.out_bf16) {
-                    const float mk = g.omask ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
-                    g.out_bf16[o] = pack16(x * mk, g.f16);
+            // rows in groups of 8: the residual loads of a group are issued together so that their
+            // latency is paid once per group, not once per row
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 8) {
+                float rv[8], mk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int t = trow0 + r0 + i;
+                    rv[i] = (g.res && t < g.Tout) ? g.res[((size_t)b * g.Tout + t) * g.N + n] : 0.f;
+                    mk[i] = (g.omask && t < g.Tout) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int t = trow0 + r0 + i;
+                    if (t < g.Tout) {
+                        float x = tb[(r0 + i) * 33 + lane] + bias;
+                        if (g.act == 1) x = gelu_erf_f(x);
+                        x += rv[i];
+                        const size_t o = ((size_t)b * g.Tout + t) * g.N + n;
+                        if (g.out_f32) g.out_f32[o] = x;
+                        if (g.out_bf16) g.out_bf16[o] = pack16(x * mk[i], g.f16);
+                    }
                 }
             }
         }
