@@ -21,11 +21,12 @@
 namespace mb200 {
 
 constexpr int kGM = 128, kGN = 256, kGK = 64;          // CTA tile; UMMA 128 x 256 x 16
-constexpr int kGStages = 4;
+constexpr int kGStages = 2;                            // x 48 KB; two CTAs share an SM (and its 512 TMEM columns)
 constexpr int kGStageA = kGM * kGK * 2, kGStageB = kGN * kGK * 2;
 constexpr int kGStageBytes = kGStageA + kGStageB;      // 48 KB
-constexpr int kGEpiBytes = 4 * 32 * 33 * 4;            // per-warp transpose buffers
-constexpr int kGSmemBytes = kGStages * kGStageBytes + kGEpiBytes + 256 + 1024;
+constexpr int kGEpiPitch = 36;                         // floats; 16-byte aligned rows, conflict-free both ways
+constexpr int kGEpiBytes = 4 * 32 * kGEpiPitch * 4;    // per-warp transpose buffers
+constexpr int kGSmemBytes = kGStages * kGStageBytes + 256 + 1024;   // the epilogue's transpose tiles reuse the stage memory
 constexpr int kGThreads = 192;
 
 struct GemmBf16Args {
@@ -83,18 +84,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-__global__ void __launch_bounds__(kGThreads, 1)
+__global__ void __launch_bounds__(kGThreads, 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
     const uint32_t epi_off = kGStages * kGStageBytes;
-    const uint32_t bar_full = base + epi_off + kGEpiBytes;          // [kGStages]
+    const uint32_t bar_full = base + epi_off;                       // [kGStages]
     const uint32_t bar_empty = bar_full + 8u * kGStages;            // [kGStages]
     const uint32_t bar_acc = bar_empty + 8u * kGStages;             // accumulator ready
     const uint32_t tmem_slot = bar_acc + 8u;                        // u32 written by tcgen05.alloc
-    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + epi_off + kGEpiBytes + 16 * kGStages + 8);
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + epi_off + 16 * kGStages + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x % g.tiles_per_sample) * kGM;
@@ -150,42 +151,47 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         }
     } else {
         // ============================ epilogue ============================
+        // TMEM -> registers (lane = row) -> padded shared tile -> registers (lane = 4 columns of one
+        // of 4 rows), so that every global access is a 16-byte piece of a 128-byte row segment.
         const int q = warp & 3;                         // TMEM lane quarter this warp may touch
-        float *tb = reinterpret_cast<float *>(gbase + epi_off) + (warp - 2) * (32 * 33);
+        float *tb = reinterpret_cast<float *>(gbase) + (warp - 2) * (32 * kGEpiPitch);   // stage memory is idle once bar_acc fires
         mbar_wait_parked(bar_acc, 0, 2000);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         const int trow0 = t0 + 32 * q;
         for (int j = 0; j < kGN / 32; ++j) {
             uint32_t v[32];
             tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
             __syncwarp();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) tb[lane * 33 + i] = __uint_as_float(v[i]);
+            for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4 *>(tb + lane * kGEpiPitch + 4 * i) =
+                    make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
             __syncwarp();
-            const int n = n0 + 32 * j + lane;
-            const float bias = g.bias ? g.bias[n] : 0.f;
-            // rows in groups of 8: the residual loads of a group are issued together so that their
-            // latency is paid once per group, not once per row
-#pragma unroll 1
-            for (int r0 = 0; r0 < 32; r0 += 8) {
-                float rv[8], mk[8];
+            const int n = n0 + 32 * j + c4;
+            float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
+            float4 rv[8];
+            float mk[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int t = trow0 + r0 + i;
-                    rv[i] = (g.res && t < g.Tout) ? g.res[((size_t)b * g.Tout + t) * g.N + n] : 0.f;
-                    mk[i] = (g.omask && t < g.Tout) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
-                }
+            for (int i = 0; i < 8; ++i) {               // all residual / mask loads of the chunk first
+                const int t = trow0 + 4 * i + rsub;
+                const bool ok = t < g.Tout;
+                rv[i] = (g.res && ok) ? *reinterpret_cast<const float4 *>(g.res + ((size_t)b * g.Tout + t) * g.N + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
+            }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int t = trow0 + r0 + i;
-                    if (t < g.Tout) {
-                        float x = tb[(r0 + i) * 33 + lane] + bias;
-                        if (g.act == 1) x = gelu_erf_f(x);
-                        x += rv[i];
-                        const size_t o = ((size_t)b * g.Tout + t) * g.N + n;
-                        if (g.out_f32) g.out_f32[o] = x;
-                        if (g.out_bf16) g.out_bf16[o] = pack16(x * mk[i], g.f16);
-                    }
+            for (int i = 0; i < 8; ++i) {
+                const int t = trow0 + 4 * i + rsub;
+                if (t < g.Tout) {
+                    float4 x = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
+                    x.x += bias.x; x.y += bias.y; x.z += bias.z; x.w += bias.w;
+                    if (g.act == 1) { x.x = gelu_erf_f(x.x); x.y = gelu_erf_f(x.y); x.z = gelu_erf_f(x.z); x.w = gelu_erf_f(x.w); }
+                    x.x += rv[i].x; x.y += rv[i].y; x.z += rv[i].z; x.w += rv[i].w;
+                    const size_t o = ((size_t)b * g.Tout + t) * g.N + n;
+                    if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + o) = x;
+                    if (g.out_bf16)
+                        *reinterpret_cast<uint2 *>(g.out_bf16 + o) = make_uint2(pack16x2(x.x * mk[i], x.y * mk[i], g.f16), pack16x2(x.z * mk[i], x.w * mk[i], g.f16));
                 }
             }
         }
