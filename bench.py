@@ -43,6 +43,11 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel-only", action="store_true", help="profiling aid: skip the e2e and CPU-baseline legs")
+    ap.add_argument("--no-decoder", action="store_true", help="skip the CFM-decoder leg (BASELINE configs[2])")
+    ap.add_argument("--dec-batch", type=int, default=32)
+    ap.add_argument("--dec-T", type=int, default=800)
+    ap.add_argument("--dec-steps", type=int, default=10, help="Euler steps per solve")
+    ap.add_argument("--dec-precision", default="fp16", choices=["fp32", "fp16", "bf16"])
     return ap.parse_args()
 
 
@@ -130,6 +135,97 @@ def cpu_reference_rate(a, seconds, max_items=256):
     return {"value": n / best, "unit": UNIT, "cores": cores, "kind": "reference" if use_ref else "port",
             "sample": f"{n} utterances of the same ragged {a.tx}x{a.ty} workload, core only "
                       f"(compute_batch_alignments on numpy buffers), best of {done} passes, OpenMP prange over the batch"}
+
+
+def decoder_leg(a, dev, world, rank, dist, barrier):
+    """CFM decoder mel-frames/s (BASELINE configs[2]: 80-bin mel, T=800, Euler n=10, batch 32 per GPU,
+    random-init Matcha-size decoder).  Returns the dict that goes under "cfm_decoder" on rank 0."""
+    import torch
+    from types import SimpleNamespace
+    from matcha_b200.flow_matching import CFM
+    from oracle import decoder as odec
+    B, T, n = a.dec_batch, a.dec_T, a.dec_steps
+    params = dict(channels=(256, 256), dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=4)
+    weights = odec.make_weights(0, "init")                     # Decoder.initialize_weights distribution (decoder.py:255)
+    cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), params, precision=a.dec_precision)
+    cfm.load_state_dict(weights)
+    g = torch.Generator(device=dev); g.manual_seed(2000 + rank)
+    mu = torch.randn(B, 80, T, device=dev, generator=g)
+    z = torch.randn(B, 80, T, device=dev, generator=g)
+    mask = torch.ones(B, 1, T, device=dev)
+    t_span = torch.linspace(0, 1, n + 1, device=dev)
+    for _ in range(3):
+        out = cfm.solve_ode_euler(z, t_span, mu, mask, None, None)
+    barrier()
+    K = 5
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    for _ in range(K):
+        out = cfm.solve_ode_euler(z, t_span, mu, mask, None, None)
+    ev[1].record()
+    barrier()
+    ms = torch.tensor([ev[0].elapsed_time(ev[1]) / K], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    launches = int(cfm.estimator.last_launches)
+    # e2e: pinned host tensors in, host tensor out, through the reference-shaped CFM API
+    mu_h, z_h, mask_h = mu.cpu().pin_memory(), z.cpu().pin_memory(), mask.cpu().pin_memory()
+    out_h = torch.empty(B, 80, T).pin_memory()
+    def e2e_once():
+        o = cfm.solve_ode_euler(z_h.to(dev, non_blocking=True), t_span, mu_h.to(dev, non_blocking=True),
+                                mask_h.to(dev, non_blocking=True), None, None)
+        out_h.copy_(o, non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_once(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        e2e_once()
+    barrier()
+    e2e_s = torch.tensor([(time.perf_counter() - t0) / 3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        return None
+    flops = 2.0 * (6017024.0 * T + 1536.0 * T * T) * B * n          # SURVEY §8(d)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak, src = float(json.load(f)["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+    except Exception:
+        peak, src = 1400.0, "fallback (B200_PROFILING.md ~1.4 PFLOP/s sustained)"
+    res = {
+        "metric": "cfm_decoder_mel_frames_per_sec", "value": world * B * T / (ms / 1e3), "unit": "mel-frames/s",
+        "ms_per_solve": ms, "n_gpus": world, "scaling": "weak", "dtype": a.dec_precision, "data": "synthetic",
+        "config": {"workload": f"CFM Euler solve B={B}/GPU T_mel={T} n_timesteps={n} 80-bin mel, random-init "
+                               f"Matcha-size decoder (BASELINE configs[2])", "precision": a.dec_precision},
+        "roofline": {"bound": "tensor", "achieved": flops / (ms / 1e3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                     "frac": flops / (ms / 1e3) / 1e12 / peak, "traffic": None, "peak_source": src,
+                     "algorithmic_flops_per_solve": flops, "kernel": "gemm_bf16_kernel (tcgen05) + attention_mma_kernel"},
+        "e2e": {"value": world * B * T / float(e2e_s.item()), "unit": "mel-frames/s",
+                "h2d_bytes_per_step": int(4 * (2 * B * 80 * T + B * T)), "d2h_bytes_per_step": int(4 * B * 80 * T),
+                "api": "matcha_b200.flow_matching.CFM.solve_ode_euler on pinned host tensors"},
+        "gpu_launches_per_solve": launches,
+    }
+    if a.dec_precision != "fp32":          # accuracy of the 16-bit mode against our own fp32 mode, same inputs
+        ref = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), params, precision="fp32")
+        ref.load_state_dict(weights)
+        o32 = ref.solve_ode_euler(z, t_span, mu, mask, None, None)
+        res["rel_l2_vs_fp32_mode"] = float(torch.linalg.norm((out - o32).double()) / torch.linalg.norm(o32.double()))
+    if world == 1 and not a.no_cpu_baseline:
+        # the reference's arithmetic (torch CPU fp32, oracle/decoder.py) on a bounded sample
+        torch.set_num_threads(os.cpu_count() or 1)
+        w = weights
+        bs, ns = min(4, B), 2
+        xs, mus, ms_ = z[:bs].cpu(), mu[:bs].cpu(), mask[:bs].cpu()
+        tsp = torch.linspace(0, 1, ns + 1)
+        odec.solve_euler(w, xs, torch.linspace(0, 1, 2), mus, ms_)      # warm-up, one eval
+        t1 = time.perf_counter()
+        odec.solve_euler(w, xs, tsp, mus, ms_)
+        dt = time.perf_counter() - t1
+        res["cpu_baseline"] = {"value": bs * T / (dt * n / ns), "unit": "mel-frames/s", "cores": torch.get_num_threads(),
+                               "kind": "port", "sample": f"torch CPU fp32 restatement of the reference decoder, B={bs}, T={T}, "
+                                                         f"{ns} Euler steps timed and scaled to n={n}"}
+    return res
 
 
 def run_reference(a):
@@ -279,6 +375,15 @@ def run_ours(a):
         }
         if world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference_rate(a, a.cpu_seconds)
+    dec = None
+    if not a.no_decoder:
+        del value, path
+        torch.cuda.empty_cache()
+        dec = decoder_leg(a, dev, world, rank, dist, barrier)
+    if rank == 0:
+        if dec is not None:
+            line["cfm_decoder"] = dec
+            line["gpu_launches"] = a.steps + 5 * dec["gpu_launches_per_solve"]
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
