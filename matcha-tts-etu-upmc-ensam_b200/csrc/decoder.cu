@@ -203,7 +203,7 @@ static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu,
 
 // ================================================================== bf16 mode (tcgen05 GEMMs)
 typedef __nv_bfloat16 bf16;
-struct StageWb { const bf16 *wc1, *wc2, *wr, *wqkv, *wo, *w1, *w2, *wtail; int cin_pad; };
+struct StageWb { const bf16 *wc1, *wc2, *wr, *wqkv, *wo, *w1, *w2, *wtail, *wtail2; int cin_pad; };
 struct DecWb { StageWb st[6]; const bf16 *wf; };
 static const int kStageCinPad[6] = {kInChPad, kC, kC, kC, 2 * kC, 2 * kC};
 
@@ -217,7 +217,10 @@ static long long build_weights_bf16(const bf16 *blob, DecWb *w) {
         s.cin_pad = kStageCinPad[i];
         s.wc1 = take(256LL * 3 * s.cin_pad); s.wc2 = take(256LL * 3 * 256); s.wr = take(256LL * s.cin_pad);
         s.wqkv = take(768LL * 256); s.wo = take(256LL * 256); s.w1 = take(1024LL * 256); s.w2 = take(256LL * 1024);
-        s.wtail = (i == 1 || i == 5) ? take(256LL * 3 * 256) : nullptr;
+        s.wtail = s.wtail2 = nullptr;
+        if (i == 0) s.wtail = take(256LL * 2 * 512);              // stride-2 conv on the paired view
+        if (i == 1 || i == 5) s.wtail = take(256LL * 3 * 256);
+        if (i == 4) { s.wtail = take(256LL * 2 * 256); s.wtail2 = take(256LL * 2 * 256); }   // ConvTranspose phases
     }
     d.wf = take(256LL * 3 * 256);
     if (w) *w = d;
@@ -244,7 +247,7 @@ static bool tmap_for(Ctx &c, const bf16 *base, int ndim, uint64_t d0, uint64_t d
 // reference multiplies), w: bf16 [N][ntaps*(c0+c1)].
 static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
                    const bf16 *w, int N, const float *bias, int act, const float *res, float *out_f32,
-                   bf16 *out_b16, bool omask) {
+                   bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0) {
     if (c.err) return;
     CUtensorMap ma0, ma1, mb;
     if (!tmap_for(c, a0, 3, (uint64_t)c0, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma0)) return;
@@ -258,6 +261,7 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     g.c0_chunks = c0 / kGK; g.c1_chunks = c1 / kGK;
     g.bias = bias; g.act = act; g.res = res; g.out_f32 = out_f32; g.out_bf16 = out_b16;
     g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.N = N; g.f16 = c.f16;
+    g.out_T = out_T > 0 ? out_T : T; g.out_stride = out_T > 0 ? out_stride : 1; g.out_off = out_T > 0 ? out_off : 0;
     dim3 grid(g.tiles_per_sample * c.B, N / kGN);
     gemm_bf16_kernel<<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
     c.launches++;
@@ -304,8 +308,11 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     pack_input_bf16_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, c.mask, w.x0b, c.f16, c.B, T);
     c.launches++;
     // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
-    run_stage_bf16(c, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, w.s0, w.s0b);
-    {
+    run_stage_bf16(c, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, (T & 1) ? w.s0 : nullptr, w.s0b);
+    if ((T & 1) == 0) {
+        static const int taps_pair[2] = {-1, 0};
+        gemm_b(c, w.s0b, 2 * kC, nullptr, 0, 2, taps_pair, T2, Wb.st[0].wtail, kC, W.st[0].btail, 0, nullptr, nullptr, w.inb, true);
+    } else {
         GemmArgs g;
         g.a0 = w.s0; g.a1 = nullptr; g.c0 = kC; g.c1 = 0; g.Ta0 = T; g.mask = c.mask; g.mask_T = c.T;
         g.ntaps = 3; g.tap_off[0] = -1; g.tap_off[1] = 0; g.tap_off[2] = 1; g.tap_off[3] = 0; g.stride = 2;
@@ -319,11 +326,11 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     gemm_b(c, w.s1b, kC, nullptr, 0, 3, taps3, T2, Wb.st[1].wtail, kC, W.st[1].btail, 0, nullptr, nullptr, w.inb, true);
     run_stage_bf16(c, W.st[2], Wb.st[2], w.inb, kC, nullptr, 0, T2, tb(2), tb_per_sample, nullptr, w.upb);
     run_stage_bf16(c, W.st[3], Wb.st[3], w.upb, kC, nullptr, 0, T2, tb(3), tb_per_sample, nullptr, w.inb);
-    run_stage_bf16(c, W.st[4], Wb.st[4], w.inb, kC, w.s1b, kC, T2, tb(4), tb_per_sample, w.x3, nullptr);
+    run_stage_bf16(c, W.st[4], Wb.st[4], w.inb, kC, w.s1b, kC, T2, tb(4), tb_per_sample, nullptr, w.upb);
     // ConvTranspose1d(4,2,1) (decoder.py:112) as two phase GEMMs on the fp32 kernel, then the nearest
     // resample (odd T) + x*mask into the bf16 operand of the last Resnet1D
-    gemm(c, w.x3, kC, T2, nullptr, 0, true, 2, taps_even, 1, T2, T2, W.st[4].wtail, W.st[4].btail, kC, 0, nullptr, w.d, Tu, 2, 0);
-    gemm(c, w.x3, kC, T2, nullptr, 0, true, 2, taps_odd, 1, T2, T2, W.st[4].wtail2, W.st[4].btail, kC, 0, nullptr, w.d, Tu, 2, 1);
+    gemm_b(c, w.upb, kC, nullptr, 0, 2, taps_even, T2, Wb.st[4].wtail, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 0);
+    gemm_b(c, w.upb, kC, nullptr, 0, 2, taps_odd, T2, Wb.st[4].wtail2, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 1);
     {
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
@@ -415,7 +422,9 @@ extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_b
         pack(s.wo, b.wo, 256, 256, 256);
         pack(s.w1, b.w1, 1024, 256, 256);
         pack(s.w2, b.w2, 256, 1024, 1024);
-        if (b.wtail) pack(s.wtail, b.wtail, 256 * 3, 256, 256);
+        if (i == 0) pack_down_weight_kernel<<<256, 256, 0, st>>>(s.wtail, const_cast<bf16 *>(b.wtail), f16);
+        if (i == 1 || i == 5) pack(s.wtail, b.wtail, 256 * 3, 256, 256);
+        if (i == 4) { pack(s.wtail, b.wtail, 256 * 2, 256, 256); pack(s.wtail2, b.wtail2, 256 * 2, 256, 256); }
     }
     pack(W.wf, Wb.wf, 256 * 3, 256, 256);
     MB200_CUDA_TRY(cudaGetLastError());

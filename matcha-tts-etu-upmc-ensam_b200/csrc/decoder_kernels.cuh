@@ -533,4 +533,19 @@ pack_weight_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict
     }
 }
 
+// Stride-2 Conv1d (Downsample1D, decoder.py:95) on the paired view [B][T/2][512] of an even-T input:
+// out[t] = W0 x[2t-1] + W1 x[2t] + W2 x[2t+1] = tap(-1): [0 | W0] . pair[t-1]  +  tap(0): [W1 | W2] . pair[t]
+// dst[n][2][512] from src[n][3][256]
+__global__ void __launch_bounds__(256)
+pack_down_weight_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int f16) {
+    const int n = blockIdx.x;
+    for (int i = threadIdx.x; i < 2 * 512; i += 256) {
+        const int tap = i >> 9, c = i & 511;
+        float v = 0.f;
+        if (tap == 0) { if (c >= 256) v = src[((size_t)n * 3 + 0) * 256 + (c - 256)]; }
+        else v = src[((size_t)n * 3 + 1 + (c >> 8)) * 256 + (c & 255)];
+        dst[(size_t)n * 1024 + i] = pack16(v, f16);
+    }
+}
+
 }  // namespace mb200

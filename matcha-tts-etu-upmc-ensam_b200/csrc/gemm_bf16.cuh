@@ -40,6 +40,7 @@ struct GemmBf16Args {
     __nv_bfloat16 *out_bf16;           // bf16 [B][Tout][N] or nullptr
     const float *omask; int omask_T;   // multiplies the bf16 output rows (x*mask for the next conv)
     int N;
+    int out_T, out_stride, out_off;    // output row of tile row t: t*out_stride + out_off (ConvTranspose phases)
     int f16;                           // operands are IEEE fp16 instead of bf16
 };
 
@@ -159,6 +160,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         const int trow0 = t0 + 32 * q;
+        // output element offsets of this lane's 8 rows (column part added per chunk); -1 = row beyond Tout
+        long long orow[8];
+        float mk[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int t = trow0 + 4 * i + rsub;
+            const bool ok = t < g.Tout;
+            const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
+            orow[i] = ok ? r * g.N : -1;
+            mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
+        }
+        float4 rv[8];
+        auto load_res = [&](int jj) {                    // residual rows of chunk jj (issued one chunk ahead)
+            const int n = n0 + 32 * jj + c4;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                rv[i] = (g.res && orow[i] >= 0) ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        load_res(0);
         for (int j = 0; j < kGN / 32; ++j) {
             uint32_t v[32];
             tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
@@ -171,27 +191,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const int n = n0 + 32 * j + c4;
             float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
             if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
-            float4 rv[8];
-            float mk[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {               // all residual / mask loads of the chunk first
-                const int t = trow0 + 4 * i + rsub;
-                const bool ok = t < g.Tout;
-                rv[i] = (g.res && ok) ? *reinterpret_cast<const float4 *>(g.res + ((size_t)b * g.Tout + t) * g.N + n) : make_float4(0.f, 0.f, 0.f, 0.f);
-                mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
-            }
+            float4 x[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int t = trow0 + 4 * i + rsub;
-                if (t < g.Tout) {
-                    float4 x = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
-                    x.x += bias.x; x.y += bias.y; x.z += bias.z; x.w += bias.w;
-                    if (g.act == 1) { x.x = gelu_erf_f(x.x); x.y = gelu_erf_f(x.y); x.z = gelu_erf_f(x.z); x.w = gelu_erf_f(x.w); }
-                    x.x += rv[i].x; x.y += rv[i].y; x.z += rv[i].z; x.w += rv[i].w;
-                    const size_t o = ((size_t)b * g.Tout + t) * g.N + n;
-                    if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + o) = x;
+                x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
+                x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
+                if (g.act == 1) { x[i].x = gelu_erf_f(x[i].x); x[i].y = gelu_erf_f(x[i].y); x[i].z = gelu_erf_f(x[i].z); x[i].w = gelu_erf_f(x[i].w); }
+                x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w;
+            }
+            if (j + 1 < kGN / 32) load_res(j + 1);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (orow[i] >= 0) {
+                    if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x[i];
                     if (g.out_bf16)
-                        *reinterpret_cast<uint2 *>(g.out_bf16 + o) = make_uint2(pack16x2(x.x * mk[i], x.y * mk[i], g.f16), pack16x2(x.z * mk[i], x.w * mk[i], g.f16));
+                        *reinterpret_cast<uint2 *>(g.out_bf16 + orow[i] + n) =
+                            make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], g.f16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], g.f16));
                 }
             }
         }
