@@ -103,6 +103,7 @@ struct Ctx {
     int launches;
     int err;
     int f16;             // 16-bit operand format of the tensor-core mode: 0 bf16, 1 fp16
+    const float *fin_xin = nullptr; float fin_dt = 0.f; float *fin_out = nullptr;   // set around the final-projection GEMM
     std::vector<TmapEntry> tmaps;   // tensor maps of this call's bf16 tensors
 };
 
@@ -204,7 +205,7 @@ static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu,
 // ================================================================== bf16 mode (tcgen05 GEMMs)
 typedef __nv_bfloat16 bf16;
 struct StageWb { const bf16 *wc1, *wc2, *wr, *wqkv, *wo, *w1, *w2, *wtail, *wtail2; int cin_pad; };
-struct DecWb { StageWb st[6]; const bf16 *wf; };
+struct DecWb { StageWb st[6]; const bf16 *wf, *wp; };
 static const int kStageCinPad[6] = {kInChPad, kC, kC, kC, 2 * kC, 2 * kC};
 
 // Order must match pack_bf16 below.
@@ -223,6 +224,7 @@ static long long build_weights_bf16(const bf16 *blob, DecWb *w) {
         if (i == 4) { s.wtail = take(256LL * 2 * 256); s.wtail2 = take(256LL * 2 * 256); }   // ConvTranspose phases
     }
     d.wf = take(256LL * 3 * 256);
+    d.wp = take(256LL * 256);        // final_proj [80][256] zero-padded to the 256-wide tile
     if (w) *w = d;
     return off;
 }
@@ -262,6 +264,8 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     g.bias = bias; g.act = act; g.res = res; g.out_f32 = out_f32; g.out_bf16 = out_b16;
     g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.N = N; g.f16 = c.f16;
     g.out_T = out_T > 0 ? out_T : T; g.out_stride = out_T > 0 ? out_stride : 1; g.out_off = out_T > 0 ? out_off : 0;
+    g.fin_n = 0; g.fin_xin = nullptr; g.fin_dt = 0.f; g.fin_out = nullptr;
+    if (c.fin_out) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
     dim3 grid(g.tiles_per_sample * c.B, N / kGN);
     gemm_bf16_kernel<<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
     c.launches++;
@@ -341,9 +345,16 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     gemm_b(c, w.inb, kC, nullptr, 0, 3, taps3, T, Wb.st[5].wtail, kC, W.st[5].btail, 0, nullptr, nullptr, w.a1b, true);
     gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, Wb.wf, kC, W.bf, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    dim3 fgrid((T + 31) / 32, c.B);
-    final_proj_kernel<<<fgrid, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, W.wp, W.bp, x_in, dt, out, T);
-    c.launches++;
+    {   // final_norm + Mish + x*mask into the 16-bit operand, then final_proj + mask + Euler update in the GEMM epilogue
+        static const int tap0[1] = {0};
+        const long long n4 = (long long)c.B * T * (kC / 4);
+        int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
+        gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, c.B, T);
+        c.launches++;
+        c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
+        gemm_b(c, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
+        c.fin_out = nullptr;
+    }
 }
 
 static TimeWeights time_weights(const DecW &W) {
@@ -427,6 +438,8 @@ extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_b
         if (i == 4) { pack(s.wtail, b.wtail, 256 * 2, 256, 256); pack(s.wtail2, b.wtail2, 256 * 2, 256, 256); }
     }
     pack(W.wf, Wb.wf, 256 * 3, 256, 256);
+    MB200_CUDA_TRY(cudaMemsetAsync(const_cast<bf16 *>(Wb.wp), 0, 256 * 256 * sizeof(bf16), st));
+    pack(W.wp, Wb.wp, kMel, 256, 256);
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
 }

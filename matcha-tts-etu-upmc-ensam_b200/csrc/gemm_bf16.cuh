@@ -42,6 +42,9 @@ struct GemmBf16Args {
     int N;
     int out_T, out_stride, out_off;    // output row of tile row t: t*out_stride + out_off (ConvTranspose phases)
     int f16;                           // operands are IEEE fp16 instead of bf16
+    // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
+    // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
+    int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
 };
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
@@ -160,6 +163,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         const int trow0 = t0 + 32 * q;
+        if (g.fin_n > 0) {
+            // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
+            const int t = trow0 + lane;
+            const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
+            for (int j = 0; j * 32 < g.fin_n; ++j) {
+                uint32_t v[32];
+                tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int n = 32 * j + i;
+                    if (n < g.fin_n && t < g.Tout) {
+                        const float vel = (__uint_as_float(v[i]) + g.bias[n]) * mk;
+                        const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
+                        g.fin_out[o] = g.fin_xin ? __fadd_rn(g.fin_xin[o], __fmul_rn(g.fin_dt, vel)) : vel;
+                    }
+                }
+            }
+        } else {
         // output element offsets of this lane's 8 rows (column part added per chunk); -1 = row beyond Tout
         long long orow[8];
         float mk[8];
@@ -209,6 +230,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                             make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], g.f16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], g.f16));
                 }
             }
+        }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }

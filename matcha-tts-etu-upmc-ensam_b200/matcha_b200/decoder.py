@@ -119,6 +119,8 @@ class Decoder(torch.nn.Module):
         self._blob = {}               # device -> packed fp32 blob
         self._blob16 = {}             # device -> bf16 GEMM weights (bf16 mode)
         self._ws = {}                 # (device, B, T, rows) -> workspace
+        self._graphs = {}             # captured Euler solves
+        self.use_graph = True
 
     # -- weights ----------------------------------------------------------------------------
     def load_state_dict(self, state_dict, strict=True):
@@ -194,24 +196,55 @@ class Decoder(torch.nn.Module):
         return out.to(x.dtype)
 
     @torch.no_grad()
-    def solve_euler(self, x, t_span, mu, mask):
-        """The whole Euler loop of flow_matching.py:67-104 in one C call."""
+    def solve_euler(self, x, t_span, mu, mask, use_graph=None):
+        """The whole Euler loop of flow_matching.py:67-104 in one C call.  With ``use_graph`` (default: on for
+        CUDA inputs) the ~95 kernel launches per step are captured once per (B, T, n_steps) into a CUDA graph
+        and replayed, which removes the launch gaps between the small kernels."""
         lib = load_library()
         B, _, T = x.shape
         dev = x.device
         ts, dts = euler_time_grid(t_span.detach().to("cpu", torch.float32))
         n = len(ts)
-        xf, muf = x.float().contiguous(), mu.float().contiguous()
-        mf = mask.float().reshape(B, T).contiguous()
-        out = torch.empty_like(xf)
+        if use_graph is None:
+            use_graph = self.use_graph
         blob, b16, ws = self._blob_on(dev), self._blob16_on(dev), self._workspace(dev, B, T, n)
         t_arr = (ctypes.c_float * n)(*[float(v) for v in ts])
         dt_arr = (ctypes.c_float * n)(*[float(v) for v in dts])
-        with torch.cuda.device(dev):
-            self.last_launches = check(lib.matcha_b200_cfm_solve_euler(
-                xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), out.data_ptr(), t_arr, dt_arr, n, blob.data_ptr(),
-                b16.data_ptr() if b16 is not None else None, ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision], _stream_ptr(dev)), "cfm_solve_euler")
-        return out.to(x.dtype)
+
+        def launch(xf, muf, mf, out):
+            with torch.cuda.device(dev):
+                self.last_launches = check(lib.matcha_b200_cfm_solve_euler(
+                    xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), out.data_ptr(), t_arr, dt_arr, n, blob.data_ptr(),
+                    b16.data_ptr() if b16 is not None else None, ws.data_ptr(), ws.numel(), B, T,
+                    _PRECISIONS[self.precision], _stream_ptr(dev)), "cfm_solve_euler")
+
+        if not use_graph:
+            xf, muf = x.float().contiguous(), mu.float().contiguous()
+            mf = mask.float().reshape(B, T).contiguous()
+            out = torch.empty_like(xf)
+            launch(xf, muf, mf, out)
+            return out.to(x.dtype)
+
+        key = (str(dev), B, T, tuple(float(v) for v in ts), tuple(float(v) for v in dts), self.precision)
+        entry = self._graphs.get(key)
+        if entry is None:
+            st = {"x": torch.empty(B, 80, T, device=dev), "mu": torch.empty(B, 80, T, device=dev),
+                  "mask": torch.empty(B, T, device=dev), "out": torch.empty(B, 80, T, device=dev)}
+            st["x"].copy_(x); st["mu"].copy_(mu); st["mask"].copy_(mask.reshape(B, T))
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                launch(st["x"], st["mu"], st["mask"], st["out"])      # warm-up outside the capture (sets attributes)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                launch(st["x"], st["mu"], st["mask"], st["out"])
+            entry = (graph, st)
+            self._graphs = {key: entry}                                # keep one shape alive
+        graph, st = entry
+        st["x"].copy_(x); st["mu"].copy_(mu); st["mask"].copy_(mask.reshape(B, T))
+        graph.replay()
+        return st["out"].to(x.dtype, copy=True)
 
 
 def euler_time_grid(t_span):
