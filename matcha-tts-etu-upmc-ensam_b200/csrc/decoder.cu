@@ -67,7 +67,7 @@ static long long build_weights(const float *blob, DecW *w) {
 
 // ---------------------------------------------------------------- workspace
 struct DecWs {
-    float *tb, *x0, *h, *a, *g, *x1, *ln, *qkv, *att, *x2, *f1, *x3, *s0, *s1, *d, *stats;
+    float *tb, *th2, *x0, *h, *a, *g, *x1, *ln, *qkv, *att, *x2, *f1, *x3, *s0, *s1, *d, *stats;
     __nv_bfloat16 *x0b, *a1b, *lnb, *attb, *f1b, *inb, *s0b, *s1b, *upb;   // bf16 mode only
 };
 
@@ -77,6 +77,7 @@ static long long carve_workspace(float *base, int B, int T, int n_rows, int prec
     auto take = [&](long long n) { float *p = base ? base + off : nullptr; off += (n + 3) & ~3LL; return p; };
     DecWs w;
     w.tb = take(6LL * n_rows * kC);
+    w.th2 = take((long long)n_rows * kTimeDim);
     w.x0 = take(M * kInCh);
     w.h = take(M * kC); w.a = take(M * kC); w.g = take(M * kC); w.x1 = take(M * kC); w.ln = take(M * kC);
     w.qkv = take(M * 3 * kC); w.att = take(M * kC); w.x2 = take(M * kC); w.f1 = take(M * 4 * kC); w.x3 = take(M * kC);
@@ -267,7 +268,9 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     g.fin_n = 0; g.fin_xin = nullptr; g.fin_dt = 0.f; g.fin_out = nullptr;
     if (c.fin_out) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
     dim3 grid(g.tiles_per_sample * c.B, N / kGN);
-    gemm_bf16_kernel<<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
+    // few tiles (at most one per SM): nothing to co-schedule, spend the shared memory on a deeper TMA ring
+    g.stages = (long long)grid.x * grid.y <= kNumSMsB200 ? 4 : 2;
+    gemm_bf16_kernel<<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
     c.launches++;
 }
 
@@ -393,7 +396,7 @@ int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16
     static bool attr_set = false;
     if (!attr_set) {
         MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
         attr_set = true;
     }
     return MB200_OK;
@@ -454,11 +457,12 @@ extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_d
     Ctx c; DecW W; DecWb Wb;
     rc = prepare(c, W, Wb, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, mask_dev, B, T, n_t, precision, stream);
     if (rc != MB200_OK) return rc;
-    time_embed_kernel<<<n_t, 256, 0, c.st>>>(time_weights(W), t_dev, n_t, c.ws.tb);
+    time_embed1_kernel<<<dim3(n_t, 16), 256, 0, c.st>>>(time_weights(W), t_dev, c.ws.th2);
+    time_embed2_kernel<<<dim3(n_t, 24), 256, 0, c.st>>>(time_weights(W), c.ws.th2, n_t, c.ws.tb);
     eval_any(c, W, Wb, precision, x_dev, mu_dev, c.ws.tb, n_t, n_t == B && B > 1 ? 1 : 0, nullptr, 0.f, out_dev);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
-    return c.launches + 1;
+    return c.launches + 2;
 }
 
 extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,
@@ -476,13 +480,14 @@ extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_
     for (int i = 0; i < n_steps; ++i) tv.v[i] = t_host[i];
     float *t_stage = c.ws.h;          // free until the first conv writes it
     stage_times_kernel<<<1, 64, 0, c.st>>>(tv, n_steps, t_stage);
-    time_embed_kernel<<<n_steps, 256, 0, c.st>>>(time_weights(W), t_stage, n_steps, c.ws.tb);
+    time_embed1_kernel<<<dim3(n_steps, 16), 256, 0, c.st>>>(time_weights(W), t_stage, c.ws.th2);
+    time_embed2_kernel<<<dim3(n_steps, 24), 256, 0, c.st>>>(time_weights(W), c.ws.th2, n_steps, c.ws.tb);
     for (int k = 0; k < n_steps; ++k)
         eval_any(c, W, Wb, precision, k == 0 ? x0_dev : out_dev, mu_dev, c.ws.tb + (size_t)k * kC, n_steps, 0,
                  k == 0 ? x0_dev : out_dev, dt_host[k], out_dev);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
-    return c.launches + 2;
+    return c.launches + 3;
 }
 
 // test aid, not part of the public header: one tcgen05 implicit GEMM on caller-provided bf16 operands
@@ -492,7 +497,7 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
                                             void *stream) {
     Ctx c;
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0;
-    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
     gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);
     if (c.err) return c.err;

@@ -46,7 +46,7 @@ __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x));
 __device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
 // ------------------------------------------------------------------ time embedding
-// One block per time row (n_rows = Euler steps, or batch items for per-sample t).
+// n_rows time rows (Euler steps, or batch items for per-sample t), two launches spread over 16-24 CTAs per row.
 // out_tb[stage][row][256] = Linear_stage(Mish(time_mlp(sinusoidal(t[row]))))
 struct TimeWeights {
     const float *freq;            // [80], built on the host exactly as decoder.py:26-27 does
@@ -55,11 +55,11 @@ struct TimeWeights {
     const float *wt[6], *bt[6];   // [256][1024], [256]
 };
 
+// step 1, grid (n_rows, 16): h2[row][o] = Mish(W2 SiLU(W1 emb(t[row]) + b1) + b2)[o] for 64 outputs per block
 __global__ void __launch_bounds__(256)
-time_embed_kernel(TimeWeights w, const float *__restrict__ t, int n_rows, float *__restrict__ out_tb) {
+time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict__ h2) {
     __shared__ float emb[kInCh];
     __shared__ float h1[kTimeDim];
-    __shared__ float h2[kTimeDim];
     const int row = blockIdx.x, tid = threadIdx.x;
     const float tv = t[row];
     if (tid < 80) {
@@ -75,24 +75,31 @@ time_embed_kernel(TimeWeights w, const float *__restrict__ t, int n_rows, float 
         h1[o] = silu_f(acc + w.b1[o]);
     }
     __syncthreads();
-    // 1024x1024: one warp per output, lanes stride the input (coalesced weight rows)
     const int warp = tid >> 5, lane = tid & 31;
-    for (int o = warp; o < kTimeDim; o += 8) {
+    for (int oo = warp; oo < 64; oo += 8) {                     // one warp per output, coalesced weight rows
+        const int o = blockIdx.y * 64 + oo;
         const float *wr = w.w2 + (size_t)o * kTimeDim;
         float acc = 0.f;
         for (int i = lane; i < kTimeDim; i += 32) acc = fmaf(wr[i], h1[i], acc);
         for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
-        if (lane == 0) h2[o] = mish_f(acc + w.b2[o]);          // Mish of Resnet1D.mlp[0] applied once here
+        if (lane == 0) h2[(size_t)row * kTimeDim + o] = mish_f(acc + w.b2[o]);   // Mish of Resnet1D.mlp[0]
     }
+}
+// step 2, grid (n_rows, 6 stages x 4): out_tb[stage][row][o] = Linear_stage(h2[row])[o], 64 outputs per block
+__global__ void __launch_bounds__(256)
+time_embed2_kernel(TimeWeights w, const float *__restrict__ h2, int n_rows, float *__restrict__ out_tb) {
+    __shared__ float hs[kTimeDim];
+    const int row = blockIdx.x, st = blockIdx.y >> 2, part = blockIdx.y & 3, tid = threadIdx.x;
+    for (int i = tid; i < kTimeDim; i += 256) hs[i] = h2[(size_t)row * kTimeDim + i];
     __syncthreads();
-    for (int st = 0; st < 6; ++st) {
-        for (int o = warp; o < kC; o += 8) {
-            const float *wr = w.wt[st] + (size_t)o * kTimeDim;
-            float acc = 0.f;
-            for (int i = lane; i < kTimeDim; i += 32) acc = fmaf(wr[i], h2[i], acc);
-            for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
-            if (lane == 0) out_tb[((size_t)st * n_rows + row) * kC + o] = acc + w.bt[st][o];
-        }
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int oo = warp; oo < 64; oo += 8) {
+        const int o = part * 64 + oo;
+        const float *wr = w.wt[st] + (size_t)o * kTimeDim;
+        float acc = 0.f;
+        for (int i = lane; i < kTimeDim; i += 32) acc = fmaf(wr[i], hs[i], acc);
+        for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+        if (lane == 0) out_tb[((size_t)st * n_rows + row) * kC + o] = acc + w.bt[st][o];
     }
 }
 

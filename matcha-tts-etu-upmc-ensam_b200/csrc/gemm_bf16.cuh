@@ -21,12 +21,12 @@
 namespace mb200 {
 
 constexpr int kGM = 128, kGN = 256, kGK = 64;          // CTA tile; UMMA 128 x 256 x 16
-constexpr int kGStages = 2;                            // x 48 KB; two CTAs share an SM (and its 512 TMEM columns)
+constexpr int kGMaxStages = 4;                         // ring depth is a launch parameter: 2 (two CTAs per SM) or 4
 constexpr int kGStageA = kGM * kGK * 2, kGStageB = kGN * kGK * 2;
 constexpr int kGStageBytes = kGStageA + kGStageB;      // 48 KB
 constexpr int kGEpiPitch = 36;                         // floats; 16-byte aligned rows, conflict-free both ways
 constexpr int kGEpiBytes = 4 * 32 * kGEpiPitch * 4;    // per-warp transpose buffers
-constexpr int kGSmemBytes = kGStages * kGStageBytes + 256 + 1024;   // the epilogue's transpose tiles reuse the stage memory
+__host__ __device__ constexpr int gemm_smem_bytes(int stages) { return stages * kGStageBytes + 256 + 1024; }   // epilogue tiles reuse the stages
 constexpr int kGThreads = 192;
 
 struct GemmBf16Args {
@@ -42,6 +42,7 @@ struct GemmBf16Args {
     int N;
     int out_T, out_stride, out_off;    // output row of tile row t: t*out_stride + out_off (ConvTranspose phases)
     int f16;                           // operands are IEEE fp16 instead of bf16
+    int stages;                        // TMA ring depth (2 or 4)
     // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
     // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
     int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
@@ -94,6 +95,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
+    const int kGStages = g.stages;
     const uint32_t epi_off = kGStages * kGStageBytes;
     const uint32_t bar_full = base + epi_off;                       // [kGStages]
     const uint32_t bar_empty = bar_full + 8u * kGStages;            // [kGStages]
