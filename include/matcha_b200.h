@@ -68,10 +68,12 @@ int matcha_b200_mas_lengths_from_mask(
     int *t_xs_dev, int *t_ys_dev, void *stream);
 
 /*
- * Host-buffer convenience with the reference's C-level contract (core.pyx:101-107):
- * copies values/lengths to the device, runs the kernel, copies int32 paths back and
- * synchronises.  Returns the number of out-of-domain items (>= 0) or a negative error.
- * Device scratch is allocated and freed inside the call.
+ * Host buffers with the reference's C-level contract (core.pyx:101-107): `paths_host` must be
+ * zero-initialised by the caller, exactly as the reference requires (__init__.py:49 passes np.zeros);
+ * only the valid [t_x][t_y] block of every utterance is written.  Values and lengths go to the device
+ * and int32 paths come back in slices through a three-stream pipeline (H2D, kernel and D2H overlap);
+ * pinned host memory makes the copies asynchronous.  Returns the number of out-of-domain items (>= 0,
+ * their paths stay zero) or a negative error.  Device scratch is allocated and freed inside the call.
  */
 int matcha_b200_mas_maximum_path_host(
     int *paths_host, const float *values_host,

@@ -1,6 +1,7 @@
 // api.cu -- library-wide pieces of the C ABI: error strings, the tensor-map encoder and the
 // host-buffer MAS entry point (the numpy round trip of
 // /root/reference/matcha/utils/monotonic_align/__init__.py:45-55).
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -82,38 +83,92 @@ extern "C" int matcha_b200_last_cuda_error(void) { return g_last_cuda_error; }
 
 extern "C" const char *matcha_b200_version(void) { return "0.1.0"; }
 
+// Host-buffer MAS: the batch is cut into slices that flow through a three-stream pipeline (H2D of slice
+// i+1, kernel of slice i, D2H of slice i-1 run concurrently; PCIe is full duplex).  Only the valid
+// [t_x][t_y] block of every utterance crosses the bus in either direction, as 2-D copies.
 extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *values_host,
                                                   const int *t_xs_host, const int *t_ys_host,
                                                   int B, int T_x, int T_y, float penalty) {
     if (B < 0 || T_x <= 0 || T_y <= 0) return MB200_ERR_INVALID_ARG;
     if (B == 0) return 0;
     if (!paths_host || !values_host || !t_xs_host || !t_ys_host) return MB200_ERR_INVALID_ARG;
-    const size_t n = (size_t)B * T_x * T_y;
-    float *d_val = nullptr;
-    int *d_path = nullptr, *d_len = nullptr;
-    cudaStream_t st = nullptr;
+    const size_t item = (size_t)T_x * T_y;
+    const char *envm = getenv("MB200_MAS_HOST_MODE");     // experiments: 1 = contiguous [t_x][T_y] row blocks instead of 2-D copies
+    const bool rows_only = envm && envm[0] == '1';
+    const char *envs = getenv("MB200_MAS_HOST_SLICES");
+    int n_slices = B < 16 ? 1 : (envs ? atoi(envs) : 16);
+    if (n_slices < 1) n_slices = 1;
+    if (item * sizeof(float) * B < (64u << 20)) n_slices = 1;        // small batches: one shot
+    const int Bs = (B + n_slices - 1) / n_slices;
+    float *d_val[2] = {nullptr, nullptr};
+    int *d_path[2] = {nullptr, nullptr}, *d_len = nullptr;
+    cudaStream_t st[3] = {nullptr, nullptr, nullptr};                // h2d, compute, d2h
+    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {};
     int rc = MB200_OK, bad = 0;
     cudaError_t e;
 #define HOST_TRY(x) do { e = (x); if (e != cudaSuccess) { rc = cuda_fail(e); goto done; } } while (0)
-    HOST_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-    HOST_TRY(cudaMalloc(&d_val, n * sizeof(float)));
-    HOST_TRY(cudaMalloc(&d_path, n * sizeof(int)));
+    for (int i = 0; i < 3; ++i) HOST_TRY(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        HOST_TRY(cudaMalloc(&d_val[i], (size_t)Bs * item * sizeof(float)));
+        HOST_TRY(cudaMalloc(&d_path[i], (size_t)Bs * item * sizeof(int)));
+        HOST_TRY(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
+        HOST_TRY(cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming));
+        HOST_TRY(cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming));
+    }
     HOST_TRY(cudaMalloc(&d_len, (2 * (size_t)B + 1) * sizeof(int)));
-    HOST_TRY(cudaMemcpyAsync(d_val, values_host, n * sizeof(float), cudaMemcpyHostToDevice, st));
-    HOST_TRY(cudaMemcpyAsync(d_len, t_xs_host, B * sizeof(int), cudaMemcpyHostToDevice, st));
-    HOST_TRY(cudaMemcpyAsync(d_len + B, t_ys_host, B * sizeof(int), cudaMemcpyHostToDevice, st));
-    HOST_TRY(cudaMemsetAsync(d_len + 2 * B, 0, sizeof(int), st));
-    rc = matcha_b200_mas_compute_batch_alignments(d_path, MB200_PATH_I32, d_val, nullptr, d_len, d_len + B,
-                                                  B, T_x, T_y, penalty, d_len + 2 * B, st);
-    if (rc != MB200_OK) goto done;
-    HOST_TRY(cudaMemcpyAsync(paths_host, d_path, n * sizeof(int), cudaMemcpyDeviceToHost, st));
-    HOST_TRY(cudaMemcpyAsync(&bad, d_len + 2 * B, sizeof(int), cudaMemcpyDeviceToHost, st));
-    HOST_TRY(cudaStreamSynchronize(st));
+    HOST_TRY(cudaMemcpyAsync(d_len, t_xs_host, B * sizeof(int), cudaMemcpyHostToDevice, st[1]));
+    HOST_TRY(cudaMemcpyAsync(d_len + B, t_ys_host, B * sizeof(int), cudaMemcpyHostToDevice, st[1]));
+    HOST_TRY(cudaMemsetAsync(d_len + 2 * B, 0, sizeof(int), st[1]));
+    for (int s = 0, b0 = 0; b0 < B; ++s, b0 += Bs) {
+        const int nb = B - b0 < Bs ? B - b0 : Bs, buf = s & 1;
+        // the value buffer is free once the kernel that read it (slice s-2) is done
+        if (s >= 2) HOST_TRY(cudaStreamWaitEvent(st[0], ev_k[buf], 0));
+        for (int i = 0; i < nb; ++i) {
+            const int tx = t_xs_host[b0 + i], ty = t_ys_host[b0 + i];
+            if (tx < 1 || ty < 1 || tx > T_x || ty > T_y) continue;
+            if (rows_only)
+                HOST_TRY(cudaMemcpyAsync(d_val[buf] + (size_t)i * item, values_host + (size_t)(b0 + i) * item,
+                                         (size_t)tx * T_y * sizeof(float), cudaMemcpyHostToDevice, st[0]));
+            else
+                HOST_TRY(cudaMemcpy2DAsync(d_val[buf] + (size_t)i * item, (size_t)T_y * sizeof(float),
+                                           values_host + (size_t)(b0 + i) * item, (size_t)T_y * sizeof(float),
+                                           (size_t)ty * sizeof(float), (size_t)tx, cudaMemcpyHostToDevice, st[0]));
+        }
+        HOST_TRY(cudaEventRecord(ev_in[buf], st[0]));
+        HOST_TRY(cudaStreamWaitEvent(st[1], ev_in[buf], 0));
+        if (s >= 2) HOST_TRY(cudaStreamWaitEvent(st[1], ev_out[buf], 0));   // path buffer drained
+        rc = matcha_b200_mas_compute_batch_alignments(d_path[buf], MB200_PATH_I32, d_val[buf], nullptr, d_len + b0,
+                                                      d_len + B + b0, nb, T_x, T_y, penalty, d_len + 2 * B, st[1]);
+        if (rc != MB200_OK) goto done;
+        HOST_TRY(cudaEventRecord(ev_k[buf], st[1]));
+        HOST_TRY(cudaStreamWaitEvent(st[2], ev_k[buf], 0));
+        for (int i = 0; i < nb; ++i) {
+            const int tx = t_xs_host[b0 + i], ty = t_ys_host[b0 + i];
+            if (tx < 1 || ty < 1 || tx > ty || tx > T_x || ty > T_y) continue;   // invalid items: all-zero path
+            if (rows_only)
+                HOST_TRY(cudaMemcpyAsync(paths_host + (size_t)(b0 + i) * item, d_path[buf] + (size_t)i * item,
+                                         (size_t)tx * T_y * sizeof(int), cudaMemcpyDeviceToHost, st[2]));
+            else
+                HOST_TRY(cudaMemcpy2DAsync(paths_host + (size_t)(b0 + i) * item, (size_t)T_y * sizeof(int),
+                                           d_path[buf] + (size_t)i * item, (size_t)T_y * sizeof(int),
+                                           (size_t)ty * sizeof(int), (size_t)tx, cudaMemcpyDeviceToHost, st[2]));
+        }
+        HOST_TRY(cudaEventRecord(ev_out[buf], st[2]));
+    }
+    HOST_TRY(cudaStreamSynchronize(st[2]));
+    HOST_TRY(cudaMemcpyAsync(&bad, d_len + 2 * B, sizeof(int), cudaMemcpyDeviceToHost, st[1]));
+    HOST_TRY(cudaStreamSynchronize(st[1]));
 #undef HOST_TRY
 done:
-    if (d_val) cudaFree(d_val);
-    if (d_path) cudaFree(d_path);
+    for (int i = 0; i < 3; ++i) if (st[i]) cudaStreamSynchronize(st[i]);
+    for (int i = 0; i < 2; ++i) {
+        if (d_val[i]) cudaFree(d_val[i]);
+        if (d_path[i]) cudaFree(d_path[i]);
+        if (ev_in[i]) cudaEventDestroy(ev_in[i]);
+        if (ev_k[i]) cudaEventDestroy(ev_k[i]);
+        if (ev_out[i]) cudaEventDestroy(ev_out[i]);
+    }
     if (d_len) cudaFree(d_len);
-    if (st) cudaStreamDestroy(st);
+    for (int i = 0; i < 3; ++i) if (st[i]) cudaStreamDestroy(st[i]);
     return rc != MB200_OK ? rc : bad;
 }

@@ -129,9 +129,11 @@ def maximum_path(value, mask, mask_mode="full", check_lengths=False):
 
 def compute_batch_alignments(paths, values, t_xs, t_ys, max_neg_val=-1e9):
     """core.pyx:101-107 with the same argument order.  Accepts either numpy arrays (host buffers:
-    copied to the device and back inside the call, synchronous, like the reference) or CUDA
-    tensors (asynchronous on the current stream).  ``paths`` is filled in place (int32, or
-    float32 for CUDA tensors); ``values`` is left untouched (the reference clobbers it)."""
+    copied to the device and back inside the call through a sliced H2D / kernel / D2H pipeline,
+    synchronous, like the reference; ``paths`` must be zero-initialised by the caller exactly as the
+    reference requires, __init__.py:49) or CUDA tensors (asynchronous on the current stream, every
+    element of ``paths`` written).  ``paths`` is int32 (or float32 for CUDA tensors); ``values`` is
+    left untouched (the reference clobbers it)."""
     _require_cuda()
     lib = load_library()
     if isinstance(values, np.ndarray):

