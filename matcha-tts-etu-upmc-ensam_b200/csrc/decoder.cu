@@ -105,6 +105,7 @@ struct Ctx {
     int err;
     int f16;             // 16-bit operand format of the tensor-core mode: 0 bf16, 1 fp16
     const float *fin_xin = nullptr; float fin_dt = 0.f; float *fin_out = nullptr;   // set around the final-projection GEMM
+    int debug = 0;
     std::vector<TmapEntry> tmaps;   // tensor maps of this call's bf16 tensors
 };
 
@@ -270,7 +271,11 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     dim3 grid(g.tiles_per_sample * c.B, N / kGN);
     // few tiles (at most one per SM): nothing to co-schedule, spend the shared memory on a deeper TMA ring
     g.stages = (long long)grid.x * grid.y <= kNumSMsB200 ? 4 : 2;
-    gemm_bf16_kernel<<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
+    g.debug = c.debug;
+    if ((long long)c.B * g.out_T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
+    if (g.fin_n > 0) gemm_bf16_kernel<2><<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
+    else if (act == 1) gemm_bf16_kernel<1><<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
+    else gemm_bf16_kernel<0><<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
     c.launches++;
 }
 
@@ -396,7 +401,9 @@ int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16
     static bool attr_set = false;
     if (!attr_set) {
         MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
         attr_set = true;
     }
     return MB200_OK;
@@ -496,11 +503,17 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
                                             const float *res, float *out_f32, void *out_bf16, const float *mask,
                                             void *stream) {
     Ctx c;
-    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0;
-    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0; c.debug = 1;
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
     gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+extern "C" int matcha_b200_debug_gemm_stamps(long long *out8) {
+    MB200_CUDA_TRY(cudaMemcpyFromSymbol(out8, mb200::g_gemm_dbg, sizeof(long long) * 8));
     return MB200_OK;
 }

@@ -43,6 +43,7 @@ struct GemmBf16Args {
     int out_T, out_stride, out_off;    // output row of tile row t: t*out_stride + out_off (ConvTranspose phases)
     int f16;                           // operands are IEEE fp16 instead of bf16
     int stages;                        // TMA ring depth (2 or 4)
+    int debug;
     // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
     // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
     int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
@@ -89,6 +90,11 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// profiling aid: clock64 stamps of CTA 0 (start, first stage landed, accumulator ready, epilogue done)
+__device__ long long g_gemm_dbg[8];
+
+// EPI: 0 plain, 1 erf-GELU, 2 final projection (compile-time so that unused epilogue code costs no issue slots)
+template <int EPI>
 __global__ void __launch_bounds__(kGThreads, 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
@@ -122,6 +128,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot_p;
+    const bool dbg = g.debug && blockIdx.x == 0 && blockIdx.y == 0;
+    if (dbg && threadIdx.x == 0) g_gemm_dbg[0] = clock64();
 
     if (warp == 0) {
         // ============================ TMA producer ============================
@@ -145,6 +153,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             for (int kb = 0; kb < n_kb; ++kb) {
                 const int s = kb % kGStages;
                 mbar_wait_parked(bar_full + 8u * s, (kb / kGStages) & 1, 1000);
+                if (dbg && kb == 0) g_gemm_dbg[1] = clock64();
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
                 const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sb);
@@ -163,9 +172,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         float *tb = reinterpret_cast<float *>(gbase) + (warp - 2) * (32 * kGEpiPitch);   // stage memory is idle once bar_acc fires
         mbar_wait_parked(bar_acc, 0, 2000);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (dbg && threadIdx.x == 64) g_gemm_dbg[2] = clock64();
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         const int trow0 = t0 + 32 * q;
-        if (g.fin_n > 0) {
+        if (EPI == 2) {
             // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
             const int t = trow0 + lane;
             const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
@@ -184,14 +194,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             }
         } else {
         // output element offsets of this lane's 8 rows (column part added per chunk); -1 = row beyond Tout
-        long long orow[8];
+        int orow[8];                                   // element offsets fit 32 bits (B*T*N < 2^31, checked on the host)
         float mk[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int t = trow0 + 4 * i + rsub;
             const bool ok = t < g.Tout;
             const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
-            orow[i] = ok ? r * g.N : -1;
+            orow[i] = ok ? (int)(r * g.N) : -1;
             mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
         }
         float4 rv[8];
@@ -205,12 +215,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         for (int j = 0; j < kGN / 32; ++j) {
             uint32_t v[32];
             tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
+            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[4] = clock64();
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 8; ++i)
                 *reinterpret_cast<float4 *>(tb + lane * kGEpiPitch + 4 * i) =
                     make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
             __syncwarp();
+            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[5] = clock64();
             const int n = n0 + 32 * j + c4;
             float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
             if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
@@ -219,9 +231,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             for (int i = 0; i < 8; ++i) {
                 x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
                 x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
-                if (g.act == 1) { x[i].x = gelu_erf_f(x[i].x); x[i].y = gelu_erf_f(x[i].y); x[i].z = gelu_erf_f(x[i].z); x[i].w = gelu_erf_f(x[i].w); }
+                if (EPI == 1) { x[i].x = gelu_erf_f(x[i].x); x[i].y = gelu_erf_f(x[i].y); x[i].z = gelu_erf_f(x[i].z); x[i].w = gelu_erf_f(x[i].w); }
                 x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w;
             }
+            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[6] = clock64();
             if (j + 1 < kGN / 32) load_res(j + 1);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -232,6 +245,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                             make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], g.f16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], g.f16));
                 }
             }
+            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[7] = clock64();
+            if (dbg && threadIdx.x == 64 && j == 0) g_gemm_dbg[3] = clock64();
         }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

@@ -26,4 +26,8 @@ for (c0, taps, N, with_res, with_b16, with_f32) in [(64, [0], 256, 0, 0, 0), (64
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 100
     fl = 2.0 * B * T * N * c0 * len(taps)
+    torch.cuda.synchronize()
+    buf = (ctypes.c_longlong * 8)(); lib.matcha_b200_debug_gemm_stamps(buf)
+    st_ = [(buf[i] - buf[0]) / 1965.0 for i in range(8)]
+    print(f"   stamps us: first-stage {st_[1]:.2f} acc-ready {st_[2]:.2f} chunk0-done {st_[3]:.2f} | chunk1: ldtm {st_[4]:.2f} transposed {st_[5]:.2f} math {st_[6]:.2f} stored {st_[7]:.2f}")
     print(f"K={c0*len(taps):5d} N={N:5d} res={with_res} b16={with_b16} f32={with_f32}: {us:8.1f} us  {fl/us/1e6:7.1f} TFLOP/s")
