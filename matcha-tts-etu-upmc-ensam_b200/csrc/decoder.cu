@@ -268,14 +268,13 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     g.out_T = out_T > 0 ? out_T : T; g.out_stride = out_T > 0 ? out_stride : 1; g.out_off = out_T > 0 ? out_off : 0;
     g.fin_n = 0; g.fin_xin = nullptr; g.fin_dt = 0.f; g.fin_out = nullptr;
     if (c.fin_out) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
-    dim3 grid(g.tiles_per_sample * c.B, N / kGN);
-    // few tiles (at most one per SM): nothing to co-schedule, spend the shared memory on a deeper TMA ring
-    g.stages = (long long)grid.x * grid.y <= kNumSMsB200 ? 4 : 2;
+    const long long n_tiles = (long long)g.tiles_per_sample * c.B * (N / kGN);
+    const int grid = (int)(n_tiles < kNumSMsB200 ? n_tiles : kNumSMsB200);      // persistent: one CTA per SM
     g.debug = c.debug;
     if ((long long)c.B * g.out_T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
-    if (g.fin_n > 0) gemm_bf16_kernel<2><<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
-    else if (act == 1) gemm_bf16_kernel<1><<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
-    else gemm_bf16_kernel<0><<<grid, kGThreads, gemm_smem_bytes(g.stages), c.st>>>(ma0, ma1, mb, g);
+    if (g.fin_n > 0) gemm_bf16_kernel<2><<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
+    else if (act == 1) gemm_bf16_kernel<1><<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
+    else gemm_bf16_kernel<0><<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
     c.launches++;
 }
 
@@ -401,9 +400,9 @@ int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16
     static bool attr_set = false;
     if (!attr_set) {
         MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
         attr_set = true;
     }
     return MB200_OK;
@@ -504,8 +503,8 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
                                             void *stream) {
     Ctx c;
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0; c.debug = 1;
-    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
-    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(kGMaxStages)));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
     gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);
     if (c.err) return c.err;

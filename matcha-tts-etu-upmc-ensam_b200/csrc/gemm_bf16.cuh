@@ -2,15 +2,17 @@
 //
 // D[128 x 256] (fp32, TMEM) = sum over (tap, 64-channel chunk) of A[128 x 64] * W[256 x 64]^T, bf16
 // operands staged in shared memory by TMA in the 128B-swizzled K-major layout both TMA and the
-// UMMA shared-memory descriptor understand.  One CTA per output tile:
+// UMMA shared-memory descriptor understand.  Warp roles:
 //   warp 0      TMA producer: A boxes from a 3-D map over the bf16 activation [B][T][C] (the conv
 //               taps are row offsets; rows outside [0,T) come back as zeros, which is the conv's
 //               zero padding, decoder.py:59), W boxes from a 2-D map over [N][K].
-//   warp 1      allocates 256 TMEM columns and issues tcgen05.mma (one elected lane), releasing
-//               stages with tcgen05.commit.
-//   warps 2..5  epilogue: tcgen05.ld (lane = output row), transpose through shared memory so that
+//   warp 1      allocates all 512 TMEM columns (two 128x256 fp32 accumulators) and issues tcgen05.mma
+//               (one elected lane), releasing stages with tcgen05.commit.
+//   warps 2..9  epilogue: tcgen05.ld (lane = output row), transpose through shared memory so that
 //               global accesses are row-contiguous, then bias / erf-GELU / residual / row mask and
 //               fp32 and/or bf16 stores.
+// The CTA is persistent (one per SM, tiles dealt round-robin): while the epilogue warps drain one
+// accumulator, the MMA warp already fills the other one with the CTA's next tile.
 // Reference arithmetic: nn.Conv1d / nn.Linear of decoder.py:59,78,192,239,248 and the diffusers
 // Attention / FeedForward projections (transformer.py:251-259,156,180).
 #pragma once
@@ -21,13 +23,14 @@
 namespace mb200 {
 
 constexpr int kGM = 128, kGN = 256, kGK = 64;          // CTA tile; UMMA 128 x 256 x 16
-constexpr int kGMaxStages = 4;                         // ring depth is a launch parameter: 2 (two CTAs per SM) or 4
+constexpr int kGStages = 3;                            // TMA ring depth (x 48 KB)
 constexpr int kGStageA = kGM * kGK * 2, kGStageB = kGN * kGK * 2;
 constexpr int kGStageBytes = kGStageA + kGStageB;      // 48 KB
+constexpr int kGEpiWarps = 8;                          // two warps per TMEM lane quarter, four 32-column chunks each
 constexpr int kGEpiPitch = 36;                         // floats; 16-byte aligned rows, conflict-free both ways
-constexpr int kGEpiBytes = 4 * 32 * kGEpiPitch * 4;    // per-warp transpose buffers
-__host__ __device__ constexpr int gemm_smem_bytes(int stages) { return stages * kGStageBytes + 256 + 1024; }   // epilogue tiles reuse the stages
-constexpr int kGThreads = 192;
+constexpr int kGEpiBytes = kGEpiWarps * 32 * kGEpiPitch * 4;    // per-warp transpose buffers
+constexpr int kGSmemBytes = kGStages * kGStageBytes + kGEpiBytes + 256 + 1024;
+constexpr int kGThreads = 32 * (2 + kGEpiWarps);
 
 struct GemmBf16Args {
     int B, Tout, tiles_per_sample;
@@ -42,7 +45,6 @@ struct GemmBf16Args {
     int N;
     int out_T, out_stride, out_off;    // output row of tile row t: t*out_stride + out_off (ConvTranspose phases)
     int f16;                           // operands are IEEE fp16 instead of bf16
-    int stages;                        // TMA ring depth (2 or 4)
     int debug;
     // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
     // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
@@ -90,45 +92,45 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// profiling aid: clock64 stamps of CTA 0 (start, first stage landed, accumulator ready, epilogue done)
+// profiling aid: clock64 stamps of CTA 0 (start, first stage landed, first accumulator ready, first tile stored)
 __device__ long long g_gemm_dbg[8];
 
 // EPI: 0 plain, 1 erf-GELU, 2 final projection (compile-time so that unused epilogue code costs no issue slots)
 template <int EPI>
-__global__ void __launch_bounds__(kGThreads, 2)
+__global__ void __launch_bounds__(kGThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
-    const int kGStages = g.stages;
     const uint32_t epi_off = kGStages * kGStageBytes;
-    const uint32_t bar_full = base + epi_off;                       // [kGStages]
-    const uint32_t bar_empty = bar_full + 8u * kGStages;            // [kGStages]
-    const uint32_t bar_acc = bar_empty + 8u * kGStages;             // accumulator ready
-    const uint32_t tmem_slot = bar_acc + 8u;                        // u32 written by tcgen05.alloc
-    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + epi_off + 16 * kGStages + 8);
+    const uint32_t bar_full = base + epi_off + kGEpiBytes;          // [kGStages]  TMA -> MMA
+    const uint32_t bar_empty = bar_full + 8u * kGStages;            // [kGStages]  MMA -> TMA
+    const uint32_t bar_tfull = bar_empty + 8u * kGStages;           // [2] accumulator ready   MMA -> epilogue
+    const uint32_t bar_tempty = bar_tfull + 16u;                    // [2] accumulator drained epilogue -> MMA
+    const uint32_t tmem_slot = bar_tempty + 16u;                    // u32 written by tcgen05.alloc
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + epi_off + kGEpiBytes + 16 * kGStages + 32);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x % g.tiles_per_sample) * kGM;
-    const int n0 = blockIdx.y * kGN;
     const int chunks = g.c0_chunks + g.c1_chunks;
     const int n_kb = g.ntaps * chunks;
+    const int n_tiles_n = g.N / kGN;
+    const int n_tiles = g.B * g.tiles_per_sample * n_tiles_n;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kGStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
-        mbar_init(bar_acc, 1u);
+        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8u * a, 1u); mbar_init(bar_tempty + 8u * a, kGEpiWarps); }
         mbar_fence_init();
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(kGN) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot_p;
-    const bool dbg = g.debug && blockIdx.x == 0 && blockIdx.y == 0;
+    const bool dbg = g.debug && blockIdx.x == 0;
     if (dbg && threadIdx.x == 0) g_gemm_dbg[0] = clock64();
 
     if (warp == 0) {
@@ -136,125 +138,146 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         if (lane == 0) {
             tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmB);
             if (g.c1_chunks) tma_prefetch_desc(&tmA1);
-            for (int kb = 0; kb < n_kb; ++kb) {
-                const int s = kb % kGStages;
-                mbar_wait_parked(bar_empty + 8u * s, ((kb / kGStages) & 1) ^ 1, 1000);
-                const int tap = kb / chunks, ch = kb - tap * chunks;
-                const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
-                mbar_arrive_expect_tx(bar_full + 8u * s, kGStageBytes);
-                if (ch < g.c0_chunks) tma_load_3d(sa, &tmA0, bar_full + 8u * s, ch * kGK, t0 + g.tap_off[tap], b);
-                else tma_load_3d(sa, &tmA1, bar_full + 8u * s, (ch - g.c0_chunks) * kGK, t0 + g.tap_off[tap], b);
-                tma_load_2d(sb, &tmB, bar_full + 8u * s, kb * kGK, n0);
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int mt = tile / n_tiles_n, n0 = (tile - mt * n_tiles_n) * kGN;
+                const int b = mt / g.tiles_per_sample, t0 = (mt - b * g.tiles_per_sample) * kGM;
+                for (int kb = 0; kb < n_kb; ++kb, ++it) {
+                    const uint32_t s = it % kGStages;
+                    mbar_wait_parked(bar_empty + 8u * s, ((it / kGStages) & 1) ^ 1, 1000);
+                    const int tap = kb / chunks, ch = kb - tap * chunks;
+                    const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
+                    mbar_arrive_expect_tx(bar_full + 8u * s, kGStageBytes);
+                    if (ch < g.c0_chunks) tma_load_3d(sa, &tmA0, bar_full + 8u * s, ch * kGK, t0 + g.tap_off[tap], b);
+                    else tma_load_3d(sa, &tmA1, bar_full + 8u * s, (ch - g.c0_chunks) * kGK, t0 + g.tap_off[tap], b);
+                    tma_load_2d(sb, &tmB, bar_full + 8u * s, kb * kGK, n0);
+                }
             }
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ============================
         if (lane == 0) {
-            for (int kb = 0; kb < n_kb; ++kb) {
-                const int s = kb % kGStages;
-                mbar_wait_parked(bar_full + 8u * s, (kb / kGStages) & 1, 1000);
-                if (dbg && kb == 0) g_gemm_dbg[1] = clock64();
+            const uint32_t idesc = g.f16 ? kIdescF16 : kIdescBf16;
+            uint32_t it = 0, lt = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+                const uint32_t acc = lt & 1;
+                mbar_wait_parked(bar_tempty + 8u * acc, ((lt >> 1) & 1) ^ 1, 1000);     // epilogue has drained it
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
-                const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sb);
+                for (int kb = 0; kb < n_kb; ++kb, ++it) {
+                    const uint32_t s = it % kGStages;
+                    mbar_wait_parked(bar_full + 8u * s, (it / kGStages) & 1, 1000);
+                    if (dbg && it == 0) g_gemm_dbg[1] = clock64();
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sb);
 #pragma unroll
-                for (int k = 0; k < kGK / 16; ++k)     // 32 bytes along K per UMMA_K=16 step: +2 in 16-byte units
-                    umma_bf16(tmem_d, da + 2u * k, db + 2u * k, g.f16 ? kIdescF16 : kIdescBf16, (kb | k) != 0 ? 1u : 0u);
-                umma_commit(bar_empty + 8u * s);        // frees the stage when these MMAs have read it
+                    for (int k = 0; k < kGK / 16; ++k)     // 32 bytes along K per UMMA_K=16 step: +2 in 16-byte units
+                        umma_bf16(tmem_d + acc * kGN, da + 2u * k, db + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit(bar_empty + 8u * s);        // frees the stage when these MMAs have read it
+                }
+                umma_commit(bar_tfull + 8u * acc);          // accumulator complete
             }
-            umma_commit(bar_acc);                       // accumulator complete
         }
     } else {
         // ============================ epilogue ============================
         // TMEM -> registers (lane = row) -> padded shared tile -> registers (lane = 4 columns of one
         // of 4 rows), so that every global access is a 16-byte piece of a 128-byte row segment.
+        const int ew = warp - 2;
         const int q = warp & 3;                         // TMEM lane quarter this warp may touch
-        float *tb = reinterpret_cast<float *>(gbase) + (warp - 2) * (32 * kGEpiPitch);   // stage memory is idle once bar_acc fires
-        mbar_wait_parked(bar_acc, 0, 2000);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        if (dbg && threadIdx.x == 64) g_gemm_dbg[2] = clock64();
+        const int jhalf = (ew >> 2) * 4;                // this warp's four 32-column chunks
+        float *tb = reinterpret_cast<float *>(gbase + epi_off) + ew * (32 * kGEpiPitch);
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
-        const int trow0 = t0 + 32 * q;
-        if (EPI == 2) {
-            // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
-            const int t = trow0 + lane;
-            const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
-            for (int j = 0; j * 32 < g.fin_n; ++j) {
-                uint32_t v[32];
-                tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
+        uint32_t lt = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+            const int mt = tile / n_tiles_n, n0 = (tile - mt * n_tiles_n) * kGN;
+            const int b = mt / g.tiles_per_sample, t0 = (mt - b * g.tiles_per_sample) * kGM;
+            const uint32_t acc = lt & 1;
+            const uint32_t tacc = tmem_d + acc * kGN + ((uint32_t)(32 * q) << 16);
+            const int trow0 = t0 + 32 * q;
+            mbar_wait_parked(bar_tfull + 8u * acc, (lt >> 1) & 1, 2000);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (dbg && lt == 0 && threadIdx.x == 64) g_gemm_dbg[2] = clock64();
+            if (EPI == 2) {
+                // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
+                const int t = trow0 + lane;
+                const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
+                for (int j = jhalf; j < jhalf + 4 && j * 32 < g.fin_n; ++j) {
+                    uint32_t v[32];
+                    tmem_ld32(tacc + 32 * j, v);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const int n = 32 * j + i;
-                    if (n < g.fin_n && t < g.Tout) {
-                        const float vel = (__uint_as_float(v[i]) + g.bias[n]) * mk;
-                        const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
-                        g.fin_out[o] = g.fin_xin ? __fadd_rn(g.fin_xin[o], __fmul_rn(g.fin_dt, vel)) : vel;
+                    for (int i = 0; i < 32; ++i) {
+                        const int n = 32 * j + i;
+                        if (n < g.fin_n && t < g.Tout) {
+                            const float vel = (__uint_as_float(v[i]) + g.bias[n]) * mk;
+                            const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
+                            g.fin_out[o] = g.fin_xin ? __fadd_rn(g.fin_xin[o], __fmul_rn(g.fin_dt, vel)) : vel;
+                        }
+                    }
+                }
+            } else {
+                // output element offsets of this lane's 8 rows (column part added per chunk); -1 = row beyond Tout
+                int orow[8];                                   // fit 32 bits (B*T*N < 2^31, checked on the host)
+                float mk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int t = trow0 + 4 * i + rsub;
+                    const bool ok = t < g.Tout;
+                    const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
+                    orow[i] = ok ? (int)(r * g.N) : -1;
+                    mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
+                }
+                float4 rv[8];
+                auto load_res = [&](int jj) {                    // residual rows of chunk jj (issued one chunk ahead)
+                    const int n = n0 + 32 * jj + c4;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        rv[i] = (g.res && orow[i] >= 0) ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                };
+                load_res(jhalf);
+                for (int j = jhalf; j < jhalf + 4; ++j) {
+                    uint32_t v[32];
+                    tmem_ld32(tacc + 32 * j, v);
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        *reinterpret_cast<float4 *>(tb + lane * kGEpiPitch + 4 * i) =
+                            make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                    __syncwarp();
+                    const int n = n0 + 32 * j + c4;
+                    float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
+                    float4 x[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
+                        x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
+                        if (EPI == 1) { x[i].x = gelu_erf_f(x[i].x); x[i].y = gelu_erf_f(x[i].y); x[i].z = gelu_erf_f(x[i].z); x[i].w = gelu_erf_f(x[i].w); }
+                        x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w;
+                    }
+                    if (j + 1 < jhalf + 4) load_res(j + 1);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        if (orow[i] >= 0) {
+                            if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x[i];
+                            if (g.out_bf16)
+                                *reinterpret_cast<uint2 *>(g.out_bf16 + orow[i] + n) =
+                                    make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], g.f16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], g.f16));
+                        }
                     }
                 }
             }
-        } else {
-        // output element offsets of this lane's 8 rows (column part added per chunk); -1 = row beyond Tout
-        int orow[8];                                   // element offsets fit 32 bits (B*T*N < 2^31, checked on the host)
-        float mk[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int t = trow0 + 4 * i + rsub;
-            const bool ok = t < g.Tout;
-            const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
-            orow[i] = ok ? (int)(r * g.N) : -1;
-            mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
-        }
-        float4 rv[8];
-        auto load_res = [&](int jj) {                    // residual rows of chunk jj (issued one chunk ahead)
-            const int n = n0 + 32 * jj + c4;
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                rv[i] = (g.res && orow[i] >= 0) ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
-        };
-        load_res(0);
-        for (int j = 0; j < kGN / 32; ++j) {
-            uint32_t v[32];
-            tmem_ld32(tmem_d + ((uint32_t)(32 * q) << 16) + 32 * j, v);
-            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[4] = clock64();
+            // this warp's TMEM reads are complete (tcgen05.wait::ld): hand the accumulator back to the MMA warp
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                *reinterpret_cast<float4 *>(tb + lane * kGEpiPitch + 4 * i) =
-                    make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
-            __syncwarp();
-            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[5] = clock64();
-            const int n = n0 + 32 * j + c4;
-            float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
-            float4 x[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
-                x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
-                if (EPI == 1) { x[i].x = gelu_erf_f(x[i].x); x[i].y = gelu_erf_f(x[i].y); x[i].z = gelu_erf_f(x[i].z); x[i].w = gelu_erf_f(x[i].w); }
-                x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w;
-            }
-            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[6] = clock64();
-            if (j + 1 < kGN / 32) load_res(j + 1);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                if (orow[i] >= 0) {
-                    if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x[i];
-                    if (g.out_bf16)
-                        *reinterpret_cast<uint2 *>(g.out_bf16 + orow[i] + n) =
-                            make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], g.f16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], g.f16));
-                }
-            }
-            if (dbg && threadIdx.x == 64 && j == 1) g_gemm_dbg[7] = clock64();
-            if (dbg && threadIdx.x == 64 && j == 0) g_gemm_dbg[3] = clock64();
+            if (lane == 0) mbar_arrive(bar_tempty + 8u * acc);
+            if (dbg && lt == 0 && threadIdx.x == 64) g_gemm_dbg[3] = clock64();
         }
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(kGN) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(512) : "memory");
     }
 }
 
