@@ -139,7 +139,7 @@ static void gn_mish(Ctx &c, const float *h, const float *gamma, const float *bet
     const long long n4 = (long long)c.B * T * (kC / 4);
     int blocks = (int)((n4 + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, c.B, T);
+    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, 0, c.B, T);
     c.launches++;
 }
 static void layernorm(Ctx &c, const float *x, const float *g, const float *b, float *out, int T) {
@@ -288,10 +288,10 @@ static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf1
     const size_t rows = (size_t)c.B * T;
     gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, c.B, T);
+    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, 1, c.B, T);
     gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, c.B, T);
+    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, 1, c.B, T);
     gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
     layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
     bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
@@ -356,7 +356,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         static const int tap0[1] = {0};
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, c.B, T);
+        gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, 1, c.B, T);
         c.launches++;
         c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
         gemm_b(c, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);

@@ -32,6 +32,25 @@ __device__ __forceinline__ float mish_f(float x) {
     const float sp = (x > 20.0f) ? x : log1pf(expf(x));
     return x * tanhf(sp);
 }
+// Same function in closed form: tanh(log(1+e^x)) = (n^2 + 2n) / (n^2 + 2n + 2), n = e^x  (one exp, one divide;
+// no cancellation for either sign of x).  Used on the 16-bit tensor-core path.
+__device__ __forceinline__ float mish_fast_f(float x) {
+    if (x > 20.0f) return x;
+    const float n = __expf(x);
+    const float p = fmaf(n, n, 2.0f * n);
+    return x * __fdividef(p, p + 2.0f);
+}
+// erf-GELU with erf from Abramowitz & Stegun 7.1.26 (|abs error| < 1.5e-7), for the 16-bit path's epilogue
+__device__ __forceinline__ float gelu_erf_fast_f(float x) {
+    const float z = fabsf(x) * 0.70710678118654752440f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float e = 1.0f - poly * t * __expf(-z * z);       // erf(|x|/sqrt2)
+    return 0.5f * x * (1.0f + copysignf(e, x));
+}
 // 16-bit GEMM operands: bf16 (f16 == 0) or IEEE fp16 (f16 == 1); both travel as __nv_bfloat16-typed storage
 __device__ __forceinline__ uint32_t pack16x2(float a, float b, int f16) {
     if (f16) { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t *>(&h); }
@@ -289,7 +308,7 @@ __global__ void __launch_bounds__(256)
 gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, const float *__restrict__ gamma,
                const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
                const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out,
-               __nv_bfloat16 *__restrict__ out_bf16, int f16, int B, int T) {
+               __nv_bfloat16 *__restrict__ out_bf16, int f16, int fast, int B, int T) {
     const size_t n4 = (size_t)B * T * (kC / 4);
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
         const int c = (int)(i % (kC / 4)) * 4;
@@ -300,10 +319,17 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
         const float4 v = *reinterpret_cast<const float4 *>(h + i * 4);
         const float4 ga = *reinterpret_cast<const float4 *>(gamma + c), be = *reinterpret_cast<const float4 *>(beta + c);
         float4 o;
-        o.x = mish_f((v.x - mean) * rstd * ga.x + be.x) * mk;
-        o.y = mish_f((v.y - mean) * rstd * ga.y + be.y) * mk;
-        o.z = mish_f((v.z - mean) * rstd * ga.z + be.z) * mk;
-        o.w = mish_f((v.w - mean) * rstd * ga.w + be.w) * mk;
+        if (fast) {
+            o.x = mish_fast_f((v.x - mean) * rstd * ga.x + be.x) * mk;
+            o.y = mish_fast_f((v.y - mean) * rstd * ga.y + be.y) * mk;
+            o.z = mish_fast_f((v.z - mean) * rstd * ga.z + be.z) * mk;
+            o.w = mish_fast_f((v.w - mean) * rstd * ga.w + be.w) * mk;
+        } else {
+            o.x = mish_f((v.x - mean) * rstd * ga.x + be.x) * mk;
+            o.y = mish_f((v.y - mean) * rstd * ga.y + be.y) * mk;
+            o.z = mish_f((v.z - mean) * rstd * ga.z + be.z) * mk;
+            o.w = mish_f((v.w - mean) * rstd * ga.w + be.w) * mk;
+        }
         if (tb) {
             const float4 tv = *reinterpret_cast<const float4 *>(tb + (size_t)(tb_per_sample ? b : 0) * kC + c);
             o.x += tv.x; o.y += tv.y; o.z += tv.z; o.w += tv.w;

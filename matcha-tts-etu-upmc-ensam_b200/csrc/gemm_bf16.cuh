@@ -203,14 +203,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
                 for (int j = jhalf; j < jhalf + 4 && j * 32 < g.fin_n; ++j) {
                     uint32_t v[32];
+                    float xin[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {              // all loads of the chunk first
+                        const int n = 32 * j + i;
+                        xin[i] = (g.fin_xin && n < g.fin_n && t < g.Tout) ? g.fin_xin[((size_t)b * g.fin_n + n) * g.Tout + t] : 0.f;
+                    }
                     tmem_ld32(tacc + 32 * j, v);
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
                         const int n = 32 * j + i;
                         if (n < g.fin_n && t < g.Tout) {
                             const float vel = (__uint_as_float(v[i]) + g.bias[n]) * mk;
-                            const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
-                            g.fin_out[o] = g.fin_xin ? __fadd_rn(g.fin_xin[o], __fmul_rn(g.fin_dt, vel)) : vel;
+                            g.fin_out[((size_t)b * g.fin_n + n) * g.Tout + t] = g.fin_xin ? __fadd_rn(xin[i], __fmul_rn(g.fin_dt, vel)) : vel;
                         }
                     }
                 }
@@ -251,7 +256,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     for (int i = 0; i < 8; ++i) {
                         x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
                         x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
-                        if (EPI == 1) { x[i].x = gelu_erf_f(x[i].x); x[i].y = gelu_erf_f(x[i].y); x[i].z = gelu_erf_f(x[i].z); x[i].w = gelu_erf_f(x[i].w); }
+                        if (EPI == 1) { x[i].x = gelu_erf_fast_f(x[i].x); x[i].y = gelu_erf_fast_f(x[i].y); x[i].z = gelu_erf_fast_f(x[i].z); x[i].w = gelu_erf_fast_f(x[i].w); }
                         x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w;
                     }
                     if (j + 1 < jhalf + 4) load_res(j + 1);
