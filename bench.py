@@ -143,12 +143,11 @@ def decoder_leg(a, dev, world, rank, dist, barrier):
     import torch
     from types import SimpleNamespace
     from matcha_b200.flow_matching import CFM
-    from oracle import decoder as odec
     B, T, n = a.dec_batch, a.dec_T, a.dec_steps
     params = dict(channels=(256, 256), dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=4)
-    weights = odec.make_weights(0, "init")                     # Decoder.initialize_weights distribution (decoder.py:255)
     cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), params, precision=a.dec_precision)
-    cfm.load_state_dict(weights)
+    cfm.estimator.initialize_weights(seed=0)                   # Decoder.initialize_weights distribution (decoder.py:255)
+    weights = cfm.estimator.state_dict()
     g = torch.Generator(device=dev); g.manual_seed(2000 + rank)
     mu = torch.randn(B, 80, T, device=dev, generator=g)
     z = torch.randn(B, 80, T, device=dev, generator=g)
@@ -213,6 +212,7 @@ def decoder_leg(a, dev, world, rank, dist, barrier):
         res["rel_l2_vs_fp32_mode"] = float(torch.linalg.norm((out - o32).double()) / torch.linalg.norm(o32.double()))
     if world == 1 and not a.no_cpu_baseline:
         # the reference's arithmetic (torch CPU fp32, oracle/decoder.py) on a bounded sample
+        from oracle import decoder as odec                     # the checker, timed as the CPU baseline only
         torch.set_num_threads(os.cpu_count() or 1)
         w = weights
         bs, ns = min(4, B), 2

@@ -112,5 +112,13 @@ __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialization attribute may
+// start while its predecessor in the stream drains; nothing the predecessor wrote may be read (and nothing it
+// reads may be overwritten) before pdl_wait(), which returns once every prerequisite grid has completed and
+// flushed.  Every kernel of the decoder path executes it in every thread, so completion stays transitive.
+// Both are no-ops for a normal launch.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 #endif  // __CUDACC__
 }  // namespace mb200

@@ -9,9 +9,12 @@
 // "b c t <-> b t c" rearranges of decoder.py:298-352 disappear, the channel concats of
 // decoder.py:288,341 and the nearest-neighbour resample of :338-339 become addressing inside the
 // implicit-GEMM loader.
+#include <stdlib.h>
+
 #include <vector>
 
 #include "attention_mma.cuh"
+#include "attention_tc.cuh"
 #include "gemm_bf16.cuh"
 
 namespace mb200 {
@@ -109,6 +112,28 @@ struct Ctx {
     std::vector<TmapEntry> tmaps;   // tensor maps of this call's bf16 tensors
 };
 
+// Every kernel of the path is launched here, with programmatic dependent launch (common.cuh: the kernel's
+// prologue overlaps the tail of its predecessor; all of them call pdl_wait() before touching memory).
+// MB200_PDL=0 falls back to plain stream order.
+static bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("MB200_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v != 0;
+}
+template <typename... KArgs, typename... Args>
+static void launch(Ctx &c, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, Args &&...args) {
+    if (c.err) return;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = c.st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+    if (e != cudaSuccess) { c.err = cuda_fail(e); return; }
+    c.launches++;
+}
+
 static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int c1, bool masked, int ntaps,
                  const int *taps, int stride, int Tin, int Tout, const float *w, const float *bias, int N, int act,
                  const float *res, float *out, int out_T, int out_stride, int out_off) {
@@ -122,8 +147,7 @@ static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int 
     g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off; g.out_bf16 = nullptr; g.omask = nullptr; g.f16 = 0;
     const int M = c.B * Tout;
     dim3 grid((M + kBM - 1) / kBM, N / kBN);
-    gemm_f32_kernel<<<grid, 256, 0, c.st>>>(g);
-    c.launches++;
+    launch(c, gemm_f32_kernel, grid, 256, 0, g);
 }
 static void linear(Ctx &c, const float *a, int K, int T, const float *w, const float *bias, int N, int act,
                    const float *res, float *out) {
@@ -131,21 +155,18 @@ static void linear(Ctx &c, const float *a, int K, int T, const float *w, const f
     gemm(c, a, K, T, nullptr, 0, false, 1, tap0, 1, T, T, w, bias, N, act, res, out, T, 1, 0);
 }
 static void gn_stats(Ctx &c, const float *h, int T) {
-    gn_stats_kernel<<<c.B * kGroups, 256, 0, c.st>>>(h, T, c.ws.stats);
-    c.launches++;
+    launch(c, gn_stats_kernel, c.B * kGroups, 256, 0, h, T, c.ws.stats);
 }
 static void gn_mish(Ctx &c, const float *h, const float *gamma, const float *beta, const float *tb, int per_sample,
                     float *out, int T) {
     const long long n4 = (long long)c.B * T * (kC / 4);
     int blocks = (int)((n4 + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    gn_mish_kernel<<<blocks, 256, 0, c.st>>>(h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, 0, c.B, T);
-    c.launches++;
+    launch(c, gn_mish_kernel, blocks, 256, 0, h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, 0, c.B, T);
 }
 static void layernorm(Ctx &c, const float *x, const float *g, const float *b, float *out, int T) {
     const size_t rows = (size_t)c.B * T;
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(x, g, b, out, nullptr, 0, rows);
-    c.launches++;
+    launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, x, g, b, out, nullptr, 0, rows);
 }
 
 // Resnet1D + BasicTransformerBlock of one U-Net stage (decoder.py:80-86, transformer.py:316-368).
@@ -165,8 +186,7 @@ static void run_stage(Ctx &c, const StageW &s, const float *a0, int c0, int Ta0,
     layernorm(c, w.x1, s.ln1g, s.ln1b, w.ln, T);
     linear(c, w.ln, kC, T, s.wqkv, nullptr, 3 * kC, 0, nullptr, w.qkv);
     dim3 agrid((T + kAttBQ - 1) / kAttBQ, kHeads, c.B);
-    attention_f32_kernel<<<agrid, 128, kAttSmemBytes, c.st>>>(w.qkv, c.mask, c.T, w.att, nullptr, 0, T);
-    c.launches++;
+    launch(c, attention_f32_kernel, agrid, 128, kAttSmemBytes, w.qkv, c.mask, c.T, w.att, nullptr, 0, T);
     linear(c, w.att, kC, T, s.wo, s.bo, kC, 0, w.x1, w.x2);
     layernorm(c, w.x2, s.ln3g, s.ln3b, w.ln, T);
     linear(c, w.ln, kC, T, s.w1, s.b1, 4 * kC, 1, nullptr, w.f1);
@@ -183,8 +203,7 @@ static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu,
     const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
     auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
     dim3 pgrid((T + 31) / 32, kInCh / 32, c.B);
-    pack_input_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, w.x0, c.B, T);
-    c.launches++;
+    launch(c, pack_input_kernel, pgrid, 256, 0, x, mu, w.x0, c.B, T);
     run_stage(c, W.st[0], w.x0, kInCh, T, nullptr, 0, T, tb(0), tb_per_sample, w.s0);
     gemm(c, w.s0, kC, T, nullptr, 0, true, 3, taps3, 2, T, T2, W.st[0].wtail, W.st[0].btail, kC, 0, nullptr, w.d, T2, 1, 0);
     run_stage(c, W.st[1], w.d, kC, T2, nullptr, 0, T2, tb(1), tb_per_sample, w.s1);
@@ -199,8 +218,7 @@ static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu,
     gemm(c, w.d, kC, T, nullptr, 0, true, 3, taps3, 1, T, T, W.wf, W.bf, kC, 0, nullptr, w.h, T, 1, 0);
     gn_stats(c, w.h, T);
     dim3 fgrid((T + 31) / 32, c.B);
-    final_proj_kernel<<<fgrid, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, W.wp, W.bp, x_in, dt, out, T);
-    c.launches++;
+    launch(c, final_proj_kernel, fgrid, 256, 0, w.h, w.stats, W.gf, W.bef, c.mask, W.wp, W.bp, x_in, dt, out, T);
 }
 
 
@@ -247,6 +265,34 @@ static bool tmap_for(Ctx &c, const bf16 *base, int ndim, uint64_t d0, uint64_t d
     return true;
 }
 
+// The epilogue variants that exist (gemm_bf16.cuh: everything about the outputs is a template parameter).
+typedef void (*GemmKernel)(CUtensorMap, CUtensorMap, CUtensorMap, GemmBf16Args);
+template <int EPI, int FLAGS>
+static GemmKernel gemm_variant(bool f16) { return f16 ? (GemmKernel)gemm_bf16_kernel<EPI, FLAGS, true> : (GemmKernel)gemm_bf16_kernel<EPI, FLAGS, false>; }
+static GemmKernel pick_gemm(int epi, int flags, bool f16) {
+    switch (epi * 8 + flags) {
+        case 0 * 8 + kGF32: return gemm_variant<0, kGF32>(f16);                          // conv -> GroupNorm input
+        case 0 * 8 + (kGF32 | kGRes): return gemm_variant<0, kGF32 | kGRes>(f16);        // res_conv, attention out-proj
+        case 0 * 8 + kGB16: return gemm_variant<0, kGB16>(f16);                          // q|k|v, down/tail convs
+        case 0 * 8 + (kGB16 | kGRes): return gemm_variant<0, kGB16 | kGRes>(f16);        // FFN2 feeding a conv only
+        case 0 * 8 + (kGF32 | kGB16): return gemm_variant<0, kGF32 | kGB16>(f16);
+        case 0 * 8 + (kGF32 | kGB16 | kGRes): return gemm_variant<0, kGF32 | kGB16 | kGRes>(f16);
+        case 1 * 8 + kGB16: return gemm_variant<1, kGB16>(f16);                          // FFN1 + erf-GELU
+        case 1 * 8 + (kGF32 | kGB16 | kGRes): return gemm_variant<1, kGF32 | kGB16 | kGRes>(f16);   // tests only
+        case 2 * 8 + 0: return gemm_variant<2, 0>(f16);                                  // final_proj + Euler update
+    }
+    return nullptr;
+}
+static int gemm_set_attributes() {
+    for (int epi = 0; epi < 3; ++epi)
+        for (int flags = 0; flags < 8; ++flags)
+            for (int f16 = 0; f16 < 2; ++f16) {
+                const GemmKernel k = pick_gemm(epi, flags, f16 != 0);
+                if (k) MB200_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+            }
+    return MB200_OK;
+}
+
 // out = act(A W^T + bias) + res on the tensor cores.  a0/a1: bf16 [B][T][c0|c1] (already x*mask where the
 // reference multiplies), w: bf16 [N][ntaps*(c0+c1)].
 static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
@@ -272,10 +318,34 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     const int grid = (int)(n_tiles < kNumSMsB200 ? n_tiles : kNumSMsB200);      // persistent: one CTA per SM
     g.debug = c.debug;
     if ((long long)c.B * g.out_T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
-    if (g.fin_n > 0) gemm_bf16_kernel<2><<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
-    else if (act == 1) gemm_bf16_kernel<1><<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
-    else gemm_bf16_kernel<0><<<grid, kGThreads, kGSmemBytes, c.st>>>(ma0, ma1, mb, g);
-    c.launches++;
+    const int flags = (res ? kGRes : 0) | (out_f32 ? kGF32 : 0) | (out_b16 ? kGB16 : 0);
+    const GemmKernel k = pick_gemm(g.fin_n > 0 ? 2 : act, g.fin_n > 0 ? 0 : flags, c.f16 != 0);
+    if (!k) { c.err = MB200_ERR_UNSUPPORTED; return; }
+    launch(c, k, grid, kGThreads, kGSmemBytes, ma0, ma1, mb, g);
+}
+
+// softmax(q k^T / 8 + mask) v on 16-bit q|k|v rows: tcgen05 kernel (attention_tc.cuh); MB200_ATTN=mma selects the
+// warp-level mma.sync kernel (attention_mma.cuh), which also serves T beyond the mask table of the former.
+static bool attn_use_tc() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("MB200_ATTN"); v = (e && e[0] == 'm') ? 0 : 1; }
+    return v != 0;
+}
+static void attention_b(Ctx &c, const bf16 *qkvb, bf16 *out, int T) {
+    if (c.err) return;
+    if (attn_use_tc() && T <= kTaMaxT) {
+        CUtensorMap mq;
+        if (!tmap_for(c, qkvb, 3, (uint64_t)(3 * kC), (uint64_t)T, (uint64_t)c.B, kDHead, kTaBQ, &mq)) return;
+        AttnTcArgs a;
+        a.mask = c.mask; a.mask_T = c.T; a.out = out; a.B = c.B; a.T = T;
+        const int grid = ((T + kTaBQ - 1) / kTaBQ) * kHeads * c.B;
+        if (c.f16) launch(c, attention_tc_kernel<true>, grid, kTaThreads, kTaSmemBytes, mq, a);
+        else launch(c, attention_tc_kernel<false>, grid, kTaThreads, kTaSmemBytes, mq, a);
+        return;
+    }
+    dim3 agrid((T + kFaBQ - 1) / kFaBQ, kHeads, c.B);
+    if (c.f16) launch(c, attention_mma_kernel<true>, agrid, 128, kFaSmemBytes, qkvb, c.mask, c.T, out, T);
+    else launch(c, attention_mma_kernel<false>, agrid, 128, kFaSmemBytes, qkvb, c.mask, c.T, out, T);
 }
 
 static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf16 *in0, int c0, const bf16 *in1,
@@ -288,22 +358,19 @@ static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf1
     const size_t rows = (size_t)c.B * T;
     gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, 1, c.B, T);
+    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, 1, c.B, T);
     gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false);
     gn_stats(c, w.h, T);
-    gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, 1, c.B, T);
+    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, 1, c.B, T);
     gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
+    launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
     bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
-    dim3 agrid((T + kFaBQ - 1) / kFaBQ, kHeads, c.B);
-    if (c.f16) attention_mma_kernel<true><<<agrid, 128, kFaSmemBytes, c.st>>>(qkvb, c.mask, c.T, w.attb, T);
-    else attention_mma_kernel<false><<<agrid, 128, kFaSmemBytes, c.st>>>(qkvb, c.mask, c.T, w.attb, T);
+    attention_b(c, qkvb, w.attb, T);
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
-    layernorm_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, c.st>>>(w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
+    launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
     gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
-    c.launches += 5;
 }
 
 static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const float *x, const float *mu,
@@ -316,8 +383,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
     auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
     dim3 pgrid((T + 31) / 32, kInChPad / 32, c.B);
-    pack_input_bf16_kernel<<<pgrid, 256, 0, c.st>>>(x, mu, c.mask, w.x0b, c.f16, c.B, T);
-    c.launches++;
+    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, c.B, T);
     // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
     run_stage_bf16(c, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, (T & 1) ? w.s0 : nullptr, w.s0b);
     if ((T & 1) == 0) {
@@ -330,8 +396,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         g.B = c.B; g.Tin = T; g.Tout = T2; g.w = W.st[0].wtail; g.bias = W.st[0].btail; g.N = kC; g.K = 3 * kC;
         g.act = 0; g.res = nullptr; g.out = nullptr; g.out_T = T2; g.out_stride = 1; g.out_off = 0;
         g.out_bf16 = w.inb; g.omask = c.mask; g.f16 = c.f16;
-        gemm_f32_kernel<<<dim3((c.B * T2 + kBM - 1) / kBM, kC / kBN), 256, 0, c.st>>>(g);
-        c.launches++;
+        launch(c, gemm_f32_kernel, dim3((c.B * T2 + kBM - 1) / kBM, kC / kBN), 256, 0, g);
     }
     run_stage_bf16(c, W.st[1], Wb.st[1], w.inb, kC, nullptr, 0, T2, tb(1), tb_per_sample, nullptr, w.s1b);
     gemm_b(c, w.s1b, kC, nullptr, 0, 3, taps3, T2, Wb.st[1].wtail, kC, W.st[1].btail, 0, nullptr, nullptr, w.inb, true);
@@ -345,8 +410,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     {
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        resample_mask_bf16_kernel<<<eb, 256, 0, c.st>>>(w.d, Tu, c.mask, w.upb, c.f16, c.B, T);
-        c.launches++;
+        launch(c, resample_mask_bf16_kernel, eb, 256, 0, w.d, Tu, c.mask, w.upb, c.f16, c.B, T);
     }
     run_stage_bf16(c, W.st[5], Wb.st[5], w.upb, kC, w.s0b, kC, T, tb(5), tb_per_sample, nullptr, w.inb);
     gemm_b(c, w.inb, kC, nullptr, 0, 3, taps3, T, Wb.st[5].wtail, kC, W.st[5].btail, 0, nullptr, nullptr, w.a1b, true);
@@ -356,8 +420,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         static const int tap0[1] = {0};
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        gn_mish_kernel<<<eb, 256, 0, c.st>>>(w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, 1, c.B, T);
-        c.launches++;
+        launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, 1, c.B, T);
         c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
         gemm_b(c, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
         c.fin_out = nullptr;
@@ -378,6 +441,8 @@ using namespace mb200;
 namespace {
 struct TimeVals { float v[64]; };
 __global__ void stage_times_kernel(TimeVals tv, int n, float *out) {
+    pdl_launch_dependents();
+    pdl_wait();
     if (threadIdx.x < n) out[threadIdx.x] = tv.v[threadIdx.x];
 }
 
@@ -400,9 +465,9 @@ int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16
     static bool attr_set = false;
     if (!attr_set) {
         MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+        { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
+        MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
+        MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
         attr_set = true;
     }
     return MB200_OK;
@@ -463,12 +528,12 @@ extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_d
     Ctx c; DecW W; DecWb Wb;
     rc = prepare(c, W, Wb, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, mask_dev, B, T, n_t, precision, stream);
     if (rc != MB200_OK) return rc;
-    time_embed1_kernel<<<dim3(n_t, 16), 256, 0, c.st>>>(time_weights(W), t_dev, c.ws.th2);
-    time_embed2_kernel<<<dim3(n_t, 24), 256, 0, c.st>>>(time_weights(W), c.ws.th2, n_t, c.ws.tb);
+    launch(c, time_embed1_kernel, dim3(n_t, 16), 256, 0, time_weights(W), t_dev, c.ws.th2);
+    launch(c, time_embed2_kernel, dim3(n_t, 24), 256, 0, time_weights(W), c.ws.th2, n_t, c.ws.tb);
     eval_any(c, W, Wb, precision, x_dev, mu_dev, c.ws.tb, n_t, n_t == B && B > 1 ? 1 : 0, nullptr, 0.f, out_dev);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
-    return c.launches + 2;
+    return c.launches;
 }
 
 extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,
@@ -485,15 +550,15 @@ extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_
     TimeVals tv;
     for (int i = 0; i < n_steps; ++i) tv.v[i] = t_host[i];
     float *t_stage = c.ws.h;          // free until the first conv writes it
-    stage_times_kernel<<<1, 64, 0, c.st>>>(tv, n_steps, t_stage);
-    time_embed1_kernel<<<dim3(n_steps, 16), 256, 0, c.st>>>(time_weights(W), t_stage, c.ws.th2);
-    time_embed2_kernel<<<dim3(n_steps, 24), 256, 0, c.st>>>(time_weights(W), c.ws.th2, n_steps, c.ws.tb);
+    launch(c, stage_times_kernel, 1, 64, 0, tv, n_steps, t_stage);
+    launch(c, time_embed1_kernel, dim3(n_steps, 16), 256, 0, time_weights(W), t_stage, c.ws.th2);
+    launch(c, time_embed2_kernel, dim3(n_steps, 24), 256, 0, time_weights(W), c.ws.th2, n_steps, c.ws.tb);
     for (int k = 0; k < n_steps; ++k)
         eval_any(c, W, Wb, precision, k == 0 ? x0_dev : out_dev, mu_dev, c.ws.tb + (size_t)k * kC, n_steps, 0,
                  k == 0 ? x0_dev : out_dev, dt_host[k], out_dev);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
-    return c.launches + 3;
+    return c.launches;
 }
 
 // test aid, not part of the public header: one tcgen05 implicit GEMM on caller-provided bf16 operands
@@ -503,8 +568,7 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
                                             void *stream) {
     Ctx c;
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0; c.debug = 1;
-    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
-    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
+    { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);
     if (c.err) return c.err;
@@ -514,5 +578,34 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
 
 extern "C" int matcha_b200_debug_gemm_stamps(long long *out8) {
     MB200_CUDA_TRY(cudaMemcpyFromSymbol(out8, mb200::g_gemm_dbg, sizeof(long long) * 8));
+    return MB200_OK;
+}
+
+// test aid, not part of the public header: one self-attention call on caller-provided 16-bit q|k|v rows
+// ([B][T][768]); impl 0 = tcgen05 kernel, 1 = mma.sync kernel.  mask: [B][T] float.
+extern "C" int matcha_b200_debug_attention(const void *qkv16, const float *mask, void *out16, int B, int T, int f16,
+                                            int impl, void *stream) {
+    if (!qkv16 || !mask || !out16 || B < 1 || T < 1) return MB200_ERR_INVALID_ARG;
+    Ctx c;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16;
+    MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
+    const bf16 *qkvb = (const bf16 *)qkv16;
+    if (impl == 0) {
+        if (T > kTaMaxT) return MB200_ERR_UNSUPPORTED;
+        CUtensorMap mq;
+        if (!tmap_for(c, qkvb, 3, (uint64_t)(3 * kC), (uint64_t)T, (uint64_t)B, kDHead, kTaBQ, &mq)) return c.err;
+        AttnTcArgs a;
+        a.mask = mask; a.mask_T = T; a.out = (bf16 *)out16; a.B = B; a.T = T;
+        const int grid = ((T + kTaBQ - 1) / kTaBQ) * kHeads * B;
+        if (f16) launch(c, attention_tc_kernel<true>, grid, kTaThreads, kTaSmemBytes, mq, a);
+        else launch(c, attention_tc_kernel<false>, grid, kTaThreads, kTaSmemBytes, mq, a);
+    } else {
+        dim3 agrid((T + kFaBQ - 1) / kFaBQ, kHeads, B);
+        if (f16) launch(c, attention_mma_kernel<true>, agrid, 128, kFaSmemBytes, qkvb, mask, T, (bf16 *)out16, T);
+        else launch(c, attention_mma_kernel<false>, agrid, 128, kFaSmemBytes, qkvb, mask, T, (bf16 *)out16, T);
+    }
+    if (c.err) return c.err;
+    MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
 }

@@ -40,16 +40,19 @@ __device__ __forceinline__ float mish_fast_f(float x) {
     const float p = fmaf(n, n, 2.0f * n);
     return x * __fdividef(p, p + 2.0f);
 }
-// erf-GELU with erf from Abramowitz & Stegun 7.1.26 (|abs error| < 1.5e-7), for the 16-bit path's epilogue
+// erf-GELU for the 16-bit path's GEMM epilogue, which is issue-bound: 12 FMA-pipe + 2 MUFU instructions.
+// With q = erfc(|x|/sqrt2)/2 from Abramowitz & Stegun 7.1.26 (|abs error| < 0.75e-7):
+//   gelu(x) = x*Phi(x) = max(x, 0) - |x|*q      (x >= 0: x - x*q;  x < 0: x*q)
 __device__ __forceinline__ float gelu_erf_fast_f(float x) {
-    const float z = fabsf(x) * 0.70710678118654752440f;
-    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-    float poly = fmaf(1.061405429f, t, -1.453152027f);
-    poly = fmaf(poly, t, 1.421413741f);
-    poly = fmaf(poly, t, -0.284496736f);
-    poly = fmaf(poly, t, 0.254829592f);
-    const float e = 1.0f - poly * t * __expf(-z * z);       // erf(|x|/sqrt2)
-    return 0.5f * x * (1.0f + copysignf(e, x));
+    const float ax = fabsf(x);
+    float t, ex;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.3275911f * 0.70710678118654752440f, 1.0f)));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex) : "f"(x * x * (-0.5f * 1.4426950408889634f)));   // exp(-x^2/2)
+    float poly = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);
+    poly = fmaf(poly, t, 0.5f * 1.421413741f);
+    poly = fmaf(poly, t, 0.5f * -0.284496736f);
+    poly = fmaf(poly, t, 0.5f * 0.254829592f);
+    return fmaxf(x, 0.0f) - ax * (poly * t * ex);
 }
 // 16-bit GEMM operands: bf16 (f16 == 0) or IEEE fp16 (f16 == 1); both travel as __nv_bfloat16-typed storage
 __device__ __forceinline__ uint32_t pack16x2(float a, float b, int f16) {
@@ -77,6 +80,8 @@ struct TimeWeights {
 // step 1, grid (n_rows, 16): h2[row][o] = Mish(W2 SiLU(W1 emb(t[row]) + b1) + b2)[o] for 64 outputs per block
 __global__ void __launch_bounds__(256)
 time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict__ h2) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float emb[kInCh];
     __shared__ float h1[kTimeDim];
     const int row = blockIdx.x, tid = threadIdx.x;
@@ -107,6 +112,8 @@ time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict
 // step 2, grid (n_rows, 6 stages x 4): out_tb[stage][row][o] = Linear_stage(h2[row])[o], 64 outputs per block
 __global__ void __launch_bounds__(256)
 time_embed2_kernel(TimeWeights w, const float *__restrict__ h2, int n_rows, float *__restrict__ out_tb) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float hs[kTimeDim];
     const int row = blockIdx.x, st = blockIdx.y >> 2, part = blockIdx.y & 3, tid = threadIdx.x;
     for (int i = tid; i < kTimeDim; i += 256) hs[i] = h2[(size_t)row * kTimeDim + i];
@@ -127,6 +134,8 @@ time_embed2_kernel(TimeWeights w, const float *__restrict__ h2, int n_rows, floa
 __global__ void __launch_bounds__(256)
 pack_input_kernel(const float *__restrict__ x, const float *__restrict__ mu, float *__restrict__ out,
                   int B, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float tile[32][33];
     const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 160 channels
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;                  // 32 x 8
@@ -169,6 +178,8 @@ constexpr int kBM = 128, kBN = 64, kBK = 16;
 
 __global__ void __launch_bounds__(256)
 gemm_f32_kernel(const GemmArgs g) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ __align__(16) float As[kBK][kBM + 4];
     __shared__ __align__(16) float Bs[kBK][kBN + 4];
     const int tid = threadIdx.x;
@@ -274,6 +285,8 @@ gemm_f32_kernel(const GemmArgs g) {
 // the statistics run over the full padded T).
 __global__ void __launch_bounds__(256)
 gn_stats_kernel(const float *__restrict__ h, int T, float *__restrict__ stats) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int b = blockIdx.x / kGroups, grp = blockIdx.x % kGroups;
     const float *p = h + (size_t)b * T * kC + grp * kGroupCh;
     double s = 0.0, ss = 0.0;
@@ -309,6 +322,8 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
                const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
                const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out,
                __nv_bfloat16 *__restrict__ out_bf16, int f16, int fast, int B, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     const size_t n4 = (size_t)B * T * (kC / 4);
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
         const int c = (int)(i % (kC / 4)) * 4;
@@ -346,6 +361,8 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta,
                  float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int f16, size_t rows) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -385,6 +402,8 @@ constexpr int kAttSmemBytes = (2 * kAttBK * kAttPitch + kAttBQ * kAttPitch) * 4;
 __global__ void __launch_bounds__(128)
 attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ mask, int mask_T,
                      float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int f16, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ __align__(16) float att_smem[];
     float (*Ks)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem);
     float (*Vs)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem + kAttBK * kAttPitch);
@@ -483,6 +502,8 @@ final_proj_kernel(const float *__restrict__ hf, const float *__restrict__ stats,
                   const float *__restrict__ beta, const float *__restrict__ mask, const float *__restrict__ wp,
                   const float *__restrict__ bp, const float *__restrict__ x_in, float dt,
                   float *__restrict__ out, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float A[32][kC + 1];
     const int b = blockIdx.y, t0 = blockIdx.x * 32, tid = threadIdx.x;
     for (int i = tid; i < 32 * kC; i += 256) {
@@ -519,6 +540,8 @@ constexpr int kInChPad = 192;      // 160 input channels padded to three 64-wide
 __global__ void __launch_bounds__(256)
 pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
                        __nv_bfloat16 *__restrict__ out, int f16, int B, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float tile[32][33];
     const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 192 channels
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -541,6 +564,8 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
 __global__ void __launch_bounds__(256)
 resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__restrict__ mask,
                           __nv_bfloat16 *__restrict__ out, int f16, int B, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     const size_t n4 = (size_t)B * T * (kC / 4);
     const float scale = (float)Tin / (float)T;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {

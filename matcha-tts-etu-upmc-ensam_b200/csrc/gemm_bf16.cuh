@@ -79,7 +79,7 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -89,17 +89,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
           "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
           "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld32_issue(taddr, r); tmem_ld_wait(); }
 
 // profiling aid: clock64 stamps of CTA 0 (start, first stage landed, first accumulator ready, first tile stored)
 __device__ long long g_gemm_dbg[8];
 
-// EPI: 0 plain, 1 erf-GELU, 2 final projection (compile-time so that unused epilogue code costs no issue slots)
-template <int EPI>
+// EPI: 0 plain, 1 erf-GELU, 2 final projection; FLAGS: which of residual / fp32 output / 16-bit output exist;
+// F16: operand format.  All compile-time: the epilogue is issue-bound, a runtime "if (g.res)" costs slots.
+constexpr int kGRes = 1, kGF32 = 2, kGB16 = 4;
+template <int EPI, int FLAGS, bool F16>
 __global__ void __launch_bounds__(kGThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
+    constexpr bool RES = (FLAGS & kGRes) != 0, F32 = (FLAGS & kGF32) != 0, B16 = (FLAGS & kGB16) != 0;
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
@@ -121,6 +125,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         for (int s = 0; s < kGStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
         for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8u * a, 1u); mbar_init(bar_tempty + 8u * a, kGEpiWarps); }
         mbar_fence_init();
+        tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmB);
+        if (g.c1_chunks) tma_prefetch_desc(&tmA1);
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512) : "memory");
@@ -130,14 +136,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot_p;
+    // barriers, TMEM and descriptors are set up while the previous kernel of the stream drains
+    pdl_launch_dependents();
+    pdl_wait();
     const bool dbg = g.debug && blockIdx.x == 0;
     if (dbg && threadIdx.x == 0) g_gemm_dbg[0] = clock64();
 
     if (warp == 0) {
         // ============================ TMA producer ============================
         if (lane == 0) {
-            tma_prefetch_desc(&tmA0); tma_prefetch_desc(&tmB);
-            if (g.c1_chunks) tma_prefetch_desc(&tmA1);
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 const int mt = tile / n_tiles_n, n0 = (tile - mt * n_tiles_n) * kGN;
@@ -157,7 +164,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     } else if (warp == 1) {
         // ============================ MMA issuer ============================
         if (lane == 0) {
-            const uint32_t idesc = g.f16 ? kIdescF16 : kIdescBf16;
+            const uint32_t idesc = F16 ? kIdescF16 : kIdescBf16;
             uint32_t it = 0, lt = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
                 const uint32_t acc = lt & 1;
@@ -229,25 +236,39 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const bool ok = t < g.Tout;
                     const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
                     orow[i] = ok ? (int)(r * g.N) : -1;
-                    mk[i] = (g.omask && ok) ? g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
+                    mk[i] = 1.0f;
+                    if (B16 && g.omask && ok) mk[i] = g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
                 }
                 float4 rv[8];
                 auto load_res = [&](int jj) {                    // residual rows of chunk jj (issued one chunk ahead)
                     const int n = n0 + 32 * jj + c4;
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
-                        rv[i] = (g.res && orow[i] >= 0) ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
                 };
-                load_res(jhalf);
-                for (int j = jhalf; j < jhalf + 4; ++j) {
-                    uint32_t v[32];
-                    tmem_ld32(tacc + 32 * j, v);
+                if (RES) load_res(jhalf);
+                uint32_t v[2][32];                               // TMEM chunk j+1 is in flight while chunk j is processed
+                tmem_ld32_issue(tacc + 32 * jhalf, v[0]);
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    const int j = jhalf + jj;
+                    tmem_ld_wait();
+                    if (jj + 1 < 4) tmem_ld32_issue(tacc + 32 * (j + 1), v[(jj + 1) & 1]);
+                    else {
+                        // every TMEM read of this warp has landed: hand the accumulator back to the MMA warp now
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_tempty + 8u * acc);
+                    }
                     __syncwarp();
+                    if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[4] = clock64();
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
                         *reinterpret_cast<float4 *>(tb + lane * kGEpiPitch + 4 * i) =
-                            make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                            make_float4(__uint_as_float(v[jj & 1][4 * i]), __uint_as_float(v[jj & 1][4 * i + 1]),
+                                        __uint_as_float(v[jj & 1][4 * i + 2]), __uint_as_float(v[jj & 1][4 * i + 3]));
                     __syncwarp();
+                    if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[5] = clock64();
                     const int n = n0 + 32 * j + c4;
                     float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
@@ -257,24 +278,28 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
                         x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
                         if (EPI == 1) { x[i].x = gelu_erf_fast_f(x[i].x); x[i].y = gelu_erf_fast_f(x[i].y); x[i].z = gelu_erf_fast_f(x[i].z); x[i].w = gelu_erf_fast_f(x[i].w); }
-                        x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w;
+                        if (RES) { x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w; }
                     }
-                    if (j + 1 < jhalf + 4) load_res(j + 1);
+                    if (RES && jj + 1 < 4) load_res(j + 1);
+                    if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[6] = clock64();
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         if (orow[i] >= 0) {
-                            if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x[i];
-                            if (g.out_bf16)
+                            if (F32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x[i];
+                            if (B16)
                                 *reinterpret_cast<uint2 *>(g.out_bf16 + orow[i] + n) =
-                                    make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], g.f16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], g.f16));
+                                    make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], F16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], F16));
                         }
                     }
+                    if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[7] = clock64();
                 }
             }
-            // this warp's TMEM reads are complete (tcgen05.wait::ld): hand the accumulator back to the MMA warp
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8u * acc);
+            if (EPI == 2) {
+                // this warp's TMEM reads are complete (tcgen05.wait::ld): hand the accumulator back to the MMA warp
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_tempty + 8u * acc);
+            }
             if (dbg && lt == 0 && threadIdx.x == 64) g_gemm_dbg[3] = clock64();
         }
     }

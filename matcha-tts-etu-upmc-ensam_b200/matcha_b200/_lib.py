@@ -64,6 +64,8 @@ def load_library():
     lib.matcha_b200_cfm_solve_euler.restype = c_int
     lib.matcha_b200_cfm_solve_euler.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                                 c_void_p, c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_debug_attention.restype = c_int
+    lib.matcha_b200_debug_attention.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]
     lib.matcha_b200_debug_gemm_bf16.restype = c_int
     lib.matcha_b200_debug_gemm_bf16.argtypes = [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p,
                                                 c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]

@@ -123,6 +123,32 @@ class Decoder(torch.nn.Module):
         self.use_graph = True
 
     # -- weights ----------------------------------------------------------------------------
+    def initialize_weights(self, seed=0):
+        """Random-init weights with the distribution the reference constructor leaves behind
+        (decoder.py:255-268): Kaiming-normal (fan_in, relu gain) for every Conv1d / Linear weight, zero
+        biases, GroupNorm 1/0; LayerNorm keeps its 1/0 default and the ConvTranspose1d of Upsample1D
+        (decoder.py:112), which initialize_weights does not match, keeps torch's default
+        U(-1/sqrt(fan_in), 1/sqrt(fan_in)) with fan_in = weight.size(1) * k.  CPU generator, so the values
+        depend on `seed` only.  Used by bench.py ("random-init Matcha LJSpeech-size decoder")."""
+        g = torch.Generator().manual_seed(seed)
+        sd = OrderedDict()
+        for name, shape in expected_keys().items():
+            is_norm = ".norm" in name or name.startswith("final_norm") or ".block.1." in name
+            if name.startswith("Upsampling_Blocks.0.2.conv."):
+                bound = 1.0 / math.sqrt(shape[0] * 4 if len(shape) == 1 else shape[1] * shape[2])
+                sd[name] = (torch.rand(shape, generator=g) * 2 - 1) * bound
+            elif name.endswith(".weight") and not is_norm:
+                fan_in = 1
+                for d in shape[1:]:
+                    fan_in *= d
+                sd[name] = torch.randn(shape, generator=g) * math.sqrt(2.0 / fan_in)
+            elif name.endswith(".weight"):
+                sd[name] = torch.ones(shape)
+            else:
+                sd[name] = torch.zeros(shape)
+        self.load_state_dict(sd)
+        return self
+
     def load_state_dict(self, state_dict, strict=True):
         sd = OrderedDict()
         for k, v in state_dict.items():

@@ -49,3 +49,19 @@ def test_no_cpu_fallback():
     x = torch.zeros(1, 80, 8)
     with pytest.raises(RuntimeError):
         m.estimator(x, torch.ones(1, 1, 8), x, torch.tensor(0.5))
+
+
+def test_initialize_weights_distribution():
+    """C14: Kaiming-normal conv/linear weights, zero biases, unit norms; ConvTranspose keeps torch's default."""
+    from matcha_b200.decoder import Decoder, expected_keys
+    d = Decoder().initialize_weights(seed=3)
+    sd = d.state_dict()
+    assert list(sd.keys()) == list(expected_keys().keys())
+    w = sd["Mid_Blocks.0.0.block1.block.0.weight"]                      # [256, 256, 3], fan_in 768
+    assert abs(w.std().item() / (2.0 / 768) ** 0.5 - 1) < 0.02 and abs(w.mean().item()) < 1e-3
+    assert sd["Mid_Blocks.0.0.block1.block.0.bias"].abs().max().item() == 0
+    assert torch.equal(sd["final_norm.weight"], torch.ones(256)) and torch.equal(sd["Mid_Blocks.0.1.0.norm1.bias"], torch.zeros(256))
+    ct = sd["Upsampling_Blocks.0.2.conv.weight"]                        # ConvTranspose1d [256, 256, 4]: U(+-1/32)
+    assert ct.abs().max().item() <= 1 / 32 and ct.abs().max().item() > 0.99 / 32
+    again = Decoder().initialize_weights(seed=3).state_dict()
+    assert all(torch.equal(sd[k], again[k]) for k in sd)

@@ -6,13 +6,12 @@ for p in (ROOT, os.path.join(ROOT, "matcha-tts-etu-upmc-ensam_b200")):
     sys.path.insert(0, p)
 import torch
 from matcha_b200.flow_matching import CFM
-from oracle import decoder as odec
 B, T, n = (int(v) for v in (sys.argv[1:4] if len(sys.argv) > 3 else (32, 800, 10)))
 prec = sys.argv[4] if len(sys.argv) > 4 else "fp32"
 iters = int(sys.argv[5]) if len(sys.argv) > 5 else 3
 cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4),
           dict(channels=(256, 256), dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=4), precision=prec)
-cfm.load_state_dict(odec.make_weights(0, "init"))
+cfm.estimator.initialize_weights(seed=0)
 dev = torch.device("cuda:0")
 g = torch.Generator(device=dev); g.manual_seed(0)
 mu, z = torch.randn(B, 80, T, device=dev, generator=g), torch.randn(B, 80, T, device=dev, generator=g)

@@ -7,8 +7,8 @@ import torch
 from matcha_b200._lib import check, load_library
 lib = load_library()
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-B, T = 32, int(os.environ.get('GB_T', '800'))
-for (c0, taps, N, with_res, with_b16, with_f32) in [(64, [0], 256, 0, 0, 0), (64, [0], 256, 0, 1, 0), (64, [0], 256, 0, 0, 1), (256, [0], 256, 0, 0, 1), (1024, [0], 256, 0, 0, 1), (256, [-1, 0, 1], 256, 0, 0, 1),
+B, T = int(os.environ.get('GB_B', '32')), int(os.environ.get('GB_T', '800'))
+for (c0, taps, N, with_res, with_b16, with_f32) in [(64, [0], 256, 0, 1, 0), (64, [0], 256, 0, 0, 1), (256, [0], 256, 0, 0, 1), (1024, [0], 256, 0, 0, 1), (256, [-1, 0, 1], 256, 0, 0, 1),
                                           (256, [0], 256, 1, 1, 1), (256, [0], 1024, 0, 1, 0), (256, [0], 768, 0, 1, 0), (1024, [0], 256, 1, 1, 1)]:
     a = torch.randn(B, T, c0, device="cuda").bfloat16()
     w = (torch.randn(N, len(taps) * c0, device="cuda") * 0.05).bfloat16()
