@@ -32,7 +32,8 @@ def build(force=False, verbose=False):
     if not force and up_to_date():
         return lib_file()
     os.makedirs(os.path.join(HERE, "lib"), exist_ok=True)
-    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", lib_file()] + sources()
+    extra = os.environ.get("MB200_NVCC_EXTRA", "").split()          # e.g. -DSOME_PROFILING_SWITCH=1
+    cmd = [NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", lib_file()] + sources()
     subprocess.run(cmd, check=True, cwd=HERE)
     return lib_file()
 

@@ -4,31 +4,39 @@
 // key mask; transformer.py:251-259,320-325).  qkv: 16-bit [B][T][768] = [q | k | v], head h at
 // columns h*64; out: 16-bit [B][T][256].
 //
-// One CTA = one (sample, head, 128-query block).  Warp roles:
-//   warp 0      TMA producer: the Q tile once, then (K, V) tiles of 128 keys through a 3-stage ring.  One
-//               3-D tensor map over [B][T][768] serves all three; rows beyond T come back as zeros.
-//   warp 1      MMA issuer: S_j = Q K_j^T (M128 x N128 x K64, fp32 in TMEM, double-buffered) and
-//               O_j = P_j V_j (M128 x N64 x K128; V is consumed MN-major straight from its [key][d] tile).
-//   warps 2..9  softmax: thread = one query row x 64 keys of the block (two warps share a TMEM lane quarter
-//               and split the keys; the row max is exchanged through shared memory).  exp2 in fp32, P written
-//               16-bit into the 128B-swizzled K-major A-operand layout, O_j read back from TMEM and
-//               accumulated in registers with the usual online-softmax rescale, so TMEM is never rewritten.
-// The block is MUFU-bound by design: 128 x 128 exp2 per key block = 1024 cycles, the two MMAs take 512.
+// One CTA = one (sample, head, 128-query block); two CTAs share an SM (256 TMEM columns and ~100 KB of shared
+// memory each), so that one CTA's exp2 phase (MUFU-bound) overlaps the other's logits phase and its
+// prologue.  Full query blocks come first in the grid, the ragged last block of every (sample, head) last.
+// Warp roles:
+//   warp 0      TMA producer: the Q tile once (lane 0), K tiles of 64 keys (lane 0) and V tiles (lane 1)
+//               through two 3-stage rings (a K stage is free as soon as its S is computed, a V stage after its
+//               PV).  Two 3-D tensor maps over [B][T][768] (128-row and 64-row boxes); rows beyond T are zeros.
+//   warp 1      MMA issuer: S_j = Q K_j^T (M128 x N64 x K64, fp32 in TMEM, double-buffered) and
+//               O += P_j V_j (M128 x N64 x K64; V is consumed MN-major straight from its [key][d] tile),
+//               accumulated in TMEM over all key blocks.
+//   warps 2..5  softmax: thread = one query row (TMEM lane).  Logits, max and exp2 in fp32 registers, P written
+//               16-bit into the 128B-swizzled K-major A-operand layout.  The reference point m of
+//               p = exp(z - m) only moves when a block's max exceeds it by more than 8 octaves (p <= 256 is
+//               harmless in 16 bits); then the row sum and the row's O in TMEM are rescaled (rare after the
+//               first block).  Softmax is invariant to m, so the result is the reference's.
+// The kernel is MUFU-bound by design: one exp2 per (query, key) at 16 per clock per SM.
 #pragma once
 #include "gemm_bf16.cuh"
 
 namespace mb200 {
 
-constexpr int kTaBQ = 128, kTaBK = 128, kTaStages = 3;
-constexpr int kTaThreads = 320;
-constexpr int kTaMaxT = 2048;                               // mask-bias table in shared memory
-constexpr int kTaTile = 128 * 128;                          // bytes of one 128-row x 64-halfword tile
-constexpr int kTaOffKV = kTaTile;                           // Q | (K,V) x stages | P x 2 (two 64-key panels each)
-constexpr int kTaOffP = kTaOffKV + kTaStages * 2 * kTaTile;
-constexpr int kTaOffMask = kTaOffP + 2 * 2 * kTaTile;
-constexpr int kTaOffXch = kTaOffMask + kTaMaxT * 4;         // [2][2][128] floats
-constexpr int kTaOffBar = kTaOffXch + 2 * 2 * 128 * 4;
+constexpr int kTaBQ = 128, kTaBK = 64, kTaStages = 3;
+constexpr int kTaThreads = 192;
+constexpr int kTaTileQ = kTaBQ * 128;                       // bytes of a 128-row x 64-halfword tile (Q, P)
+constexpr int kTaTileK = kTaBK * 128;                       // bytes of a 64-key tile (K, V)
+constexpr int kTaOffK = kTaTileQ;                           // Q | K x stages | V x stages | P x 2 | mask slices | barriers
+constexpr int kTaOffV = kTaOffK + kTaStages * kTaTileK;
+constexpr int kTaOffP = kTaOffV + kTaStages * kTaTileK;
+constexpr int kTaOffMk = kTaOffP + 2 * kTaTileQ;            // [4 warps][2][64] floats: the block's key-mask slice
+constexpr int kTaOffBar = kTaOffMk + 4 * 2 * 64 * 4;
 constexpr int kTaSmemBytes = kTaOffBar + 256 + 1024;
+constexpr int kTaTmemCols = 256;                            // S: 2 x 64 columns, O: 64 columns
+constexpr float kTaRescale = 5.545177444f;                  // 8 ln 2
 
 struct AttnTcArgs {
     const float *mask; int mask_T;      // [B][mask_T] 0/1, added to the logits
@@ -48,218 +56,250 @@ __device__ __forceinline__ float ex2_approx(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+          "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+          "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+          "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
+}
 
 template <bool F16>
-__global__ void __launch_bounds__(kTaThreads, 1)
-attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnTcArgs g) {
+__global__ void __launch_bounds__(kTaThreads, 2)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcArgs g) {
     extern __shared__ uint8_t tasm_raw[];
     const uint32_t base = (smem_u32(tasm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = tasm_raw + (base - smem_u32(tasm_raw));
-    float *maskb = reinterpret_cast<float *>(gbase + kTaOffMask);
-    float *xch = reinterpret_cast<float *>(gbase + kTaOffXch);
     const uint32_t bar0 = base + kTaOffBar;
     const uint32_t bar_q = bar0;                             // Q landed
-    const uint32_t bar_kvf = bar0 + 8;                       // [3] K,V landed
-    const uint32_t bar_kve = bar_kvf + 8 * kTaStages;        // [3] stage consumed (tcgen05.commit)
-    const uint32_t bar_sf = bar_kve + 8 * kTaStages;         // [2] S ready
+    const uint32_t bar_kf = bar0 + 8;                        // [3] K landed
+    const uint32_t bar_ke = bar_kf + 8 * kTaStages;          // [3] K stage consumed (S committed)
+    const uint32_t bar_vf = bar_ke + 8 * kTaStages;          // [3] V landed
+    const uint32_t bar_ve = bar_vf + 8 * kTaStages;          // [3] V stage consumed (PV committed)
+    const uint32_t bar_sf = bar_ve + 8 * kTaStages;          // [2] S ready
     const uint32_t bar_se = bar_sf + 16;                     // [2] S read by the softmax warps
     const uint32_t bar_pf = bar_se + 16;                     // [2] P written
-    const uint32_t bar_of = bar_pf + 16;                     // [2] O_j ready
-    const uint32_t bar_oe = bar_of + 16;                     // [2] O_j read
-    const uint32_t tmem_slot = bar_oe + 16;
-    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + kTaOffBar + 8 + 16 * kTaStages + 80);
+    const uint32_t bar_pv = bar_pf + 16;                     // every PV (one phase per key block)
+    const uint32_t tmem_slot = bar_pv + 8;
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + kTaOffBar + 8 + 32 * kTaStages + 56);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int T = g.T;
     // heavy tiles (full query blocks) first, the ragged last block of every (b, h) at the end of the grid
     const int n_full = T / kTaBQ, heavy = n_full * kHeads * g.B;
     int qb, bh;
-    if ((int)blockIdx.x < heavy) { qb = blockIdx.x % n_full; bh = blockIdx.x / n_full; }
+    if ((int)blockIdx.x < heavy) { bh = blockIdx.x / n_full; qb = blockIdx.x - bh * n_full; }
     else { qb = n_full; bh = blockIdx.x - heavy; }
     const int b = bh / kHeads, h = bh - b * kHeads, q0 = qb * kTaBQ;
     const int n_blk = (T + kTaBK - 1) / kTaBK;
     const int rows_valid = T - q0 < kTaBQ ? T - q0 : kTaBQ;
-    const uint32_t n_sm_warps = 2u * (uint32_t)((rows_valid + 31) / 32);     // softmax warps that have rows
+    const uint32_t n_sm_warps = (uint32_t)((rows_valid + 31) / 32);          // softmax warps that have rows
 
     if (threadIdx.x == 0) {
-        mbar_init(bar_q, 1u);
-        for (int s = 0; s < kTaStages; ++s) { mbar_init(bar_kvf + 8u * s, 1u); mbar_init(bar_kve + 8u * s, 1u); }
+        mbar_init(bar_q, 1u); mbar_init(bar_pv, 1u);
+        for (int s = 0; s < kTaStages; ++s) {
+            mbar_init(bar_kf + 8u * s, 1u); mbar_init(bar_ke + 8u * s, 1u);
+            mbar_init(bar_vf + 8u * s, 1u); mbar_init(bar_ve + 8u * s, 1u);
+        }
         for (int a = 0; a < 2; ++a) {
-            mbar_init(bar_sf + 8u * a, 1u); mbar_init(bar_se + 8u * a, n_sm_warps);
-            mbar_init(bar_pf + 8u * a, n_sm_warps);
-            mbar_init(bar_of + 8u * a, 1u); mbar_init(bar_oe + 8u * a, n_sm_warps);
+            mbar_init(bar_sf + 8u * a, 1u); mbar_init(bar_se + 8u * a, n_sm_warps); mbar_init(bar_pf + 8u * a, n_sm_warps);
         }
         mbar_fence_init();
-        tma_prefetch_desc(&tmQKV);
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV);
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(kTaTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    pdl_launch_dependents();
-    pdl_wait();
-    // additive key mask in the exp2 domain; keys beyond T never win the max and contribute exp2(-inf) = 0
-    for (int k = threadIdx.x; k < n_blk * kTaBK; k += kTaThreads)
-        maskb[k] = k < T ? g.mask[(size_t)b * g.mask_T + k] * 1.4426950408889634f : -INFINITY;
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot_p;
-    const uint32_t tmem_s = tmem, tmem_o = tmem + 256;       // S: 2 x 128 columns, O: 2 x 64 columns
+    const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         // ============================ TMA producer ============================
         if (lane == 0) {
-            mbar_arrive_expect_tx(bar_q, kTaTile);
-            tma_load_3d(base, &tmQKV, bar_q, h * kDHead, q0, b);
+            mbar_arrive_expect_tx(bar_q, kTaTileQ);
+            tma_load_3d(base, &tmQ, bar_q, h * kDHead, q0, b);
             for (int j = 0; j < n_blk; ++j) {
                 const uint32_t s = j % kTaStages;
-                mbar_wait_parked(bar_kve + 8u * s, ((j / kTaStages) & 1) ^ 1, 1000);
-                const uint32_t sk = base + kTaOffKV + s * 2 * kTaTile, sv = sk + kTaTile;
-                mbar_arrive_expect_tx(bar_kvf + 8u * s, 2 * kTaTile);
-                tma_load_3d(sk, &tmQKV, bar_kvf + 8u * s, kC + h * kDHead, j * kTaBK, b);
-                tma_load_3d(sv, &tmQKV, bar_kvf + 8u * s, 2 * kC + h * kDHead, j * kTaBK, b);
+                mbar_wait_parked(bar_ke + 8u * s, ((j / kTaStages) & 1) ^ 1, 500);
+                mbar_arrive_expect_tx(bar_kf + 8u * s, kTaTileK);
+                tma_load_3d(base + kTaOffK + s * kTaTileK, &tmKV, bar_kf + 8u * s, kC + h * kDHead, j * kTaBK, b);
+            }
+        } else if (lane == 1) {
+            for (int j = 0; j < n_blk; ++j) {
+                const uint32_t s = j % kTaStages;
+                mbar_wait_parked(bar_ve + 8u * s, ((j / kTaStages) & 1) ^ 1, 500);
+                mbar_arrive_expect_tx(bar_vf + 8u * s, kTaTileK);
+                tma_load_3d(base + kTaOffV + s * kTaTileK, &tmKV, bar_vf + 8u * s, 2 * kC + h * kDHead, j * kTaBK, b);
             }
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ============================
         if (lane == 0) {
-            auto issue_pv = [&](int i) {
+            const uint32_t idesc_pv = ta_idesc(F16, kDHead, true);
+            auto issue_pv = [&](int i) {                    // O += P_i V_i, issued one block late (after S_{i+1})
                 const int kcnt = T - i * kTaBK < kTaBK ? T - i * kTaBK : kTaBK, n16 = (kcnt + 15) & ~15;
                 const uint32_t a = i & 1, s = i % kTaStages;
-                mbar_wait_parked(bar_pf + 8u * a, (i >> 1) & 1, 1000);
-                mbar_wait_parked(bar_oe + 8u * a, ((i >> 1) & 1) ^ 1, 1000);
+                mbar_wait_parked(bar_vf + 8u * s, (i / kTaStages) & 1, 500);
+                mbar_wait_parked(bar_pf + 8u * a, (i >> 1) & 1, 200);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint64_t dp = umma_desc_sw128(base + kTaOffP + a * 2 * kTaTile);
-                const uint64_t dv = umma_desc_sw128(base + kTaOffKV + s * 2 * kTaTile + kTaTile);
-                const uint32_t idesc = ta_idesc(F16, kDHead, true);
-                for (int ks = 0; ks < n16 / 16; ++ks)      // 16 keys per step: P panel ks/4 (+32 B per step), V +2048 B
-                    umma_bf16(tmem_o + a * 64, dp + (uint64_t)((ks >> 2) * (kTaTile >> 4) + (ks & 3) * 2),
-                              dv + (uint64_t)(ks * 128), idesc, ks != 0 ? 1u : 0u);
-                umma_commit(bar_of + 8u * a);
-                umma_commit(bar_kve + 8u * s);              // K_i and V_i are no longer needed
+                const uint64_t dp = umma_desc_sw128(base + kTaOffP + a * kTaTileQ);
+                const uint64_t dv = umma_desc_sw128(base + kTaOffV + s * kTaTileK);
+                for (int ks = 0; ks < n16 / 16; ++ks)      // 16 keys per step: P +32 B along its row, V +2048 B
+                    umma_bf16(tmem_o, dp + (uint64_t)(2 * ks), dv + (uint64_t)(128 * ks), idesc_pv, (i | ks) != 0 ? 1u : 0u);
+                umma_commit(bar_pv);
+                umma_commit(bar_ve + 8u * s);
             };
-            mbar_wait_parked(bar_q, 0, 1000);
+            mbar_wait_parked(bar_q, 0, 500);
             const uint64_t dq = umma_desc_sw128(base);
             for (int j = 0; j < n_blk; ++j) {
                 const int kcnt = T - j * kTaBK < kTaBK ? T - j * kTaBK : kTaBK, n16 = (kcnt + 15) & ~15;
                 const uint32_t a = j & 1, s = j % kTaStages;
-                mbar_wait_parked(bar_kvf + 8u * s, (j / kTaStages) & 1, 1000);
-                mbar_wait_parked(bar_se + 8u * a, ((j >> 1) & 1) ^ 1, 1000);
+                mbar_wait_parked(bar_kf + 8u * s, (j / kTaStages) & 1, 500);
+                mbar_wait_parked(bar_se + 8u * a, ((j >> 1) & 1) ^ 1, 200);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint64_t dk = umma_desc_sw128(base + kTaOffKV + s * 2 * kTaTile);
+                const uint64_t dk = umma_desc_sw128(base + kTaOffK + s * kTaTileK);
                 const uint32_t idesc = ta_idesc(F16, n16, false);
 #pragma unroll
                 for (int k = 0; k < kDHead / 16; ++k)
-                    umma_bf16(tmem_s + a * 128, dq + 2u * k, dk + 2u * k, idesc, k != 0 ? 1u : 0u);
+                    umma_bf16(tmem_s + a * 64, dq + 2u * k, dk + 2u * k, idesc, k != 0 ? 1u : 0u);
                 umma_commit(bar_sf + 8u * a);
+                umma_commit(bar_ke + 8u * s);
                 if (j > 0) issue_pv(j - 1);
             }
             issue_pv(n_blk - 1);
         }
     } else {
         // ============================ softmax ============================
-        const int q = warp & 3, hf = (warp - 2) >> 2;        // TMEM lane quarter, key half of the block
+        const int q = warp & 3;                              // TMEM lane quarter of this warp
         const int row = 32 * q + lane;
         if (32 * q < rows_valid) {
             const uint32_t lane_off = (uint32_t)(32 * q) << 16;
-            const float c = 0.125f * 1.4426950408889634f;     // scale = dim_head^-0.5 (diffusers Attention), log2 e
-            float m_run = -INFINITY, l_run = 0.f;
-            float o[32];
-#pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = 0.f;
+            const float kLog2e = 1.4426950408889634f;
+            float *mk = reinterpret_cast<float *>(gbase + kTaOffMk) + (warp - 2) * 128;
+            const float *mrow = g.mask + (size_t)b * g.mask_T;
+            float m_ref = -INFINITY, l_run = 0.f;             // p = exp(z - m_ref); l_run = sum of p so far
+            // this warp's copy of the next block's 64 mask values travels global -> registers (one block ahead) -> shared
+            float mk0 = lane < T ? __ldg(mrow + lane) : 0.f;
+            float mk1 = 32 + lane < T ? __ldg(mrow + 32 + lane) : 0.f;
             for (int j = 0; j < n_blk; ++j) {
                 const uint32_t a = j & 1;
-                const int kvalid = T - j * kTaBK - 64 * hf;    // keys of this thread's half that exist
-                float t[64];
-                mbar_wait_parked(bar_sf + 8u * a, (j >> 1) & 1, 200);
+                const int k0 = j * kTaBK;
+                const int kvalid = T - k0;                     // keys of this block that exist
+                float *mkb = mk + a * 64;
+                mkb[lane] = mk0; mkb[32 + lane] = mk1;
+                __syncwarp();
+                if (j + 1 < n_blk) {
+                    mk0 = k0 + kTaBK + lane < T ? __ldg(mrow + k0 + kTaBK + lane) : 0.f;
+                    mk1 = k0 + kTaBK + 32 + lane < T ? __ldg(mrow + k0 + kTaBK + 32 + lane) : 0.f;
+                }
+                // the mask slice goes to registers before the wait on S, so that its latency is off the critical path
+                float z[64];                                   // mask, then logits q.k/8 + mask (natural-log domain)
+                {
+                    const float4 *mk4 = reinterpret_cast<const float4 *>(mkb);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float4 m = mk4[i];
+                        z[4 * i] = m.x; z[4 * i + 1] = m.y; z[4 * i + 2] = m.z; z[4 * i + 3] = m.w;
+                    }
+                }
+                mbar_wait_parked(bar_sf + 8u * a, (j >> 1) & 1, 100);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 {
                     uint32_t v0[32], v1[32];
-                    tmem_ld32_issue(tmem_s + a * 128 + 64 * hf + lane_off, v0);
-                    tmem_ld32_issue(tmem_s + a * 128 + 64 * hf + 32 + lane_off, v1);
+                    tmem_ld32_issue(tmem_s + a * 64 + lane_off, v0);
+                    tmem_ld32_issue(tmem_s + a * 64 + 32 + lane_off, v1);
                     tmem_ld_wait();
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar_se + 8u * a);
-                    const float4 *mb4 = reinterpret_cast<const float4 *>(maskb + j * kTaBK + 64 * hf);
                     if (kvalid >= 64) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const float4 m0 = mb4[i], m1 = mb4[8 + i];
-                            t[4 * i] = fmaf(__uint_as_float(v0[4 * i]), c, m0.x); t[4 * i + 1] = fmaf(__uint_as_float(v0[4 * i + 1]), c, m0.y);
-                            t[4 * i + 2] = fmaf(__uint_as_float(v0[4 * i + 2]), c, m0.z); t[4 * i + 3] = fmaf(__uint_as_float(v0[4 * i + 3]), c, m0.w);
-                            t[32 + 4 * i] = fmaf(__uint_as_float(v1[4 * i]), c, m1.x); t[32 + 4 * i + 1] = fmaf(__uint_as_float(v1[4 * i + 1]), c, m1.y);
-                            t[32 + 4 * i + 2] = fmaf(__uint_as_float(v1[4 * i + 2]), c, m1.z); t[32 + 4 * i + 3] = fmaf(__uint_as_float(v1[4 * i + 3]), c, m1.w);
+                        for (int i = 0; i < 32; ++i) {
+                            z[i] = fmaf(__uint_as_float(v0[i]), 0.125f, z[i]);
+                            z[32 + i] = fmaf(__uint_as_float(v1[i]), 0.125f, z[32 + i]);
                         }
                     } else {                                  // ragged last block: stale TMEM columns must not leak in
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
-                            t[i] = i < kvalid ? fmaf(__uint_as_float(v0[i]), c, maskb[j * kTaBK + 64 * hf + i]) : -INFINITY;
-                            t[32 + i] = 32 + i < kvalid ? fmaf(__uint_as_float(v1[i]), c, maskb[j * kTaBK + 64 * hf + 32 + i]) : -INFINITY;
+                            z[i] = i < kvalid ? fmaf(__uint_as_float(v0[i]), 0.125f, z[i]) : -INFINITY;
+                            z[32 + i] = 32 + i < kvalid ? fmaf(__uint_as_float(v1[i]), 0.125f, z[32 + i]) : -INFINITY;
                         }
                     }
                 }
-                float mloc = -INFINITY;
+                float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-                for (int i = 0; i < 64; ++i) mloc = fmaxf(mloc, t[i]);
-                xch[(a * 2 + hf) * 128 + row] = mloc;
-                named_bar_sync(1 + q, 64);
-                const float m_new = fmaxf(m_run, fmaxf(mloc, xch[(a * 2 + (hf ^ 1)) * 128 + row]));
-                const float alpha = ex2_approx(m_run - m_new);            // 0 on the first block
-                m_run = m_new;
-                // P = exp2(t - m) as 16-bit, row `row`, keys 64*hf.. of buffer a: K-major, 128B swizzle
-                float lsum = 0.f;
-                const uint32_t prow = base + kTaOffP + a * 2 * kTaTile + hf * kTaTile + row * 128;
+                for (int i = 0; i < 16; ++i) {
+                    mx[0] = fmaxf(mx[0], z[4 * i]); mx[1] = fmaxf(mx[1], z[4 * i + 1]);
+                    mx[2] = fmaxf(mx[2], z[4 * i + 2]); mx[3] = fmaxf(mx[3], z[4 * i + 3]);
+                }
+                const float m_blk = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+                // move the reference point only when this block would overflow the 8-octave headroom
+                const bool move = m_blk > m_ref + kTaRescale;          // always true on the first block (m_ref = -inf)
+                if (__any_sync(0xffffffffu, move)) {
+                    const float alpha = move ? ex2_approx((m_ref - m_blk) * kLog2e) : 1.0f;   // 0 on the first block
+                    if (move) m_ref = m_blk;
+                    l_run *= alpha;
+                    if (j > 0) {
+                        // O_row *= alpha in TMEM: every PV issued so far has finished (PV_{j-1} is phase j-1 of bar_pv),
+                        // and PV_j cannot start before this warp has arrived on bar_pf below
+                        mbar_wait_parked(bar_pv, (j - 1) & 1, 100);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                        for (int hcol = 0; hcol < 2; ++hcol) {
+                            uint32_t ov[32];
+                            tmem_ld32(tmem_o + 32 * hcol + lane_off, ov);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+                            tmem_st32(tmem_o + 32 * hcol + lane_off, ov);
+                        }
+                        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                    }
+                }
+                // P = exp(z - m_ref) as 16-bit, row `row` of buffer a: K-major, 128B swizzle
+                const float nm = -m_ref * kLog2e;
+                float ls[4] = {0.f, 0.f, 0.f, 0.f};
+                const uint32_t prow = base + kTaOffP + a * kTaTileQ + row * 128;
 #pragma unroll
                 for (int ch = 0; ch < 8; ++ch) {
                     float p[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) { p[i] = ex2_approx(t[8 * ch + i] - m_new); lsum += p[i]; }
+                    for (int i = 0; i < 8; ++i) { p[i] = ex2_approx(fmaf(z[8 * ch + i], kLog2e, nm)); ls[i & 3] += p[i]; }
                     const uint32_t dst = prow + ((ch ^ (row & 7)) << 4);
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pack16x2(p[0], p[1], F16)),
                                  "r"(pack16x2(p[2], p[3], F16)), "r"(pack16x2(p[4], p[5], F16)), "r"(pack16x2(p[6], p[7], F16)) : "memory");
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_pf + 8u * a);
-                l_run = l_run * alpha + lsum;
-                // O_{j-1} (scaled to the previous max) joins the running sum, then both move to the new max
-                if (j > 0) {
-                    const uint32_t pa = (j - 1) & 1;
-                    uint32_t ov[32];
-                    mbar_wait_parked(bar_of + 8u * pa, ((j - 1) >> 1) & 1, 200);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    tmem_ld32(tmem_o + pa * 64 + 32 * hf + lane_off, ov);
-                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_oe + 8u * pa);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) o[i] = (o[i] + __uint_as_float(ov[i])) * alpha;
-                }
+                l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
             }
-            {
-                const uint32_t pa = (n_blk - 1) & 1;
+            // O is complete when the last PV (phase n_blk-1 of bar_pv) has been committed
+            mbar_wait_parked(bar_pv, (n_blk - 1) & 1, 100);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const float inv = 1.0f / l_run;
+#pragma unroll
+            for (int hcol = 0; hcol < 2; ++hcol) {
                 uint32_t ov[32];
-                mbar_wait_parked(bar_of + 8u * pa, ((n_blk - 1) >> 1) & 1, 200);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                tmem_ld32(tmem_o + pa * 64 + 32 * hf + lane_off, ov);
-                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                tmem_ld32(tmem_o + 32 * hcol + lane_off, ov);
+                if (q0 + row < T) {
+                    uint4 *po = reinterpret_cast<uint4 *>(g.out + ((size_t)b * T + q0 + row) * kC + h * kDHead + 32 * hcol);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] += __uint_as_float(ov[i]);
-            }
-            // row sum: both halves used the same running max, so the partial sums simply add
-            const uint32_t xa = n_blk & 1;
-            xch[(xa * 2 + hf) * 128 + row] = l_run;
-            named_bar_sync(1 + q, 64);
-            const float inv = 1.0f / (l_run + xch[(xa * 2 + (hf ^ 1)) * 128 + row]);
-            if (q0 + row < T) {
-                uint4 *po = reinterpret_cast<uint4 *>(g.out + ((size_t)b * T + q0 + row) * kC + h * kDHead + 32 * hf);
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    po[i] = make_uint4(pack16x2(o[8 * i] * inv, o[8 * i + 1] * inv, F16), pack16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv, F16),
-                                       pack16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv, F16), pack16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv, F16));
+                    for (int i = 0; i < 4; ++i)
+                        po[i] = make_uint4(pack16x2(__uint_as_float(ov[8 * i]) * inv, __uint_as_float(ov[8 * i + 1]) * inv, F16),
+                                           pack16x2(__uint_as_float(ov[8 * i + 2]) * inv, __uint_as_float(ov[8 * i + 3]) * inv, F16),
+                                           pack16x2(__uint_as_float(ov[8 * i + 4]) * inv, __uint_as_float(ov[8 * i + 5]) * inv, F16),
+                                           pack16x2(__uint_as_float(ov[8 * i + 6]) * inv, __uint_as_float(ov[8 * i + 7]) * inv, F16));
+                }
             }
         }
     }
@@ -267,7 +307,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnTcArgs 
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTaTmemCols) : "memory");
     }
 }
 

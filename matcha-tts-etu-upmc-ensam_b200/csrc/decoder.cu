@@ -98,7 +98,7 @@ static long long carve_workspace(float *base, int B, int T, int n_rows, int prec
 }
 
 // ---------------------------------------------------------------- launch helpers
-struct TmapEntry { const void *base; uint64_t d0, d1; CUtensorMap map; };
+struct TmapEntry { const void *base; uint64_t d0, d1; uint32_t b1; CUtensorMap map; };
 struct Ctx {
     cudaStream_t st;
     const float *mask;   // [B][T] float 0/1, pitch T at every U-Net level (prefix truncation)
@@ -252,9 +252,9 @@ static long long build_weights_bf16(const bf16 *blob, DecWb *w) {
 static bool tmap_for(Ctx &c, const bf16 *base, int ndim, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t b0,
                      uint32_t b1, CUtensorMap *out) {
     for (auto &e : c.tmaps)
-        if (e.base == base && e.d0 == d0 && e.d1 == d1) { *out = e.map; return true; }
+        if (e.base == base && e.d0 == d0 && e.d1 == d1 && e.b1 == b1) { *out = e.map; return true; }
     TmapEntry e;
-    e.base = base; e.d0 = d0; e.d1 = d1;
+    e.base = base; e.d0 = d0; e.d1 = d1; e.b1 = b1;
     const uint64_t dims[3] = {d0, d1, d2};
     const uint64_t strides[2] = {d0 * 2, d0 * d1 * 2};
     const uint32_t box[3] = {b0, b1, 1};
@@ -325,7 +325,7 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
 }
 
 // softmax(q k^T / 8 + mask) v on 16-bit q|k|v rows: tcgen05 kernel (attention_tc.cuh); MB200_ATTN=mma selects the
-// warp-level mma.sync kernel (attention_mma.cuh), which also serves T beyond the mask table of the former.
+// warp-level mma.sync kernel (attention_mma.cuh).
 static bool attn_use_tc() {
     static int v = -1;
     if (v < 0) { const char *e = getenv("MB200_ATTN"); v = (e && e[0] == 'm') ? 0 : 1; }
@@ -333,14 +333,15 @@ static bool attn_use_tc() {
 }
 static void attention_b(Ctx &c, const bf16 *qkvb, bf16 *out, int T) {
     if (c.err) return;
-    if (attn_use_tc() && T <= kTaMaxT) {
-        CUtensorMap mq;
+    if (attn_use_tc()) {
+        CUtensorMap mq, mkv;
         if (!tmap_for(c, qkvb, 3, (uint64_t)(3 * kC), (uint64_t)T, (uint64_t)c.B, kDHead, kTaBQ, &mq)) return;
+        if (!tmap_for(c, qkvb, 3, (uint64_t)(3 * kC), (uint64_t)T, (uint64_t)c.B, kDHead, kTaBK, &mkv)) return;
         AttnTcArgs a;
         a.mask = c.mask; a.mask_T = c.T; a.out = out; a.B = c.B; a.T = T;
         const int grid = ((T + kTaBQ - 1) / kTaBQ) * kHeads * c.B;
-        if (c.f16) launch(c, attention_tc_kernel<true>, grid, kTaThreads, kTaSmemBytes, mq, a);
-        else launch(c, attention_tc_kernel<false>, grid, kTaThreads, kTaSmemBytes, mq, a);
+        if (c.f16) launch(c, attention_tc_kernel<true>, grid, kTaThreads, kTaSmemBytes, mq, mkv, a);
+        else launch(c, attention_tc_kernel<false>, grid, kTaThreads, kTaSmemBytes, mq, mkv, a);
         return;
     }
     dim3 agrid((T + kFaBQ - 1) / kFaBQ, kHeads, c.B);
@@ -592,14 +593,14 @@ extern "C" int matcha_b200_debug_attention(const void *qkv16, const float *mask,
     MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
     const bf16 *qkvb = (const bf16 *)qkv16;
     if (impl == 0) {
-        if (T > kTaMaxT) return MB200_ERR_UNSUPPORTED;
-        CUtensorMap mq;
+        CUtensorMap mq, mkv;
         if (!tmap_for(c, qkvb, 3, (uint64_t)(3 * kC), (uint64_t)T, (uint64_t)B, kDHead, kTaBQ, &mq)) return c.err;
+        if (!tmap_for(c, qkvb, 3, (uint64_t)(3 * kC), (uint64_t)T, (uint64_t)B, kDHead, kTaBK, &mkv)) return c.err;
         AttnTcArgs a;
         a.mask = mask; a.mask_T = T; a.out = (bf16 *)out16; a.B = B; a.T = T;
         const int grid = ((T + kTaBQ - 1) / kTaBQ) * kHeads * B;
-        if (f16) launch(c, attention_tc_kernel<true>, grid, kTaThreads, kTaSmemBytes, mq, a);
-        else launch(c, attention_tc_kernel<false>, grid, kTaThreads, kTaSmemBytes, mq, a);
+        if (f16) launch(c, attention_tc_kernel<true>, grid, kTaThreads, kTaSmemBytes, mq, mkv, a);
+        else launch(c, attention_tc_kernel<false>, grid, kTaThreads, kTaSmemBytes, mq, mkv, a);
     } else {
         dim3 agrid((T + kFaBQ - 1) / kFaBQ, kHeads, B);
         if (f16) launch(c, attention_mma_kernel<true>, agrid, 128, kFaSmemBytes, qkvb, mask, T, (bf16 *)out16, T);
