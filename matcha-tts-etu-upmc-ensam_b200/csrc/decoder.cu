@@ -72,7 +72,10 @@ static long long build_weights(const float *blob, DecW *w) {
 struct DecWs {
     float *tb, *th2, *x0, *h, *a, *g, *x1, *ln, *qkv, *att, *x2, *f1, *x3, *s0, *s1, *d, *stats;
     __nv_bfloat16 *x0b, *a1b, *lnb, *attb, *f1b, *inb, *s0b, *s1b, *upb;   // bf16 mode only
+    double *gstats;                                                        // bf16 mode: [13 convs][B][8][2] GroupNorm sums
 };
+
+constexpr int kGnConvs = 13;      // GroupNorm'd convolutions per eval: 2 per Resnet1D + final_conv
 
 static long long carve_workspace(float *base, int B, int T, int n_rows, int precision, DecWs *ws) {
     const long long M = (long long)B * T, Mu = (long long)B * (T + 1);
@@ -87,11 +90,13 @@ static long long carve_workspace(float *base, int B, int T, int n_rows, int prec
     w.s0 = take(M * kC); w.s1 = take(M * kC); w.d = take(Mu * kC);
     w.stats = take((long long)B * kGroups * 2);
     w.x0b = w.a1b = w.lnb = w.attb = w.f1b = w.inb = w.s0b = w.s1b = w.upb = nullptr;
+    w.gstats = nullptr;
     if (precision != MB200_PREC_F32) {
         auto take_h = [&](long long n) { return reinterpret_cast<__nv_bfloat16 *>(take((n + 1) / 2)); };
         w.x0b = take_h(M * kInChPad); w.a1b = take_h(M * kC); w.lnb = take_h(M * kC); w.attb = take_h(M * kC);
         w.f1b = take_h(M * 4 * kC); w.inb = take_h(M * kC); w.s0b = take_h(M * kC); w.s1b = take_h(M * kC);
         w.upb = take_h(M * kC);
+        w.gstats = reinterpret_cast<double *>(take(2LL * kGnConvs * B * kGroups * 2));
     }
     if (ws) *ws = w;
     return off * (long long)sizeof(float);
@@ -162,7 +167,7 @@ static void gn_mish(Ctx &c, const float *h, const float *gamma, const float *bet
     const long long n4 = (long long)c.B * T * (kC / 4);
     int blocks = (int)((n4 + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    launch(c, gn_mish_kernel, blocks, 256, 0, h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, 0, c.B, T);
+    launch(c, gn_mish_kernel, blocks, 256, 0, h, c.ws.stats, gamma, beta, c.mask, c.T, tb, per_sample, out, nullptr, 0, 0, c.B, T, nullptr);
 }
 static void layernorm(Ctx &c, const float *x, const float *g, const float *b, float *out, int T) {
     const size_t rows = (size_t)c.B * T;
@@ -270,22 +275,23 @@ typedef void (*GemmKernel)(CUtensorMap, CUtensorMap, CUtensorMap, GemmBf16Args);
 template <int EPI, int FLAGS>
 static GemmKernel gemm_variant(bool f16) { return f16 ? (GemmKernel)gemm_bf16_kernel<EPI, FLAGS, true> : (GemmKernel)gemm_bf16_kernel<EPI, FLAGS, false>; }
 static GemmKernel pick_gemm(int epi, int flags, bool f16) {
-    switch (epi * 8 + flags) {
-        case 0 * 8 + kGF32: return gemm_variant<0, kGF32>(f16);                          // conv -> GroupNorm input
-        case 0 * 8 + (kGF32 | kGRes): return gemm_variant<0, kGF32 | kGRes>(f16);        // res_conv, attention out-proj
-        case 0 * 8 + kGB16: return gemm_variant<0, kGB16>(f16);                          // q|k|v, down/tail convs
-        case 0 * 8 + (kGB16 | kGRes): return gemm_variant<0, kGB16 | kGRes>(f16);        // FFN2 feeding a conv only
-        case 0 * 8 + (kGF32 | kGB16): return gemm_variant<0, kGF32 | kGB16>(f16);
-        case 0 * 8 + (kGF32 | kGB16 | kGRes): return gemm_variant<0, kGF32 | kGB16 | kGRes>(f16);
-        case 1 * 8 + kGB16: return gemm_variant<1, kGB16>(f16);                          // FFN1 + erf-GELU
-        case 1 * 8 + (kGF32 | kGB16 | kGRes): return gemm_variant<1, kGF32 | kGB16 | kGRes>(f16);   // tests only
-        case 2 * 8 + 0: return gemm_variant<2, 0>(f16);                                  // final_proj + Euler update
+    switch (epi * 16 + flags) {
+        case 0 * 16 + kGF32: return gemm_variant<0, kGF32>(f16);                          // ConvTranspose phases
+        case 0 * 16 + (kGF32 | kGStats): return gemm_variant<0, kGF32 | kGStats>(f16);    // conv -> GroupNorm input + its sums
+        case 0 * 16 + (kGF32 | kGRes): return gemm_variant<0, kGF32 | kGRes>(f16);        // res_conv, attention out-proj
+        case 0 * 16 + kGB16: return gemm_variant<0, kGB16>(f16);                          // q|k|v, down/tail convs
+        case 0 * 16 + (kGB16 | kGRes): return gemm_variant<0, kGB16 | kGRes>(f16);        // FFN2 feeding a conv only
+        case 0 * 16 + (kGF32 | kGB16): return gemm_variant<0, kGF32 | kGB16>(f16);
+        case 0 * 16 + (kGF32 | kGB16 | kGRes): return gemm_variant<0, kGF32 | kGB16 | kGRes>(f16);
+        case 1 * 16 + kGB16: return gemm_variant<1, kGB16>(f16);                          // FFN1 + erf-GELU
+        case 1 * 16 + (kGF32 | kGB16 | kGRes): return gemm_variant<1, kGF32 | kGB16 | kGRes>(f16);   // tests only
+        case 2 * 16 + 0: return gemm_variant<2, 0>(f16);                                  // final_proj + Euler update
     }
     return nullptr;
 }
 static int gemm_set_attributes() {
     for (int epi = 0; epi < 3; ++epi)
-        for (int flags = 0; flags < 8; ++flags)
+        for (int flags = 0; flags < 16; ++flags)
             for (int f16 = 0; f16 < 2; ++f16) {
                 const GemmKernel k = pick_gemm(epi, flags, f16 != 0);
                 if (k) MB200_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
@@ -297,7 +303,7 @@ static int gemm_set_attributes() {
 // reference multiplies), w: bf16 [N][ntaps*(c0+c1)].
 static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
                    const bf16 *w, int N, const float *bias, int act, const float *res, float *out_f32,
-                   bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0) {
+                   bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0, double *gstats = nullptr) {
     if (c.err) return;
     CUtensorMap ma0, ma1, mb;
     if (!tmap_for(c, a0, 3, (uint64_t)c0, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma0)) return;
@@ -318,7 +324,8 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     const int grid = (int)(n_tiles < kNumSMsB200 ? n_tiles : kNumSMsB200);      // persistent: one CTA per SM
     g.debug = c.debug;
     if ((long long)c.B * g.out_T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
-    const int flags = (res ? kGRes : 0) | (out_f32 ? kGF32 : 0) | (out_b16 ? kGB16 : 0);
+    g.gstats = gstats;
+    const int flags = (res ? kGRes : 0) | (out_f32 ? kGF32 : 0) | (out_b16 ? kGB16 : 0) | (gstats ? kGStats : 0);
     const GemmKernel k = pick_gemm(g.fin_n > 0 ? 2 : act, g.fin_n > 0 ? 0 : flags, c.f16 != 0);
     if (!k) { c.err = MB200_ERR_UNSUPPORTED; return; }
     launch(c, k, grid, kGThreads, kGSmemBytes, ma0, ma1, mb, g);
@@ -349,7 +356,7 @@ static void attention_b(Ctx &c, const bf16 *qkvb, bf16 *out, int T) {
     else launch(c, attention_mma_kernel<false>, agrid, 128, kFaSmemBytes, qkvb, c.mask, c.T, out, T);
 }
 
-static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf16 *in0, int c0, const bf16 *in1,
+static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb, const bf16 *in0, int c0, const bf16 *in1,
                            int c1, int T, const float *tb, int tb_per_sample, float *out_f32, bf16 *out_b16) {
     static const int taps3[3] = {-1, 0, 1};
     static const int tap0[1] = {0};
@@ -357,12 +364,12 @@ static void run_stage_bf16(Ctx &c, const StageW &s, const StageWb &sb, const bf1
     const long long n4 = (long long)c.B * T * (kC / 4);
     int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
     const size_t rows = (size_t)c.B * T;
-    gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false);
-    gn_stats(c, w.h, T);
-    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, 1, c.B, T);
-    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false);
-    gn_stats(c, w.h, T);
-    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, 1, c.B, T);
+    // GroupNorm sums come out of the conv GEMMs' epilogues (slot 2*stage, 2*stage+1 of ws.gstats)
+    double *gs1 = w.gstats + (size_t)(2 * stage) * c.B * kGroups * 2, *gs2 = gs1 + (size_t)c.B * kGroups * 2;
+    gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs1);
+    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, 1, c.B, T, gs1);
+    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs2);
+    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, 1, c.B, T, gs2);
     gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
     launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
     bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
@@ -384,9 +391,9 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
     auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
     dim3 pgrid((T + 31) / 32, kInChPad / 32, c.B);
-    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, c.B, T);
+    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, c.B, T, w.gstats, kGnConvs * c.B * kGroups * 2);
     // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
-    run_stage_bf16(c, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, (T & 1) ? w.s0 : nullptr, w.s0b);
+    run_stage_bf16(c, 0, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, (T & 1) ? w.s0 : nullptr, w.s0b);
     if ((T & 1) == 0) {
         static const int taps_pair[2] = {-1, 0};
         gemm_b(c, w.s0b, 2 * kC, nullptr, 0, 2, taps_pair, T2, Wb.st[0].wtail, kC, W.st[0].btail, 0, nullptr, nullptr, w.inb, true);
@@ -399,11 +406,11 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         g.out_bf16 = w.inb; g.omask = c.mask; g.f16 = c.f16;
         launch(c, gemm_f32_kernel, dim3((c.B * T2 + kBM - 1) / kBM, kC / kBN), 256, 0, g);
     }
-    run_stage_bf16(c, W.st[1], Wb.st[1], w.inb, kC, nullptr, 0, T2, tb(1), tb_per_sample, nullptr, w.s1b);
+    run_stage_bf16(c, 1, W.st[1], Wb.st[1], w.inb, kC, nullptr, 0, T2, tb(1), tb_per_sample, nullptr, w.s1b);
     gemm_b(c, w.s1b, kC, nullptr, 0, 3, taps3, T2, Wb.st[1].wtail, kC, W.st[1].btail, 0, nullptr, nullptr, w.inb, true);
-    run_stage_bf16(c, W.st[2], Wb.st[2], w.inb, kC, nullptr, 0, T2, tb(2), tb_per_sample, nullptr, w.upb);
-    run_stage_bf16(c, W.st[3], Wb.st[3], w.upb, kC, nullptr, 0, T2, tb(3), tb_per_sample, nullptr, w.inb);
-    run_stage_bf16(c, W.st[4], Wb.st[4], w.inb, kC, w.s1b, kC, T2, tb(4), tb_per_sample, nullptr, w.upb);
+    run_stage_bf16(c, 2, W.st[2], Wb.st[2], w.inb, kC, nullptr, 0, T2, tb(2), tb_per_sample, nullptr, w.upb);
+    run_stage_bf16(c, 3, W.st[3], Wb.st[3], w.upb, kC, nullptr, 0, T2, tb(3), tb_per_sample, nullptr, w.inb);
+    run_stage_bf16(c, 4, W.st[4], Wb.st[4], w.inb, kC, w.s1b, kC, T2, tb(4), tb_per_sample, nullptr, w.upb);
     // ConvTranspose1d(4,2,1) (decoder.py:112) as two phase GEMMs on the fp32 kernel, then the nearest
     // resample (odd T) + x*mask into the bf16 operand of the last Resnet1D
     gemm_b(c, w.upb, kC, nullptr, 0, 2, taps_even, T2, Wb.st[4].wtail, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 0);
@@ -413,15 +420,15 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
         launch(c, resample_mask_bf16_kernel, eb, 256, 0, w.d, Tu, c.mask, w.upb, c.f16, c.B, T);
     }
-    run_stage_bf16(c, W.st[5], Wb.st[5], w.upb, kC, w.s0b, kC, T, tb(5), tb_per_sample, nullptr, w.inb);
+    run_stage_bf16(c, 5, W.st[5], Wb.st[5], w.upb, kC, w.s0b, kC, T, tb(5), tb_per_sample, nullptr, w.inb);
     gemm_b(c, w.inb, kC, nullptr, 0, 3, taps3, T, Wb.st[5].wtail, kC, W.st[5].btail, 0, nullptr, nullptr, w.a1b, true);
-    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, Wb.wf, kC, W.bf, 0, nullptr, w.h, nullptr, false);
-    gn_stats(c, w.h, T);
+    double *gsf = w.gstats + (size_t)12 * c.B * kGroups * 2;
+    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, Wb.wf, kC, W.bf, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gsf);
     {   // final_norm + Mish + x*mask into the 16-bit operand, then final_proj + mask + Euler update in the GEMM epilogue
         static const int tap0[1] = {0};
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, 1, c.B, T);
+        launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, 1, c.B, T, gsf);
         c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
         gemm_b(c, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
         c.fin_out = nullptr;

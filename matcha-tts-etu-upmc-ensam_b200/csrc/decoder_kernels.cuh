@@ -321,15 +321,26 @@ __global__ void __launch_bounds__(256)
 gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, const float *__restrict__ gamma,
                const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
                const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out,
-               __nv_bfloat16 *__restrict__ out_bf16, int f16, int fast, int B, int T) {
+               __nv_bfloat16 *__restrict__ out_bf16, int f16, int fast, int B, int T, const double *__restrict__ gsum) {
     pdl_launch_dependents();
     pdl_wait();
     const size_t n4 = (size_t)B * T * (kC / 4);
+    const double inv_n = 1.0 / ((double)T * kGroupCh);
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
         const int c = (int)(i % (kC / 4)) * 4;
         const size_t row = i / (kC / 4);
         const int b = (int)(row / T), t = (int)(row % T);
-        const float mean = stats[(b * kGroups + c / kGroupCh) * 2], rstd = stats[(b * kGroups + c / kGroupCh) * 2 + 1];
+        float mean, rstd;
+        if (gsum) {      // sums from the conv GEMM's epilogue (tensor-core path): biased variance in double
+            const double m = gsum[(b * kGroups + c / kGroupCh) * 2] * inv_n;
+            double var = gsum[(b * kGroups + c / kGroupCh) * 2 + 1] * inv_n - m * m;
+            if (var < 0.0) var = 0.0;
+            mean = (float)m;
+            rstd = 1.0f / sqrtf((float)var + 1e-5f);
+        } else {
+            mean = stats[(b * kGroups + c / kGroupCh) * 2];
+            rstd = stats[(b * kGroups + c / kGroupCh) * 2 + 1];
+        }
         const float mk = mask[(size_t)b * mask_T + t];
         const float4 v = *reinterpret_cast<const float4 *>(h + i * 4);
         const float4 ga = *reinterpret_cast<const float4 *>(gamma + c), be = *reinterpret_cast<const float4 *>(beta + c);
@@ -539,11 +550,13 @@ constexpr int kInChPad = 192;      // 160 input channels padded to three 64-wide
 // X0b[b][t][0:80] = x*mask, [80:160] = mu*mask, [160:192] = 0   (decoder.py:288 + the x*mask of :65,85)
 __global__ void __launch_bounds__(256)
 pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
-                       __nv_bfloat16 *__restrict__ out, int f16, int B, int T) {
+                       __nv_bfloat16 *__restrict__ out, int f16, int B, int T, double *__restrict__ gstats, int n_gstats) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float tile[32][33];
     const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 192 channels
+    if (blockIdx.x == 0 && blockIdx.y == 0)        // first kernel of an eval: clear the GroupNorm accumulators of its 13 convs
+        for (int i = blockIdx.z * 256 + threadIdx.x; i < n_gstats; i += gridDim.z * 256) gstats[i] = 0.0;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int i = ty; i < 32; i += 8) {
         const int c = c0 + i, t = t0 + tx;

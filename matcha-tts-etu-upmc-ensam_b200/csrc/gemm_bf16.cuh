@@ -49,6 +49,8 @@ struct GemmBf16Args {
     // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
     // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
     int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
+    // GroupNorm statistics of the fp32 output (kGStats): [B][8 groups][sum, sum of squares], accumulated with atomics
+    double *gstats;
 };
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
@@ -98,12 +100,12 @@ __device__ long long g_gemm_dbg[8];
 
 // EPI: 0 plain, 1 erf-GELU, 2 final projection; FLAGS: which of residual / fp32 output / 16-bit output exist;
 // F16: operand format.  All compile-time: the epilogue is issue-bound, a runtime "if (g.res)" costs slots.
-constexpr int kGRes = 1, kGF32 = 2, kGB16 = 4;
+constexpr int kGRes = 1, kGF32 = 2, kGB16 = 4, kGStats = 8;
 template <int EPI, int FLAGS, bool F16>
 __global__ void __launch_bounds__(kGThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
-    constexpr bool RES = (FLAGS & kGRes) != 0, F32 = (FLAGS & kGF32) != 0, B16 = (FLAGS & kGB16) != 0;
+    constexpr bool RES = (FLAGS & kGRes) != 0, F32 = (FLAGS & kGF32) != 0, B16 = (FLAGS & kGB16) != 0, STATS = (FLAGS & kGStats) != 0;
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
@@ -281,6 +283,27 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         if (RES) { x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w; }
                     }
                     if (RES && jj + 1 < 4) load_res(j + 1);
+                    if (STATS) {
+                        // the warp holds 32 rows x the 32 channels of GroupNorm group (n0 + 32 j) / 32 of sample b
+                        float gs = 0.f, gq = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            if (orow[i] >= 0) {
+                                gs += (x[i].x + x[i].y) + (x[i].z + x[i].w);
+                                gq += (x[i].x * x[i].x + x[i].y * x[i].y) + (x[i].z * x[i].z + x[i].w * x[i].w);
+                            }
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            gs += __shfl_xor_sync(0xffffffffu, gs, o);
+                            gq += __shfl_xor_sync(0xffffffffu, gq, o);
+                        }
+                        if (lane == 0) {
+                            double *gp = g.gstats + ((size_t)b * kGroups + (n0 + 32 * j) / kGroupCh) * 2;
+                            atomicAdd(gp, (double)gs);
+                            atomicAdd(gp + 1, (double)gq);
+                        }
+                    }
                     if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[6] = clock64();
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
