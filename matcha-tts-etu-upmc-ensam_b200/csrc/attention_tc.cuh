@@ -82,9 +82,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t bar_sf = bar_ve + 8 * kTaStages;          // [2] S ready
     const uint32_t bar_se = bar_sf + 16;                     // [2] S read by the softmax warps
     const uint32_t bar_pf = bar_se + 16;                     // [2] P written
-    const uint32_t bar_pv = bar_pf + 16;                     // every PV (one phase per key block)
-    const uint32_t tmem_slot = bar_pv + 8;
-    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + kTaOffBar + 8 + 32 * kTaStages + 56);
+    // [2] PV of key block j committed, on barrier j & 1.  Two barriers, because a parity wait is only unambiguous
+    // when the barrier is at most one phase away from the awaited one: PV_{j-2} is known to be complete once S_j has
+    // been read, whereas a single barrier may still be two PVs behind when the MMA warp is slow to issue.
+    const uint32_t bar_pv = bar_pf + 16;
+    const uint32_t tmem_slot = bar_pv + 16;
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + kTaOffBar + 8 + 32 * kTaStages + 64);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int T = g.T;
@@ -99,7 +102,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t n_sm_warps = (uint32_t)((rows_valid + 31) / 32);          // softmax warps that have rows
 
     if (threadIdx.x == 0) {
-        mbar_init(bar_q, 1u); mbar_init(bar_pv, 1u);
+        mbar_init(bar_q, 1u); mbar_init(bar_pv, 1u); mbar_init(bar_pv + 8u, 1u);
         for (int s = 0; s < kTaStages; ++s) {
             mbar_init(bar_kf + 8u * s, 1u); mbar_init(bar_ke + 8u * s, 1u);
             mbar_init(bar_vf + 8u * s, 1u); mbar_init(bar_ve + 8u * s, 1u);
@@ -155,7 +158,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                 const uint64_t dv = umma_desc_sw128(base + kTaOffV + s * kTaTileK);
                 for (int ks = 0; ks < n16 / 16; ++ks)      // 16 keys per step: P +32 B along its row, V +2048 B
                     umma_bf16(tmem_o, dp + (uint64_t)(2 * ks), dv + (uint64_t)(128 * ks), idesc_pv, (i | ks) != 0 ? 1u : 0u);
-                umma_commit(bar_pv);
+                umma_commit(bar_pv + 8u * (uint32_t)(i & 1));
                 umma_commit(bar_ve + 8u * s);
             };
             mbar_wait_parked(bar_q, 0, 500);
@@ -249,9 +252,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                     if (move) m_ref = m_blk;
                     l_run *= alpha;
                     if (j > 0) {
-                        // O_row *= alpha in TMEM: every PV issued so far has finished (PV_{j-1} is phase j-1 of bar_pv),
-                        // and PV_j cannot start before this warp has arrived on bar_pf below
-                        mbar_wait_parked(bar_pv, (j - 1) & 1, 100);
+                        // O_row *= alpha in TMEM: every PV issued so far has finished, and PV_j cannot start before this
+                        // warp has arrived on bar_pf below
+                        mbar_wait_parked(bar_pv + 8u * (uint32_t)((j - 1) & 1), ((j - 1) >> 1) & 1, 100);
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
                         for (int hcol = 0; hcol < 2; ++hcol) {
@@ -283,8 +286,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                 if (lane == 0) mbar_arrive(bar_pf + 8u * a);
                 l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
             }
-            // O is complete when the last PV (phase n_blk-1 of bar_pv) has been committed
-            mbar_wait_parked(bar_pv, (n_blk - 1) & 1, 100);
+            // O is complete when the last PV has been committed
+            mbar_wait_parked(bar_pv + 8u * (uint32_t)((n_blk - 1) & 1), ((n_blk - 1) >> 1) & 1, 100);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const float inv = 1.0f / l_run;
 #pragma unroll

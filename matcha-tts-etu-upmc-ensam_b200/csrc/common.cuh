@@ -112,6 +112,19 @@ __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// One lane of a converged warp (elect.sync).  Single-thread instructions (TMA, tcgen05.mma, tcgen05.commit) are
+// issued under it from warp-uniform control flow: the compiler then keeps their operands in uniform registers,
+// whereas an `if (lane == 0)` region makes it wrap each of them in a divergence ("waterfall") loop.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialization attribute may
 // start while its predecessor in the stream drains; nothing the predecessor wrote may be read (and nothing it
 // reads may be overwritten) before pdl_wait(), which returns once every prerequisite grid has completed and

@@ -92,14 +92,16 @@ time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict
         emb[80 + tid] = cosf(a);
     }
     __syncthreads();
-    for (int o = tid; o < kTimeDim; o += 256) {
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int o = warp; o < kTimeDim; o += 8) {                  // one warp per output, coalesced weight rows
         const float *wr = w.w1 + (size_t)o * kInCh;
         float acc = 0.f;
-        for (int i = 0; i < kInCh; ++i) acc = fmaf(wr[i], emb[i], acc);
-        h1[o] = silu_f(acc + w.b1[o]);
+#pragma unroll
+        for (int i = 0; i < kInCh / 32; ++i) acc = fmaf(wr[lane + 32 * i], emb[lane + 32 * i], acc);
+        for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+        if (lane == 0) h1[o] = silu_f(acc + w.b1[o]);
     }
     __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31;
     for (int oo = warp; oo < 64; oo += 8) {                     // one warp per output, coalesced weight rows
         const int o = blockIdx.y * 64 + oo;
         const float *wr = w.w2 + (size_t)o * kTimeDim;

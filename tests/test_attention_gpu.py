@@ -44,7 +44,8 @@ def rel(a, b):
     return (torch.linalg.norm((a - b).double()) / torch.linalg.norm(b.double())).item()
 
 
-SHAPES = [(2, 800), (3, 400), (2, 100), (1, 130), (2, 128), (1, 257), (2, 16), (1, 1000), (1, 7)]
+SHAPES = [(2, 800), (3, 400), (2, 100), (1, 130), (2, 128), (1, 257), (2, 16), (1, 1000), (1, 7),
+          (32, 800), (40, 400), (80, 130)]          # more tiles than persistent CTAs, ragged tiles included
 
 
 @pytest.mark.parametrize("impl", [0, 1], ids=["tcgen05", "mma_sync"])
