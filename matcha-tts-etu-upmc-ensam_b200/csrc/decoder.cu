@@ -15,6 +15,7 @@
 
 #include "attention_mma.cuh"
 #include "attention_tc.cuh"
+#include "ffn_fused.cuh"
 #include "gemm_bf16.cuh"
 
 namespace mb200 {
@@ -296,6 +297,8 @@ static int gemm_set_attributes() {
                 const GemmKernel k = pick_gemm(epi, flags, f16 != 0);
                 if (k) MB200_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
             }
+    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
     return MB200_OK;
 }
 
@@ -356,6 +359,29 @@ static void attention_b(Ctx &c, const bf16 *qkvb, bf16 *out, int T) {
     else launch(c, attention_mma_kernel<false>, agrid, 128, kFaSmemBytes, qkvb, c.mask, c.T, out, T);
 }
 
+// out = res + W2 gelu(W1 a + b1) + b2 in one kernel (ffn_fused.cuh); MB200_FFN=split keeps the two-GEMM path.
+static bool ffn_use_fused() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("MB200_FFN"); v = (e && e[0] == 's') ? 0 : 1; }
+    return v != 0;
+}
+static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1, const bf16 *w2, const float *b2,
+                  const float *res, float *out_f32, bf16 *out_b16, bool omask) {
+    if (c.err) return;
+    CUtensorMap ma, m1, m2;
+    if (!tmap_for(c, a, 3, (uint64_t)kC, (uint64_t)T, (uint64_t)c.B, 64, kFfM, &ma)) return;
+    if (!tmap_for(c, w1, 2, (uint64_t)kC, (uint64_t)kFfHid, 1, 64, kFfChunk, &m1)) return;
+    if (!tmap_for(c, w2, 2, (uint64_t)kFfHid, (uint64_t)kC, 1, 64, kC, &m2)) return;
+    FfnArgs g;
+    g.B = c.B; g.T = T; g.tiles_per_sample = (T + kFfM - 1) / kFfM;
+    g.b1 = b1; g.b2 = b2; g.res = res; g.out_f32 = out_f32; g.out_b16 = out_b16;
+    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T;
+    if ((long long)c.B * T * kC >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
+    const int grid = c.B * g.tiles_per_sample;
+    if (c.f16) launch(c, ffn_fused_kernel<true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, g);
+    else launch(c, ffn_fused_kernel<false>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, g);
+}
+
 static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb, const bf16 *in0, int c0, const bf16 *in1,
                            int c1, int T, const float *tb, int tb_per_sample, float *out_f32, bf16 *out_b16) {
     static const int taps3[3] = {-1, 0, 1};
@@ -377,8 +403,12 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
     attention_b(c, qkvb, w.attb, T);
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
     launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
-    gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
-    gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
+    if (ffn_use_fused()) {
+        ffn_b(c, w.lnb, T, sb.w1, s.b1, sb.w2, s.b2, w.x2, out_f32, out_b16, true);
+    } else {
+        gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
+        gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
+    }
 }
 
 static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const float *x, const float *mu,
@@ -579,6 +609,20 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);
+    if (c.err) return c.err;
+    MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+// test aid, not part of the public header: the fused feed-forward on caller-provided 16-bit operands
+extern "C" int matcha_b200_debug_ffn(const void *a16, const void *w1_16, const float *b1, const void *w2_16,
+                                      const float *b2, const float *res, float *out_f32, void *out_16,
+                                      const float *mask, int B, int T, int f16, void *stream) {
+    if (!a16 || !w1_16 || !w2_16 || !b1 || !b2 || !res || B < 1 || T < 1) return MB200_ERR_INVALID_ARG;
+    Ctx c;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16;
+    { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
+    ffn_b(c, (const bf16 *)a16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, res, out_f32, (bf16 *)out_16, mask != nullptr);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;

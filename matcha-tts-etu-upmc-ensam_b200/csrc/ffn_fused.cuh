@@ -1,0 +1,277 @@
+// ffn_fused.cuh -- the transformer block's feed-forward as ONE tcgen05 kernel:
+//     out = res + W2 . gelu(W1 . a + b1) + b2             FeedForward of transformer.py:105-188 (GELU proj 256->1024,
+//                                                         LoRACompatibleLinear 1024->256) + the residual of :366
+// The 1024-wide hidden activation never leaves the SM.  One CTA owns 128 rows of one sample:
+//   * A = the LayerNorm'd rows, 16-bit [128][256], stays in shared memory (4 K-blocks of the 128B-swizzled K-major
+//     layout) for the whole tile.
+//   * The hidden dimension is walked in 8 chunks of 128 columns.  FFN1(c): acc1[c&1] (TMEM, 128 columns, double
+//     buffered) = A . W1[chunk c]^T.  The epilogue warps read it (thread = row), add b1, apply GELU and write the
+//     16-bit result straight into the K-major A-operand layout of H[c&1] in shared memory.  FFN2(c): acc2 (TMEM,
+//     256 columns) += H[c&1] . W2[:, chunk c]^T.  The MMA warp issues FFN1(c+1) before FFN2(c), so the tensor
+//     pipe works on the next chunk while the epilogue warps run the GELU of this one.
+//   * W1 / W2 K-blocks stream through a 3-stage ring of 32 KB TMA stages (one stage = 128 hidden rows x 128 k of W1
+//     as two boxes, or 256 output rows x 64 hidden of W2).
+//   * Final epilogue: acc2 + b2 + residual -> fp32 rows and/or 16-bit rows * mask (the next conv's operand).
+// TMEM: acc2 256 + acc1 2 x 128 = 512 columns.  Shared: A 64 KB + H 2 x 32 KB + ring 96 KB = 224 KB.
+#pragma once
+#include "gemm_bf16.cuh"
+
+namespace mb200 {
+
+constexpr int kFfM = 128, kFfHid = 1024, kFfChunk = 128, kFfNChunks = kFfHid / kFfChunk;
+constexpr int kFfStages = 3, kFfStageBytes = 32768;
+constexpr int kFfKb = 16384;                                  // one [128][64] 16-bit K-block
+constexpr int kFfOffA = 0, kFfOffH = 4 * kFfKb, kFfOffRing = kFfOffH + 2 * 2 * kFfKb;
+constexpr int kFfOffBar = kFfOffRing + kFfStages * kFfStageBytes;
+constexpr int kFfSmemBytes = kFfOffBar + 256 + 1024;
+constexpr int kFfEpiWarps = 16;
+constexpr int kFfThreads = 32 * (2 + kFfEpiWarps);
+constexpr int kFfEpiPitch = 36;                               // floats, final-epilogue transpose tiles (in the A/H region)
+
+struct FfnArgs {
+    int B, T, tiles_per_sample;
+    const float *b1, *b2;              // [1024], [256]
+    const float *res;                  // fp32 [B][T][256]
+    float *out_f32;                    // fp32 [B][T][256] or nullptr
+    __nv_bfloat16 *out_b16;            // 16-bit [B][T][256] or nullptr, rows multiplied by omask
+    const float *omask; int omask_T;
+};
+
+// erf-GELU for 16-bit outputs with ONE MUFU op: x * Phi(x) = h + h * tanh(x * p(x^2)), h = x / 2, with p the
+// weighted minimax fit of atanh(erf(x / sqrt 2)) / x (|error of the GELU value| < 2.6e-5 before tanh.approx's own
+// 2^-11 relative error, i.e. at the level of the 16-bit rounding that follows).  x^2 is clamped where tanh has
+// long saturated, which keeps p positive.
+__device__ __forceinline__ float gelu_tanh_fit_f(float x) {
+    const float x2 = fminf(x * x, 64.0f);
+    float p = fmaf(-3.51519810e-04f, x2, 3.70056687e-02f);
+    p = fmaf(p, x2, 7.97507852e-01f);
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(p * x));
+    const float h = 0.5f * x;
+    return fmaf(h, t, h);
+}
+
+constexpr uint32_t kFfIdesc1F16 = (1u << 4) | ((uint32_t)(kFfChunk >> 3) << 17) | ((uint32_t)(kFfM >> 4) << 24);   // M128 N128
+constexpr uint32_t kFfIdesc1Bf16 = kFfIdesc1F16 | (1u << 7) | (1u << 10);
+
+template <bool F16>
+__global__ void __launch_bounds__(kFfThreads, 1)
+ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW1,
+                 const __grid_constant__ CUtensorMap tmW2, const FfnArgs g) {
+    extern __shared__ uint8_t ffsm_raw[];
+    const uint32_t base = (smem_u32(ffsm_raw) + 1023u) & ~1023u;
+    uint8_t *gbase = ffsm_raw + (base - smem_u32(ffsm_raw));
+    const uint32_t bar0 = base + kFfOffBar;
+    const uint32_t bar_a = bar0;                              // A tile landed
+    const uint32_t bar_full = bar0 + 8;                       // [3] ring stage landed
+    const uint32_t bar_empty = bar_full + 8 * kFfStages;      // [3] ring stage consumed
+    const uint32_t bar_a1f = bar_empty + 8 * kFfStages;       // [2] acc1 ready
+    const uint32_t bar_a1e = bar_a1f + 16;                    // [2] acc1 read by the epilogue warps
+    const uint32_t bar_hf = bar_a1e + 16;                     // [2] H chunk written
+    const uint32_t bar_he = bar_hf + 16;                      // [2] H chunk consumed by FFN2
+    const uint32_t bar_a2f = bar_he + 16;                     // acc2 complete
+    const uint32_t tmem_slot = bar_a2f + 8;
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_slot - base));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x - b * g.tiles_per_sample) * kFfM;
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar_a, 1u); mbar_init(bar_a2f, 1u);
+        for (int s = 0; s < kFfStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_a1f + 8u * a, 1u); mbar_init(bar_a1e + 8u * a, kFfEpiWarps);
+            mbar_init(bar_hf + 8u * a, kFfEpiWarps); mbar_init(bar_he + 8u * a, 1u);
+        }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *tmem_slot_p;
+    const uint32_t tmem_acc2 = tmem, tmem_acc1 = tmem + 256;
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0) {
+            uint32_t it = 0;
+            auto stage_w1 = [&](int c, int half) {            // W1 rows [128c, 128c+128), k in [128 half, 128 half + 128)
+                const uint32_t s = it % kFfStages;
+                mbar_wait_parked(bar_empty + 8u * s, ((it / kFfStages) & 1) ^ 1, 500);
+                const uint32_t dst = base + kFfOffRing + s * kFfStageBytes;
+                mbar_arrive_expect_tx(bar_full + 8u * s, kFfStageBytes);
+                tma_load_2d(dst, &tmW1, bar_full + 8u * s, (2 * half) * 64, c * kFfChunk);
+                tma_load_2d(dst + kFfKb, &tmW1, bar_full + 8u * s, (2 * half + 1) * 64, c * kFfChunk);
+                ++it;
+            };
+            auto stage_w2 = [&](int c, int kb) {              // W2 all 256 rows, hidden k in [128c + 64kb, +64)
+                const uint32_t s = it % kFfStages;
+                mbar_wait_parked(bar_empty + 8u * s, ((it / kFfStages) & 1) ^ 1, 500);
+                mbar_arrive_expect_tx(bar_full + 8u * s, kFfStageBytes);
+                tma_load_2d(base + kFfOffRing + s * kFfStageBytes, &tmW2, bar_full + 8u * s, c * kFfChunk + kb * 64, 0);
+                ++it;
+            };
+            // the weights do not depend on the predecessor kernel: the first stages are in flight before the wait
+            stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
+            pdl_wait();
+            mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
+            for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
+            stage_w1(1, 1);
+            for (int s = 2; s <= kFfNChunks; ++s) {
+                stage_w2(s - 2, 0); stage_w2(s - 2, 1);
+                if (s < kFfNChunks) { stage_w1(s, 0); stage_w1(s, 1); }
+            }
+            stage_w2(kFfNChunks - 1, 0); stage_w2(kFfNChunks - 1, 1);
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ============================
+        if (lane == 0) {
+            const uint32_t idesc1 = F16 ? kFfIdesc1F16 : kFfIdesc1Bf16;
+            const uint32_t idesc2 = F16 ? kIdescF16 : kIdescBf16;
+            uint32_t it = 0;
+            auto ffn1 = [&](int c) {
+                const uint32_t buf = c & 1;
+                if (c >= 2) mbar_wait_parked(bar_a1e + 8u * buf, ((c >> 1) - 1) & 1, 200);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                for (int half = 0; half < 2; ++half, ++it) {
+                    const uint32_t s = it % kFfStages;
+                    mbar_wait_parked(bar_full + 8u * s, (it / kFfStages) & 1, 200);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                    for (int kb2 = 0; kb2 < 2; ++kb2) {
+                        const uint64_t da = umma_desc_sw128(base + kFfOffA + (2 * half + kb2) * kFfKb);
+                        const uint64_t db = umma_desc_sw128(base + kFfOffRing + s * kFfStageBytes + kb2 * kFfKb);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16(tmem_acc1 + buf * kFfChunk, da + 2u * k, db + 2u * k, idesc1, (half | kb2 | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(bar_empty + 8u * s);
+                }
+                umma_commit(bar_a1f + 8u * buf);
+            };
+            auto ffn2 = [&](int c) {
+                const uint32_t buf = c & 1;
+                mbar_wait_parked(bar_hf + 8u * buf, (c >> 1) & 1, 200);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                for (int kb = 0; kb < 2; ++kb, ++it) {
+                    const uint32_t s = it % kFfStages;
+                    mbar_wait_parked(bar_full + 8u * s, (it / kFfStages) & 1, 200);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint64_t da = umma_desc_sw128(base + kFfOffH + (2 * buf + kb) * kFfKb);
+                    const uint64_t db = umma_desc_sw128(base + kFfOffRing + s * kFfStageBytes);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16(tmem_acc2, da + 2u * k, db + 2u * k, idesc2, (c | kb | k) != 0 ? 1u : 0u);
+                    umma_commit(bar_empty + 8u * s);
+                }
+                umma_commit(bar_he + 8u * buf);
+            };
+            mbar_wait_parked(bar_a, 0, 500);
+            ffn1(0);
+            for (int s = 1; s < kFfNChunks; ++s) { ffn1(s); ffn2(s - 1); }
+            ffn2(kFfNChunks - 1);
+            umma_commit(bar_a2f);
+        }
+    } else {
+        // ============================ epilogue warps ============================
+        const int ew = warp - 2;
+        const int q = warp & 3;                              // TMEM lane quarter this warp may touch
+        const int cg = ew >> 2;                              // column group
+        const int row = 32 * q + lane;                       // tile row = TMEM lane
+        const uint32_t lane_off = (uint32_t)(32 * q) << 16;
+        // ---- GELU of every hidden chunk: 32 columns [32 cg, 32 cg + 32) of the chunk per warp
+        const uint32_t hrow = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128);
+        for (int c = 0; c < kFfNChunks; ++c) {
+            const uint32_t buf = c & 1;
+            const float4 *b1v = reinterpret_cast<const float4 *>(g.b1 + c * kFfChunk + cg * 32);
+            mbar_wait_parked(bar_a1f + 8u * buf, (c >> 1) & 1, 100);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            uint32_t v[32];
+            tmem_ld32(tmem_acc1 + buf * kFfChunk + cg * 32 + lane_off, v);
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_a1e + 8u * buf);
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 bb = __ldg(b1v + i);
+                const float y0 = gelu_tanh_fit_f(__uint_as_float(v[4 * i]) + bb.x);
+                const float y1 = gelu_tanh_fit_f(__uint_as_float(v[4 * i + 1]) + bb.y);
+                const float y2 = gelu_tanh_fit_f(__uint_as_float(v[4 * i + 2]) + bb.z);
+                const float y3 = gelu_tanh_fit_f(__uint_as_float(v[4 * i + 3]) + bb.w);
+                pk[2 * i] = pack16x2(y0, y1, F16);
+                pk[2 * i + 1] = pack16x2(y2, y3, F16);
+            }
+            if (c >= 2) mbar_wait_parked(bar_he + 8u * buf, ((c >> 1) - 1) & 1, 100);    // FFN2(c-2) has consumed H[buf]
+            // columns [32 cg, +32) of the chunk = K-block cg / 2, 16-byte pieces 4 (cg & 1) .. +3 of the row
+            const uint32_t hdst = base + kFfOffH + (2 * buf + (cg >> 1)) * kFfKb + hrow;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t piece = (uint32_t)((cg & 1) * 4 + i);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hdst + ((piece ^ (uint32_t)(row & 7)) << 4)),
+                             "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3]) : "memory");
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_hf + 8u * buf);
+        }
+        // ---- final epilogue: columns [64 cg, 64 cg + 64) of acc2, transposed through shared memory (the A / H
+        //      region is free: every MMA has completed) so that global accesses are row-contiguous
+        pdl_wait();                                           // g.res is the predecessor chain's output
+        mbar_wait_parked(bar_a2f, 0, 200);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        float *tb = reinterpret_cast<float *>(gbase) + ew * (32 * kFfEpiPitch);
+        const int rsub = lane >> 3, c4 = (lane & 7) * 4;
+        int orow[8];
+        float mk[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int t = t0 + 32 * q + 4 * i + rsub;
+            const bool ok = t < g.T;
+            orow[i] = ok ? (int)(((long long)b * g.T + t) * kC) : -1;
+            mk[i] = (ok && g.omask) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
+        }
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int n = cg * 64 + jj * 32 + c4;
+            float4 rv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 bias = *reinterpret_cast<const float4 *>(g.b2 + n);
+            uint32_t v[32];
+            tmem_ld32(tmem_acc2 + cg * 64 + jj * 32 + lane_off, v);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4 *>(tb + lane * kFfEpiPitch + 4 * i) =
+                    make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float4 x = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kFfEpiPitch + c4);
+                x.x += bias.x + rv[i].x; x.y += bias.y + rv[i].y; x.z += bias.z + rv[i].z; x.w += bias.w + rv[i].w;
+                if (orow[i] >= 0) {
+                    if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x;
+                    if (g.out_b16)
+                        *reinterpret_cast<uint2 *>(g.out_b16 + orow[i] + n) =
+                            make_uint2(pack16x2(x.x * mk[i], x.y * mk[i], F16), pack16x2(x.z * mk[i], x.w * mk[i], F16));
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
+    }
+}
+
+}  // namespace mb200

@@ -1,0 +1,70 @@
+"""GPU test of the fused feed-forward kernel (csrc/ffn_fused.cuh) in isolation against a plain PyTorch fp32
+reference of the same op (transformer.py:105-188 + the residual of :366) on the same 16-bit-rounded operands.
+Tolerances: the hidden activation is rounded to 16 bits inside the kernel (rel 2^-11 for fp16, 2^-8 for bf16) and
+the GELU carries tanh.approx's 2^-11 relative error, so the FFN term is good to ~5e-4 (fp16) / 4e-3 (bf16)."""
+import ctypes
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def run_ffn(a, w1, b1, w2, b2, res, mask, f16, want_f32=True, want_16=True):
+    from matcha_b200._lib import check, load_library
+    lib = load_library()
+    B, T, _ = a.shape
+    out = torch.full((B, T, 256), float("nan"), device="cuda") if want_f32 else None
+    out16 = torch.zeros((B, T, 256), device="cuda", dtype=a.dtype) if want_16 else None
+    p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    check(lib.matcha_b200_debug_ffn(p(a), p(w1), p(b1), p(w2), p(b2), p(res), p(out), p(out16), p(mask), B, T, int(f16),
+                                    ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "debug_ffn")
+    torch.cuda.synchronize()
+    return out, out16
+
+
+def reference(a, w1, b1, w2, b2, res):
+    h = torch.nn.functional.gelu(a.float() @ w1.float().t() + b1)
+    return res + h @ w2.float().t() + b2, h @ w2.float().t() + b2
+
+
+def rel(a, b):
+    return float(torch.linalg.norm((a - b).double()) / torch.linalg.norm(b.double()))
+
+
+@pytest.mark.parametrize("B,T,f16", [(2, 200, True), (1, 128, True), (3, 130, True), (2, 5, True), (4, 400, True),
+                                     (2, 200, False), (1, 333, False)])
+def test_ffn_matches_torch(B, T, f16):
+    dt = torch.float16 if f16 else torch.bfloat16
+    g = torch.Generator(device="cuda").manual_seed(B * 11 + T)
+    a = torch.randn(B, T, 256, device="cuda", generator=g).to(dt)
+    w1 = (torch.randn(1024, 256, device="cuda", generator=g) * 0.09).to(dt)      # Kaiming scale: pre-activations ~ N(0, 2)
+    w2 = (torch.randn(256, 1024, device="cuda", generator=g) * 0.044).to(dt)
+    b1 = torch.randn(1024, device="cuda", generator=g) * 0.5
+    b2 = torch.randn(256, device="cuda", generator=g)
+    res = torch.randn(B, T, 256, device="cuda", generator=g)
+    mask = torch.ones(B, T, device="cuda")
+    mask[B - 1, (2 * T) // 3:] = 0
+    out, out16 = run_ffn(a, w1, b1, w2, b2, res, mask, f16)
+    want, want_term = reference(a, w1, b1, w2, b2, res)
+    assert torch.isfinite(out).all()
+    tol = 6e-4 if f16 else 4e-3
+    assert rel(out - res, want_term) < tol                    # the feed-forward term itself
+    assert rel(out, want) < tol
+    assert rel(out16.float(), want * mask[:, :, None]) < (1e-3 if f16 else 6e-3)
+    assert out16[B - 1, (2 * T) // 3:].abs().sum() == 0
+
+
+def test_ffn_only_16bit_output_and_large_activations():
+    g = torch.Generator(device="cuda").manual_seed(3)
+    B, T = 2, 257
+    a = (torch.randn(B, T, 256, device="cuda", generator=g) * 3).half()
+    w1 = (torch.randn(1024, 256, device="cuda", generator=g) * 0.09).half()
+    w2 = (torch.randn(256, 1024, device="cuda", generator=g) * 0.044).half()
+    b1 = torch.zeros(1024, device="cuda")
+    b2 = torch.zeros(256, device="cuda")
+    res = torch.zeros(B, T, 256, device="cuda")
+    out, out16 = run_ffn(a, w1, b1, w2, b2, res, None, True, want_f32=False)
+    want, _ = reference(a, w1, b1, w2, b2, res)
+    assert out is None
+    assert rel(out16.float(), want) < 1e-3
