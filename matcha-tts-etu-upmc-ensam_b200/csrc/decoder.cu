@@ -230,7 +230,9 @@ static void decoder_eval(Ctx &c, const DecW &W, const float *x, const float *mu,
 
 // ================================================================== bf16 mode (tcgen05 GEMMs)
 typedef __nv_bfloat16 bf16;
-struct StageWb { const bf16 *wc1, *wc2, *wr, *wqkv, *wo, *w1, *w2, *wtail, *wtail2; int cin_pad; };
+// wc1: [512][3][cin_pad] = block1's conv (rows 0..255) stacked on res_conv (rows 256..511, centre tap only, zeros
+// elsewhere): both read the stage input, one GEMM with two output blocks computes them (gemm_bf16.cuh, n_split)
+struct StageWb { const bf16 *wc1, *wc2, *wqkv, *wo, *w1, *w2, *wtail, *wtail2; int cin_pad; };
 struct DecWb { StageWb st[6]; const bf16 *wf, *wp; };
 static const int kStageCinPad[6] = {kInChPad, kC, kC, kC, 2 * kC, 2 * kC};
 
@@ -242,7 +244,7 @@ static long long build_weights_bf16(const bf16 *blob, DecWb *w) {
     for (int i = 0; i < 6; ++i) {
         StageWb &s = d.st[i];
         s.cin_pad = kStageCinPad[i];
-        s.wc1 = take(256LL * 3 * s.cin_pad); s.wc2 = take(256LL * 3 * 256); s.wr = take(256LL * s.cin_pad);
+        s.wc1 = take(512LL * 3 * s.cin_pad); s.wc2 = take(256LL * 3 * 256);
         s.wqkv = take(768LL * 256); s.wo = take(256LL * 256); s.w1 = take(1024LL * 256); s.w2 = take(256LL * 1024);
         s.wtail = s.wtail2 = nullptr;
         if (i == 0) s.wtail = take(256LL * 2 * 512);              // stride-2 conv on the paired view
@@ -306,7 +308,8 @@ static int gemm_set_attributes() {
 // reference multiplies), w: bf16 [N][ntaps*(c0+c1)].
 static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
                    const bf16 *w, int N, const float *bias, int act, const float *res, float *out_f32,
-                   bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0, double *gstats = nullptr) {
+                   bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0, double *gstats = nullptr,
+                   const float *bias2 = nullptr, float *out2_f32 = nullptr, int kb2_begin = 0, int kb2_count = 0) {
     if (c.err) return;
     CUtensorMap ma0, ma1, mb;
     if (!tmap_for(c, a0, 3, (uint64_t)c0, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma0)) return;
@@ -328,6 +331,7 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     g.debug = c.debug;
     if ((long long)c.B * g.out_T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
     g.gstats = gstats;
+    g.n_split = out2_f32 ? N / 2 : 0; g.kb2_begin = kb2_begin; g.kb2_count = kb2_count; g.bias2 = bias2; g.out2_f32 = out2_f32;
     const int flags = (res ? kGRes : 0) | (out_f32 ? kGF32 : 0) | (out_b16 ? kGB16 : 0) | (gstats ? kGStats : 0);
     const GemmKernel k = pick_gemm(g.fin_n > 0 ? 2 : act, g.fin_n > 0 ? 0 : flags, c.f16 != 0);
     if (!k) { c.err = MB200_ERR_UNSUPPORTED; return; }
@@ -375,7 +379,7 @@ static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1,
     FfnArgs g;
     g.B = c.B; g.T = T; g.tiles_per_sample = (T + kFfM - 1) / kFfM;
     g.b1 = b1; g.b2 = b2; g.res = res; g.out_f32 = out_f32; g.out_b16 = out_b16;
-    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T;
+    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.debug = c.debug;
     if ((long long)c.B * T * kC >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
     const int grid = c.B * g.tiles_per_sample;
     if (c.f16) launch(c, ffn_fused_kernel<true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, g);
@@ -392,12 +396,16 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
     const size_t rows = (size_t)c.B * T;
     // GroupNorm sums come out of the conv GEMMs' epilogues (slot 2*stage, 2*stage+1 of ws.gstats)
     double *gs1 = w.gstats + (size_t)(2 * stage) * c.B * kGroups * 2, *gs2 = gs1 + (size_t)c.B * kGroups * 2;
-    gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, kC, s.bc1, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs1);
-    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, w.a1b, c.f16, 1, c.B, T, gs1);
+    // block1's conv and res_conv in one GEMM: h = conv(x*mask) (+ GroupNorm sums), g = res_conv(x*mask) (centre tap only)
+    const int chunks = (c0 + c1) / kGK;
+    gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, 2 * kC, s.bc1, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs1, s.br, w.g, chunks, chunks);
+    const unsigned rb = (unsigned)((rows + kGmRowsPerBlock - 1) / kGmRowsPerBlock);
+    launch(c, gn_mish_rows_kernel<0>, rb, 256, 0, w.h, gs1, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, nullptr, nullptr,
+           nullptr, w.a1b, c.f16, c.B, T);
     gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs2);
-    launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, nullptr, 0, 1, c.B, T, gs2);
-    gemm_b(c, in0, c0, in1, c1, 1, tap0, T, sb.wr, kC, s.br, 0, w.g, w.x1, nullptr, false);
-    launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x1, s.ln1g, s.ln1b, nullptr, w.lnb, c.f16, rows);
+    // x1 = Mish(GN(h)) * mask + res_conv, and norm1(x1) as the q|k|v operand, in one pass
+    launch(c, gn_mish_rows_kernel<1>, rb, 256, 0, w.h, gs2, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, s.ln1g, s.ln1b, w.x1, w.lnb,
+           c.f16, c.B, T);
     bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
     attention_b(c, qkvb, w.attb, T);
@@ -458,7 +466,8 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         static const int tap0[1] = {0};
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        launch(c, gn_mish_kernel, eb, 256, 0, w.h, w.stats, W.gf, W.bef, c.mask, c.T, nullptr, 0, nullptr, w.a1b, c.f16, 1, c.B, T, gsf);
+        launch(c, gn_mish_rows_kernel<0>, (unsigned)(((size_t)c.B * T + kGmRowsPerBlock - 1) / kGmRowsPerBlock), 256, 0, w.h, gsf, W.gf,
+               W.bef, c.mask, c.T, nullptr, 0, nullptr, nullptr, nullptr, nullptr, w.a1b, c.f16, c.B, T);
         c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
         gemm_b(c, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
         c.fin_out = nullptr;
@@ -533,14 +542,18 @@ extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_b
     build_weights(blob_dev, &W);
     build_weights_bf16(reinterpret_cast<bf16 *>(blob_bf16_dev), &Wb);
     cudaStream_t st = (cudaStream_t)stream;
-    auto pack = [&](const float *src, const bf16 *dst, int rows, int cin, int cin_pad) {
-        pack_weight_bf16_kernel<<<256, 256, 0, st>>>(src, const_cast<bf16 *>(dst), rows, cin, cin_pad, f16);
+    auto pack = [&](const float *src, const bf16 *dst, int rows, int cin, int cin_pad, int dst_stride = 0) {
+        pack_weight_bf16_kernel<<<256, 256, 0, st>>>(src, const_cast<bf16 *>(dst), rows, cin, cin_pad, f16, dst_stride ? dst_stride : cin_pad);
     };
     for (int i = 0; i < 6; ++i) {
         const StageW &s = W.st[i]; const StageWb &b = Wb.st[i];
         pack(s.wc1, b.wc1, 256 * 3, s.cin, b.cin_pad);
+        {   // res_conv rows: zeros, then [256][cin] into the centre-tap columns
+            bf16 *wr = const_cast<bf16 *>(b.wc1) + 256LL * 3 * b.cin_pad;
+            MB200_CUDA_TRY(cudaMemsetAsync(wr, 0, 256LL * 3 * b.cin_pad * sizeof(bf16), st));
+            pack(s.wr, wr + b.cin_pad, 256, s.cin, b.cin_pad, 3 * b.cin_pad);
+        }
         pack(s.wc2, b.wc2, 256 * 3, 256, 256);
-        pack(s.wr, b.wr, 256, s.cin, b.cin_pad);
         pack(s.wqkv, b.wqkv, 768, 256, 256);
         pack(s.wo, b.wo, 256, 256, 256);
         pack(s.w1, b.w1, 1024, 256, 256);
@@ -620,11 +633,16 @@ extern "C" int matcha_b200_debug_ffn(const void *a16, const void *w1_16, const f
                                       const float *mask, int B, int T, int f16, void *stream) {
     if (!a16 || !w1_16 || !w2_16 || !b1 || !b2 || !res || B < 1 || T < 1) return MB200_ERR_INVALID_ARG;
     Ctx c;
-    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16; c.debug = 1;
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     ffn_b(c, (const bf16 *)a16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, res, out_f32, (bf16 *)out_16, mask != nullptr);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+extern "C" int matcha_b200_debug_ffn_stamps(long long *out64) {
+    MB200_CUDA_TRY(cudaMemcpyFromSymbol(out64, mb200::g_ffn_dbg, sizeof(long long) * 64));
     return MB200_OK;
 }
 

@@ -369,6 +369,113 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
     }
 }
 
+// Row-wise variant for the tensor-core path (GroupNorm sums come from the conv GEMM's epilogue): one warp per row,
+// four rows per warp in flight, the 8 (mean, rstd) pairs of every sample a block touches computed once into shared
+// memory.
+//   MODE 0: out16 = (Mish(GN(h)) * mask + tb) * mask                      Block1D + time bias, next conv's operand
+//   MODE 1: x = Mish(GN(h)) * mask + r;  out_f32 = x;  out16 = LayerNorm(x)   Block1D + res_conv (decoder.py:85) +
+//           norm1 of the transformer block (transformer.py:316) in one pass
+constexpr int kGmRowsPerWarp = 4, kGmRowsPerBlock = 8 * kGmRowsPerWarp;
+template <int MODE>
+__global__ void __launch_bounds__(256)
+gn_mish_rows_kernel(const float *__restrict__ h, const double *__restrict__ gsum, const float *__restrict__ gamma,
+                    const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
+                    const float *__restrict__ tb, int tb_per_sample, const float *__restrict__ r,
+                    const float *__restrict__ ln_g, const float *__restrict__ ln_b, float *__restrict__ out_f32,
+                    __nv_bfloat16 *__restrict__ out16, int f16, int B, int T) {
+    __shared__ float s_stat[kGmRowsPerBlock][kGroups][2];
+    pdl_launch_dependents();
+    pdl_wait();
+    const size_t rows = (size_t)B * T;
+    const size_t r0 = (size_t)blockIdx.x * kGmRowsPerBlock;
+    const int b0 = (int)(r0 / T);
+    {
+        const int bb = b0 + (int)(threadIdx.x >> 3), gi = threadIdx.x & 7;
+        const size_t r_last = r0 + kGmRowsPerBlock - 1 < rows ? r0 + kGmRowsPerBlock - 1 : rows - 1;
+        if (bb <= (int)(r_last / T)) {
+            const double inv_n = 1.0 / ((double)T * kGroupCh);
+            const double m = gsum[(bb * kGroups + gi) * 2] * inv_n;
+            double var = gsum[(bb * kGroups + gi) * 2 + 1] * inv_n - m * m;
+            if (var < 0.0) var = 0.0;
+            s_stat[bb - b0][gi][0] = (float)m;
+            s_stat[bb - b0][gi][1] = 1.0f / sqrtf((float)var + 1e-5f);
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = lane * 4, c1 = 128 + lane * 4, g0 = lane >> 3, g1 = 4 + (lane >> 3);
+    const float4 ga0 = *reinterpret_cast<const float4 *>(gamma + c0), ga1 = *reinterpret_cast<const float4 *>(gamma + c1);
+    const float4 be0 = *reinterpret_cast<const float4 *>(beta + c0), be1 = *reinterpret_cast<const float4 *>(beta + c1);
+    float4 v0[kGmRowsPerWarp], v1[kGmRowsPerWarp], x0[kGmRowsPerWarp], x1[kGmRowsPerWarp];
+    float mk[kGmRowsPerWarp];
+    int bs[kGmRowsPerWarp];
+#pragma unroll
+    for (int j = 0; j < kGmRowsPerWarp; ++j) {               // every load of the warp's four rows first
+        const size_t row = r0 + warp * kGmRowsPerWarp + j;
+        const bool ok = row < rows;
+        const int b = ok ? (int)(row / T) : b0, t = ok ? (int)(row - (size_t)b * T) : 0;
+        bs[j] = b;
+        mk[j] = ok ? mask[(size_t)b * mask_T + t] : 0.f;
+        v0[j] = ok ? *reinterpret_cast<const float4 *>(h + row * kC + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
+        v1[j] = ok ? *reinterpret_cast<const float4 *>(h + row * kC + c1) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (MODE == 1) {
+            x0[j] = ok ? *reinterpret_cast<const float4 *>(r + row * kC + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
+            x1[j] = ok ? *reinterpret_cast<const float4 *>(r + row * kC + c1) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (tb) {
+            x0[j] = *reinterpret_cast<const float4 *>(tb + (size_t)(tb_per_sample ? b : 0) * kC + c0);
+            x1[j] = *reinterpret_cast<const float4 *>(tb + (size_t)(tb_per_sample ? b : 0) * kC + c1);
+        } else {
+            x0[j] = x1[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    float4 lg0, lg1, lb0, lb1;
+    if (MODE == 1) {
+        lg0 = *reinterpret_cast<const float4 *>(ln_g + c0); lg1 = *reinterpret_cast<const float4 *>(ln_g + c1);
+        lb0 = *reinterpret_cast<const float4 *>(ln_b + c0); lb1 = *reinterpret_cast<const float4 *>(ln_b + c1);
+    }
+#pragma unroll
+    for (int j = 0; j < kGmRowsPerWarp; ++j) {
+        const size_t row = r0 + warp * kGmRowsPerWarp + j;
+        if (row >= rows) break;
+        const float m0 = s_stat[bs[j] - b0][g0][0], rs0 = s_stat[bs[j] - b0][g0][1];
+        const float m1 = s_stat[bs[j] - b0][g1][0], rs1 = s_stat[bs[j] - b0][g1][1];
+        const float k = mk[j];
+        float4 a, b;       // Mish(GN(h)) * mask + (time bias | res_conv)
+        a.x = mish_fast_f((v0[j].x - m0) * rs0 * ga0.x + be0.x) * k + x0[j].x;
+        a.y = mish_fast_f((v0[j].y - m0) * rs0 * ga0.y + be0.y) * k + x0[j].y;
+        a.z = mish_fast_f((v0[j].z - m0) * rs0 * ga0.z + be0.z) * k + x0[j].z;
+        a.w = mish_fast_f((v0[j].w - m0) * rs0 * ga0.w + be0.w) * k + x0[j].w;
+        b.x = mish_fast_f((v1[j].x - m1) * rs1 * ga1.x + be1.x) * k + x1[j].x;
+        b.y = mish_fast_f((v1[j].y - m1) * rs1 * ga1.y + be1.y) * k + x1[j].y;
+        b.z = mish_fast_f((v1[j].z - m1) * rs1 * ga1.z + be1.z) * k + x1[j].z;
+        b.w = mish_fast_f((v1[j].w - m1) * rs1 * ga1.w + be1.w) * k + x1[j].w;
+        if (MODE == 0) {
+            *reinterpret_cast<uint2 *>(out16 + row * kC + c0) = make_uint2(pack16x2(a.x * k, a.y * k, f16), pack16x2(a.z * k, a.w * k, f16));
+            *reinterpret_cast<uint2 *>(out16 + row * kC + c1) = make_uint2(pack16x2(b.x * k, b.y * k, f16), pack16x2(b.z * k, b.w * k, f16));
+        } else {
+            *reinterpret_cast<float4 *>(out_f32 + row * kC + c0) = a;
+            *reinterpret_cast<float4 *>(out_f32 + row * kC + c1) = b;
+            float sum = (a.x + a.y) + (a.z + a.w) + (b.x + b.y) + (b.z + b.w);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            const float mean = sum * (1.0f / kC);
+            float d[8] = {a.x - mean, a.y - mean, a.z - mean, a.w - mean, b.x - mean, b.y - mean, b.z - mean, b.w - mean};
+            float q = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) q = fmaf(d[i], d[i], q);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+            const float rstd = rsqrtf(q * (1.0f / kC) + 1e-5f);
+            *reinterpret_cast<uint2 *>(out16 + row * kC + c0) =
+                make_uint2(pack16x2(d[0] * rstd * lg0.x + lb0.x, d[1] * rstd * lg0.y + lb0.y, f16),
+                           pack16x2(d[2] * rstd * lg0.z + lb0.z, d[3] * rstd * lg0.w + lb0.w, f16));
+            *reinterpret_cast<uint2 *>(out16 + row * kC + c1) =
+                make_uint2(pack16x2(d[4] * rstd * lg1.x + lb1.x, d[5] * rstd * lg1.y + lb1.y, f16),
+                           pack16x2(d[6] * rstd * lg1.z + lb1.z, d[7] * rstd * lg1.w + lb1.w, f16));
+        }
+    }
+}
+
 // ------------------------------------------------------------------ LayerNorm(256), eps 1e-5
 // one warp per row
 __global__ void __launch_bounds__(256)
@@ -597,12 +704,13 @@ resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__
 
 // dst[n][tap][0:cin_pad] = bf16(src[n][tap][0:cin]) zero-padded: GEMM weights for the tcgen05 path
 __global__ void __launch_bounds__(256)
-pack_weight_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int rows, int cin, int cin_pad, int f16) {
+pack_weight_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int rows, int cin, int cin_pad, int f16,
+                        int dst_stride) {
     const size_t n = (size_t)rows * cin_pad;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
         const size_t r = i / cin_pad;
         const int c = (int)(i % cin_pad);
-        dst[i] = pack16(c < cin ? src[r * cin + c] : 0.f, f16);
+        dst[r * dst_stride + c] = pack16(c < cin ? src[r * cin + c] : 0.f, f16);
     }
 }
 

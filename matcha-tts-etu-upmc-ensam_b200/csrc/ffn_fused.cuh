@@ -35,6 +35,7 @@ struct FfnArgs {
     float *out_f32;                    // fp32 [B][T][256] or nullptr
     __nv_bfloat16 *out_b16;            // 16-bit [B][T][256] or nullptr, rows multiplied by omask
     const float *omask; int omask_T;
+    int debug;
 };
 
 // erf-GELU for 16-bit outputs with ONE MUFU op: x * Phi(x) = h + h * tanh(x * p(x^2)), h = x / 2, with p the
@@ -53,6 +54,10 @@ __device__ __forceinline__ float gelu_tanh_fit_f(float x) {
 
 constexpr uint32_t kFfIdesc1F16 = (1u << 4) | ((uint32_t)(kFfChunk >> 3) << 17) | ((uint32_t)(kFfM >> 4) << 24);   // M128 N128
 constexpr uint32_t kFfIdesc1Bf16 = kFfIdesc1F16 | (1u << 7) | (1u << 10);
+
+// profiling aid (FfnArgs.debug): clock64 stamps of CTA 0 -- [0] start, [1] A landed, [2] acc2 complete, [3] end of the final
+// epilogue; [8 + 5c ..] chunk c in epilogue warp 0: acc1 ready, TMEM read, GELU done, H free, H written
+__device__ long long g_ffn_dbg[64];
 
 template <bool F16>
 __global__ void __launch_bounds__(kFfThreads, 1)
@@ -96,6 +101,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t tmem = *tmem_slot_p;
     const uint32_t tmem_acc2 = tmem, tmem_acc1 = tmem + 256;
     pdl_launch_dependents();
+    const bool dbg = g.debug && blockIdx.x == 0;
+    if (dbg && threadIdx.x == 0) g_ffn_dbg[0] = clock64();
 
     if (warp == 0) {
         // ============================ TMA producer ============================
@@ -123,11 +130,11 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
             for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
             stage_w1(1, 1);
-            for (int s = 2; s <= kFfNChunks; ++s) {
+            for (int s = 2; s < kFfNChunks; ++s) {            // same order as the MMA warp: FFN1 runs two chunks ahead of FFN2
+                stage_w1(s, 0); stage_w1(s, 1);
                 stage_w2(s - 2, 0); stage_w2(s - 2, 1);
-                if (s < kFfNChunks) { stage_w1(s, 0); stage_w1(s, 1); }
             }
-            stage_w2(kFfNChunks - 1, 0); stage_w2(kFfNChunks - 1, 1);
+            for (int c = kFfNChunks - 2; c < kFfNChunks; ++c) { stage_w2(c, 0); stage_w2(c, 1); }
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ============================
@@ -173,9 +180,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 umma_commit(bar_he + 8u * buf);
             };
             mbar_wait_parked(bar_a, 0, 500);
-            ffn1(0);
-            for (int s = 1; s < kFfNChunks; ++s) { ffn1(s); ffn2(s - 1); }
-            ffn2(kFfNChunks - 1);
+            // FFN1 runs two chunks ahead of FFN2: the GELU of chunk c has FFN2(c-2), FFN1(c+1), FFN2(c-1) and FFN1(c+2)
+            // (4 x 1024 tensor-pipe cycles) to finish before FFN2(c) needs H(c), so the epilogue warps are bound by their
+            // throughput, not by their latency
+            ffn1(0); ffn1(1);
+            for (int s = 2; s < kFfNChunks; ++s) { ffn1(s); ffn2(s - 2); }
+            ffn2(kFfNChunks - 2); ffn2(kFfNChunks - 1);
             umma_commit(bar_a2f);
         }
     } else {
@@ -187,13 +197,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
         // ---- GELU of every hidden chunk: 32 columns [32 cg, 32 cg + 32) of the chunk per warp
         const uint32_t hrow = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128);
+        // b1 is read through L1 (the few KB the 224 KB carve-out leaves): each warp's 128-byte line is prefetched two
+        // chunks ahead, so that the loads below do not pay the L2 round trip inside the chunk
+        if (lane < 2) asm volatile("prefetch.global.L1 [%0];" ::"l"(g.b1 + lane * kFfChunk + cg * 32));
         for (int c = 0; c < kFfNChunks; ++c) {
             const uint32_t buf = c & 1;
             const float4 *b1v = reinterpret_cast<const float4 *>(g.b1 + c * kFfChunk + cg * 32);
+            if (lane == 0 && c + 2 < kFfNChunks) asm volatile("prefetch.global.L1 [%0];" ::"l"(g.b1 + (c + 2) * kFfChunk + cg * 32));
             mbar_wait_parked(bar_a1f + 8u * buf, (c >> 1) & 1, 100);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const bool dw = dbg && threadIdx.x == 64;
+            if (dw) g_ffn_dbg[8 + 5 * c] = clock64();
             uint32_t v[32];
             tmem_ld32(tmem_acc1 + buf * kFfChunk + cg * 32 + lane_off, v);
+            if (dw) g_ffn_dbg[9 + 5 * c] = clock64();
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_a1e + 8u * buf);
@@ -208,7 +225,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 pk[2 * i] = pack16x2(y0, y1, F16);
                 pk[2 * i + 1] = pack16x2(y2, y3, F16);
             }
+            if (dw) g_ffn_dbg[10 + 5 * c] = clock64();
             if (c >= 2) mbar_wait_parked(bar_he + 8u * buf, ((c >> 1) - 1) & 1, 100);    // FFN2(c-2) has consumed H[buf]
+            if (dw) g_ffn_dbg[11 + 5 * c] = clock64();
             // columns [32 cg, +32) of the chunk = K-block cg / 2, 16-byte pieces 4 (cg & 1) .. +3 of the row
             const uint32_t hdst = base + kFfOffH + (2 * buf + (cg >> 1)) * kFfKb + hrow;
 #pragma unroll
@@ -220,12 +239,11 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_hf + 8u * buf);
+            if (dw) g_ffn_dbg[12 + 5 * c] = clock64();
         }
         // ---- final epilogue: columns [64 cg, 64 cg + 64) of acc2, transposed through shared memory (the A / H
         //      region is free: every MMA has completed) so that global accesses are row-contiguous
         pdl_wait();                                           // g.res is the predecessor chain's output
-        mbar_wait_parked(bar_a2f, 0, 200);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         float *tb = reinterpret_cast<float *>(gbase) + ew * (32 * kFfEpiPitch);
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         int orow[8];
@@ -237,13 +255,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             orow[i] = ok ? (int)(((long long)b * g.T + t) * kC) : -1;
             mk[i] = (ok && g.omask) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
         }
-#pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
+        float4 rv[8];
+        auto load_res = [&](int jj) {
             const int n = cg * 64 + jj * 32 + c4;
-            float4 rv[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i)
                 rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        load_res(0);                                          // in flight while the last FFN2 chunks complete
+        mbar_wait_parked(bar_a2f, 0, 200);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (dbg && threadIdx.x == 64) g_ffn_dbg[2] = clock64();
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int n = cg * 64 + jj * 32 + c4;
             const float4 bias = *reinterpret_cast<const float4 *>(g.b2 + n);
             uint32_t v[32];
             tmem_ld32(tmem_acc2 + cg * 64 + jj * 32 + lane_off, v);
@@ -257,6 +282,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int i = 0; i < 8; ++i) {
                 float4 x = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kFfEpiPitch + c4);
                 x.x += bias.x + rv[i].x; x.y += bias.y + rv[i].y; x.z += bias.z + rv[i].z; x.w += bias.w + rv[i].w;
+                if (jj == 0 && i == 7) load_res(1);
                 if (orow[i] >= 0) {
                     if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x;
                     if (g.out_b16)
@@ -266,6 +292,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
         }
     }
+    if (dbg && threadIdx.x == 64) g_ffn_dbg[3] = clock64();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {

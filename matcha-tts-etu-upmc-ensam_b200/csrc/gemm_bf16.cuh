@@ -51,6 +51,13 @@ struct GemmBf16Args {
     int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
     // GroupNorm statistics of the fp32 output (kGStats): [B][8 groups][sum, sum of squares], accumulated with atomics
     double *gstats;
+    // Second output block (Resnet1D: block1's conv and res_conv read the same input, decoder.py:81,85): the N tiles at
+    // columns >= n_split only walk K-blocks [kb2_begin, kb2_begin + kb2_count) (the centre tap), add bias2, write fp32
+    // to out2_f32 (pitch n_split) and take no GroupNorm sums.  n_split == 0: off.  Tiles are then dealt N-major,
+    // i.e. all the heavy tiles first.
+    int n_split, kb2_begin, kb2_count;
+    const float *bias2;
+    float *out2_f32;
 };
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
@@ -121,7 +128,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     const int chunks = g.c0_chunks + g.c1_chunks;
     const int n_kb = g.ntaps * chunks;
     const int n_tiles_n = g.N / kGN;
-    const int n_tiles = g.B * g.tiles_per_sample * n_tiles_n;
+    const int n_mtiles = g.B * g.tiles_per_sample;
+    const int n_tiles = n_mtiles * n_tiles_n;
+    auto tile_coords = [&](int tile, int &mt, int &n0) {
+        if (g.n_split) { const int nt = tile / n_mtiles; mt = tile - nt * n_mtiles; n0 = nt * kGN; }     // N-major
+        else { mt = tile / n_tiles_n; n0 = (tile - mt * n_tiles_n) * kGN; }
+    };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kGStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
@@ -149,9 +161,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         if (lane == 0) {
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                const int mt = tile / n_tiles_n, n0 = (tile - mt * n_tiles_n) * kGN;
+                int mt, n0;
+                tile_coords(tile, mt, n0);
                 const int b = mt / g.tiles_per_sample, t0 = (mt - b * g.tiles_per_sample) * kGM;
-                for (int kb = 0; kb < n_kb; ++kb, ++it) {
+                const bool light = g.n_split && n0 >= g.n_split;
+                const int kb_lo = light ? g.kb2_begin : 0, kb_hi = light ? g.kb2_begin + g.kb2_count : n_kb;
+                for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
                     const uint32_t s = it % kGStages;
                     mbar_wait_parked(bar_empty + 8u * s, ((it / kGStages) & 1) ^ 1, 1000);
                     const int tap = kb / chunks, ch = kb - tap * chunks;
@@ -170,9 +185,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             uint32_t it = 0, lt = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
                 const uint32_t acc = lt & 1;
+                int mt, n0;
+                tile_coords(tile, mt, n0);
+                const bool light = g.n_split && n0 >= g.n_split;
+                const int kb_lo = light ? g.kb2_begin : 0, kb_hi = light ? g.kb2_begin + g.kb2_count : n_kb;
                 mbar_wait_parked(bar_tempty + 8u * acc, ((lt >> 1) & 1) ^ 1, 1000);     // epilogue has drained it
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                for (int kb = 0; kb < n_kb; ++kb, ++it) {
+                for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
                     const uint32_t s = it % kGStages;
                     mbar_wait_parked(bar_full + 8u * s, (it / kGStages) & 1, 1000);
                     if (dbg && it == 0) g_gemm_dbg[1] = clock64();
@@ -181,7 +200,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sb);
 #pragma unroll
                     for (int k = 0; k < kGK / 16; ++k)     // 32 bytes along K per UMMA_K=16 step: +2 in 16-byte units
-                        umma_bf16(tmem_d + acc * kGN, da + 2u * k, db + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        umma_bf16(tmem_d + acc * kGN, da + 2u * k, db + 2u * k, idesc, (kb != kb_lo || k != 0) ? 1u : 0u);
                     umma_commit(bar_empty + 8u * s);        // frees the stage when these MMAs have read it
                 }
                 umma_commit(bar_tfull + 8u * acc);          // accumulator complete
@@ -198,8 +217,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         uint32_t lt = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
-            const int mt = tile / n_tiles_n, n0 = (tile - mt * n_tiles_n) * kGN;
+            int mt, n0;
+            tile_coords(tile, mt, n0);
             const int b = mt / g.tiles_per_sample, t0 = (mt - b * g.tiles_per_sample) * kGM;
+            const bool light = g.n_split && n0 >= g.n_split;
+            const int ldo = g.n_split ? g.n_split : g.N;              // output row pitch
+            const int ncol0 = light ? n0 - g.n_split : n0;             // column of the tile in its output block
+            float *const outp = light ? g.out2_f32 : g.out_f32;
+            const float *const biasp = light ? g.bias2 : g.bias;
             const uint32_t acc = lt & 1;
             const uint32_t tacc = tmem_d + acc * kGN + ((uint32_t)(32 * q) << 16);
             const int trow0 = t0 + 32 * q;
@@ -237,13 +262,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const int t = trow0 + 4 * i + rsub;
                     const bool ok = t < g.Tout;
                     const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
-                    orow[i] = ok ? (int)(r * g.N) : -1;
+                    orow[i] = ok ? (int)(r * ldo) : -1;
                     mk[i] = 1.0f;
                     if (B16 && g.omask && ok) mk[i] = g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
                 }
                 float4 rv[8];
                 auto load_res = [&](int jj) {                    // residual rows of chunk jj (issued one chunk ahead)
-                    const int n = n0 + 32 * jj + c4;
+                    const int n = ncol0 + 32 * jj + c4;
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
                         rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -271,9 +296,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                                         __uint_as_float(v[jj & 1][4 * i + 2]), __uint_as_float(v[jj & 1][4 * i + 3]));
                     __syncwarp();
                     if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[5] = clock64();
-                    const int n = n0 + 32 * j + c4;
+                    const int n = ncol0 + 32 * j + c4;
                     float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (g.bias) bias = *reinterpret_cast<const float4 *>(g.bias + n);
+                    if (biasp) bias = *reinterpret_cast<const float4 *>(biasp + n);
                     float4 x[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -283,7 +308,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         if (RES) { x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w; }
                     }
                     if (RES && jj + 1 < 4) load_res(j + 1);
-                    if (STATS) {
+                    if (STATS && !light) {
                         // the warp holds 32 rows x the 32 channels of GroupNorm group (n0 + 32 j) / 32 of sample b
                         float gs = 0.f, gq = 0.f;
 #pragma unroll
@@ -308,7 +333,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         if (orow[i] >= 0) {
-                            if (F32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x[i];
+                            if (F32) *reinterpret_cast<float4 *>(outp + orow[i] + n) = x[i];
                             if (B16)
                                 *reinterpret_cast<uint2 *>(g.out_bf16 + orow[i] + n) =
                                     make_uint2(pack16x2(x[i].x * mk[i], x[i].y * mk[i], F16), pack16x2(x[i].z * mk[i], x[i].w * mk[i], F16));

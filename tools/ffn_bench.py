@@ -33,3 +33,9 @@ for B, T in [(32, 800), (32, 400), (8, 800)]:
         us = e0.elapsed_time(e1) * 50
         fl = 4.0 * B * T * 256 * 1024
         print(f"B={B} T={T} {name}: {us:8.1f} us  {fl/us/1e6:7.1f} TFLOP/s")
+        if name == "fused":
+            buf = (ctypes.c_longlong * 64)(); lib.matcha_b200_debug_ffn_stamps(buf)
+            u = lambda i: (buf[i] - buf[0]) / 1965.0
+            print(f"   stamps us: A landed {u(1):.2f}  acc2 complete {u(2):.2f}  end {u(3):.2f}")
+            for c in range(8):
+                print(f"   chunk {c}: acc1 ready {u(8+5*c):6.2f}  tmem read {u(9+5*c):6.2f}  gelu {u(10+5*c):6.2f}  H free {u(11+5*c):6.2f}  H written {u(12+5*c):6.2f}")
