@@ -370,7 +370,8 @@ static bool ffn_use_fused() {
     return v != 0;
 }
 static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1, const bf16 *w2, const float *b2,
-                  const float *res, float *out_f32, bf16 *out_b16, bool omask) {
+                  const float *res, float *out_f32, bf16 *out_b16, bool omask, const float *ln_in = nullptr,
+                  const float *ln_g = nullptr, const float *ln_b = nullptr) {
     if (c.err) return;
     CUtensorMap ma, m1, m2;
     if (!tmap_for(c, a, 3, (uint64_t)kC, (uint64_t)T, (uint64_t)c.B, 64, kFfM, &ma)) return;
@@ -380,6 +381,7 @@ static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1,
     g.B = c.B; g.T = T; g.tiles_per_sample = (T + kFfM - 1) / kFfM;
     g.b1 = b1; g.b2 = b2; g.res = res; g.out_f32 = out_f32; g.out_b16 = out_b16;
     g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.debug = c.debug;
+    g.ln_in = ln_in; g.ln_g = ln_g; g.ln_b = ln_b;
     if ((long long)c.B * T * kC >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
     const int grid = c.B * g.tiles_per_sample;
     if (c.f16) launch(c, ffn_fused_kernel<true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, g);
@@ -410,10 +412,10 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
     gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
     attention_b(c, qkvb, w.attb, T);
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
-    launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
-    if (ffn_use_fused()) {
-        ffn_b(c, w.lnb, T, sb.w1, s.b1, sb.w2, s.b2, w.x2, out_f32, out_b16, true);
+    if (ffn_use_fused()) {      // norm3 is applied while the kernel builds its A operand
+        ffn_b(c, w.lnb, T, sb.w1, s.b1, sb.w2, s.b2, w.x2, out_f32, out_b16, true, w.x2, s.ln3g, s.ln3b);
     } else {
+        launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
         gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
         gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
     }
@@ -630,12 +632,14 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
 // test aid, not part of the public header: the fused feed-forward on caller-provided 16-bit operands
 extern "C" int matcha_b200_debug_ffn(const void *a16, const void *w1_16, const float *b1, const void *w2_16,
                                       const float *b2, const float *res, float *out_f32, void *out_16,
-                                      const float *mask, int B, int T, int f16, void *stream) {
+                                      const float *mask, int B, int T, int f16, void *stream, const float *ln_in,
+                                      const float *ln_g, const float *ln_b) {
     if (!a16 || !w1_16 || !w2_16 || !b1 || !b2 || !res || B < 1 || T < 1) return MB200_ERR_INVALID_ARG;
     Ctx c;
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16; c.debug = 1;
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
-    ffn_b(c, (const bf16 *)a16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, res, out_f32, (bf16 *)out_16, mask != nullptr);
+    ffn_b(c, (const bf16 *)a16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, res, out_f32, (bf16 *)out_16, mask != nullptr,
+          ln_in, ln_g, ln_b);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;

@@ -389,19 +389,6 @@ gn_mish_rows_kernel(const float *__restrict__ h, const double *__restrict__ gsum
     const size_t rows = (size_t)B * T;
     const size_t r0 = (size_t)blockIdx.x * kGmRowsPerBlock;
     const int b0 = (int)(r0 / T);
-    {
-        const int bb = b0 + (int)(threadIdx.x >> 3), gi = threadIdx.x & 7;
-        const size_t r_last = r0 + kGmRowsPerBlock - 1 < rows ? r0 + kGmRowsPerBlock - 1 : rows - 1;
-        if (bb <= (int)(r_last / T)) {
-            const double inv_n = 1.0 / ((double)T * kGroupCh);
-            const double m = gsum[(bb * kGroups + gi) * 2] * inv_n;
-            double var = gsum[(bb * kGroups + gi) * 2 + 1] * inv_n - m * m;
-            if (var < 0.0) var = 0.0;
-            s_stat[bb - b0][gi][0] = (float)m;
-            s_stat[bb - b0][gi][1] = 1.0f / sqrtf((float)var + 1e-5f);
-        }
-    }
-    __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c0 = lane * 4, c1 = 128 + lane * 4, g0 = lane >> 3, g1 = 4 + (lane >> 3);
     const float4 ga0 = *reinterpret_cast<const float4 *>(gamma + c0), ga1 = *reinterpret_cast<const float4 *>(gamma + c1);
@@ -428,6 +415,20 @@ gn_mish_rows_kernel(const float *__restrict__ h, const double *__restrict__ gsum
             x0[j] = x1[j] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
+    // the GroupNorm sums are read after the row loads have been issued: both L2 round trips overlap
+    {
+        const int bb = b0 + (int)(threadIdx.x >> 3), gi = threadIdx.x & 7;
+        const size_t r_last = r0 + kGmRowsPerBlock - 1 < rows ? r0 + kGmRowsPerBlock - 1 : rows - 1;
+        if (bb <= (int)(r_last / T)) {
+            const double inv_n = 1.0 / ((double)T * kGroupCh);
+            const double m = gsum[(bb * kGroups + gi) * 2] * inv_n;
+            double var = gsum[(bb * kGroups + gi) * 2 + 1] * inv_n - m * m;
+            if (var < 0.0) var = 0.0;
+            s_stat[bb - b0][gi][0] = (float)m;
+            s_stat[bb - b0][gi][1] = 1.0f / sqrtf((float)var + 1e-5f);
+        }
+    }
+    __syncthreads();
     float4 lg0, lg1, lb0, lb1;
     if (MODE == 1) {
         lg0 = *reinterpret_cast<const float4 *>(ln_g + c0); lg1 = *reinterpret_cast<const float4 *>(ln_g + c1);

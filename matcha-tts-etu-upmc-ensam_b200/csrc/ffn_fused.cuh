@@ -35,6 +35,10 @@ struct FfnArgs {
     float *out_f32;                    // fp32 [B][T][256] or nullptr
     __nv_bfloat16 *out_b16;            // 16-bit [B][T][256] or nullptr, rows multiplied by omask
     const float *omask; int omask_T;
+    // norm3 of the transformer block (transformer.py:352) folded in: when ln_in != nullptr the A operand is
+    // LayerNorm(ln_in rows) * ln_g + ln_b, built in shared memory by the epilogue warps (idle until the first FFN1
+    // chunk completes) instead of arriving by TMA
+    const float *ln_in, *ln_g, *ln_b;
     int debug;
 };
 
@@ -82,7 +86,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x - b * g.tiles_per_sample) * kFfM;
 
     if (threadIdx.x == 0) {
-        mbar_init(bar_a, 1u); mbar_init(bar_a2f, 1u);
+        mbar_init(bar_a, g.ln_in ? (uint32_t)kFfEpiWarps : 1u); mbar_init(bar_a2f, 1u);
         for (int s = 0; s < kFfStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_a1f + 8u * a, 1u); mbar_init(bar_a1e + 8u * a, kFfEpiWarps);
@@ -127,8 +131,10 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // the weights do not depend on the predecessor kernel: the first stages are in flight before the wait
             stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
             pdl_wait();
-            mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
-            for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
+            if (!g.ln_in) {
+                mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
+                for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
+            }
             stage_w1(1, 1);
             for (int s = 2; s < kFfNChunks; ++s) {            // same order as the MMA warp: FFN1 runs two chunks ahead of FFN2
                 stage_w1(s, 0); stage_w1(s, 1);
@@ -195,6 +201,54 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int cg = ew >> 2;                              // column group
         const int row = 32 * q + lane;                       // tile row = TMEM lane
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
+        if (g.ln_in) {
+            // ---- A = LayerNorm(256, eps 1e-5) of the tile's rows, one warp per row (8 rows per warp, 4 in flight),
+            //      written 16-bit into the four 128B-swizzled K-blocks the UMMA descriptors expect
+            pdl_wait();
+            const float4 lg0 = *reinterpret_cast<const float4 *>(g.ln_g + lane * 4), lg1 = *reinterpret_cast<const float4 *>(g.ln_g + 128 + lane * 4);
+            const float4 lb0 = *reinterpret_cast<const float4 *>(g.ln_b + lane * 4), lb1 = *reinterpret_cast<const float4 *>(g.ln_b + 128 + lane * 4);
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                float4 xa[4], xb[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = ew * 8 + half * 4 + j;
+                    const bool ok = t0 + r < g.T;
+                    const float *px = g.ln_in + ((size_t)b * g.T + t0 + r) * kC;
+                    xa[j] = ok ? *reinterpret_cast<const float4 *>(px + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    xb[j] = ok ? *reinterpret_cast<const float4 *>(px + 128 + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = ew * 8 + half * 4 + j;
+                    float sum = (xa[j].x + xa[j].y) + (xa[j].z + xa[j].w) + (xb[j].x + xb[j].y) + (xb[j].z + xb[j].w);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    const float mean = sum * (1.0f / kC);
+                    float d[8] = {xa[j].x - mean, xa[j].y - mean, xa[j].z - mean, xa[j].w - mean,
+                                  xb[j].x - mean, xb[j].y - mean, xb[j].z - mean, xb[j].w - mean};
+                    float qq = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) qq = fmaf(d[i], d[i], qq);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) qq += __shfl_xor_sync(0xffffffffu, qq, o);
+                    const float rstd = rsqrtf(qq * (1.0f / kC) + 1e-5f);
+                    const bool ok = t0 + r < g.T;             // rows beyond T are zeros, as the TMA path delivers them
+                    const uint32_t p0 = ok ? pack16x2(d[0] * rstd * lg0.x + lb0.x, d[1] * rstd * lg0.y + lb0.y, F16) : 0u;
+                    const uint32_t p1 = ok ? pack16x2(d[2] * rstd * lg0.z + lb0.z, d[3] * rstd * lg0.w + lb0.w, F16) : 0u;
+                    const uint32_t p2 = ok ? pack16x2(d[4] * rstd * lg1.x + lb1.x, d[5] * rstd * lg1.y + lb1.y, F16) : 0u;
+                    const uint32_t p3 = ok ? pack16x2(d[6] * rstd * lg1.z + lb1.z, d[7] * rstd * lg1.w + lb1.w, F16) : 0u;
+                    // channels 4 lane .. +3: K-block lane / 16, 16-byte piece (lane % 16) / 2 (swizzled), half (lane & 1)
+                    const uint32_t dst = base + kFfOffA + (uint32_t)(lane >> 4) * kFfKb + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128) +
+                                         (((uint32_t)((lane & 15) >> 1) ^ (uint32_t)(r & 7)) << 4) + (uint32_t)(lane & 1) * 8u;
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(dst), "r"(p0), "r"(p1) : "memory");
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(dst + 2u * kFfKb), "r"(p2), "r"(p3) : "memory");
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_a);
+        }
         // ---- GELU of every hidden chunk: 32 columns [32 cg, 32 cg + 32) of the chunk per warp
         const uint32_t hrow = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128);
         // b1 is read through L1 (the few KB the 224 KB carve-out leaves): each warp's 128-byte line is prefetched two

@@ -10,15 +10,16 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def run_ffn(a, w1, b1, w2, b2, res, mask, f16, want_f32=True, want_16=True):
+def run_ffn(a, w1, b1, w2, b2, res, mask, f16, want_f32=True, want_16=True, ln=None):
     from matcha_b200._lib import check, load_library
     lib = load_library()
     B, T, _ = a.shape
     out = torch.full((B, T, 256), float("nan"), device="cuda") if want_f32 else None
     out16 = torch.zeros((B, T, 256), device="cuda", dtype=a.dtype) if want_16 else None
     p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    ln_in, ln_g, ln_b = ln if ln is not None else (None, None, None)
     check(lib.matcha_b200_debug_ffn(p(a), p(w1), p(b1), p(w2), p(b2), p(res), p(out), p(out16), p(mask), B, T, int(f16),
-                                    ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "debug_ffn")
+                                    ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), p(ln_in), p(ln_g), p(ln_b)), "debug_ffn")
     torch.cuda.synchronize()
     return out, out16
 
@@ -68,3 +69,22 @@ def test_ffn_only_16bit_output_and_large_activations():
     want, _ = reference(a, w1, b1, w2, b2, res)
     assert out is None
     assert rel(out16.float(), want) < 1e-3
+
+
+@pytest.mark.parametrize("B,T", [(2, 200), (1, 131), (3, 64)])
+def test_ffn_with_layernorm_folded_in(B, T):
+    """norm3 + FeedForward + residual (transformer.py:352-366): the kernel builds its A operand from the fp32 rows."""
+    g = torch.Generator(device="cuda").manual_seed(T)
+    x = torch.randn(B, T, 256, device="cuda", generator=g) * 1.7 + 0.3
+    ln_g = 1 + 0.2 * torch.randn(256, device="cuda", generator=g)
+    ln_b = 0.1 * torch.randn(256, device="cuda", generator=g)
+    w1 = (torch.randn(1024, 256, device="cuda", generator=g) * 0.09).half()
+    w2 = (torch.randn(256, 1024, device="cuda", generator=g) * 0.044).half()
+    b1 = torch.randn(1024, device="cuda", generator=g) * 0.5
+    b2 = torch.randn(256, device="cuda", generator=g)
+    dummy = torch.zeros(B, T, 256, device="cuda", dtype=torch.float16)
+    out, _ = run_ffn(dummy, w1, b1, w2, b2, x, None, True, want_16=False, ln=(x, ln_g, ln_b))
+    a = torch.nn.functional.layer_norm(x, (256,), ln_g, ln_b, 1e-5)
+    want, want_term = reference(a.half(), w1, b1, w2, b2, x)
+    assert rel(out - x, want_term) < 8e-4
+    assert rel(out, want) < 6e-4

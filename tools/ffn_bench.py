@@ -20,7 +20,7 @@ for B, T in [(32, 800), (32, 400), (8, 800)]:
     hid = torch.empty(B, T, 1024, device="cuda", dtype=torch.float16)
     tap = (ctypes.c_int * 1)(0)
     def fused():
-        check(lib.matcha_b200_debug_ffn(p(a), p(w1), p(b1), p(w2), p(b2), p(res), p(out), p(out16), p(mask), B, T, 1, st), "ffn")
+        check(lib.matcha_b200_debug_ffn(p(a), p(w1), p(b1), p(w2), p(b2), p(res), p(out), p(out16), p(mask), B, T, 1, st, p(res), p(b2), p(b2)), "ffn")
     def split():
         check(lib.matcha_b200_debug_gemm_bf16(p(a), 256, None, 0, 1, tap, B, T, p(w1), 1024, p(b1), 1, None, None, p(hid), None, st), "g1")
         check(lib.matcha_b200_debug_gemm_bf16(p(hid), 1024, None, 0, 1, tap, B, T, p(w2), 256, p(b2), 0, p(res), p(out), p(out16), p(mask), st), "g2")
