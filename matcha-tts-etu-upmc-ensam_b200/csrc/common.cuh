@@ -36,6 +36,8 @@ int encode_tmap_2d_f32(CUtensorMap *map, const void *base, uint64_t rows, uint64
 int encode_tmap_bf16(CUtensorMap *map, const void *base, int ndim, const uint64_t *dims,
                      const uint64_t *strides_bytes, const uint32_t *box);
 
+int encode_tmap_out(CUtensorMap *map, const void *base, int is_f32, const uint64_t *dims, const uint64_t *strides_bytes);
+
 // ---------------------------------------------------------------- device side
 #ifdef __CUDACC__
 
@@ -88,6 +90,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c_inner), "r"(c_outer) : "memory");
 }
+// TMA store of one 3-D box shared -> global (bulk async-group completion); rows / columns outside the tensor are clipped.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"((uint64_t)map), "r"(src), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)map) : "memory");
 }

@@ -273,8 +273,26 @@ static bool tmap_for(Ctx &c, const bf16 *base, int ndim, uint64_t d0, uint64_t d
     return true;
 }
 
+// Output map for the TMA-store epilogue: rows [B][T][pitch] of fp32 or 16-bit elements, row t of the tile grid at
+// row t * row_stride of the tensor (ConvTranspose phases write every other row).
+static bool tmap_out_for(Ctx &c, const void *base, bool f32, int ncols, int pitch, int T, int out_T, int row_stride, CUtensorMap *out) {
+    const uint64_t key1 = (uint64_t)pitch * 8 + (f32 ? 1 : 0) + 2 + (uint64_t)row_stride * 4;
+    for (auto &e : c.tmaps)
+        if (e.base == base && e.d0 == (uint64_t)ncols && e.d1 == (uint64_t)T && e.b1 == 0xffffffffu - (uint32_t)key1) { *out = e.map; return true; }
+    TmapEntry e;
+    e.base = base; e.d0 = (uint64_t)ncols; e.d1 = (uint64_t)T; e.b1 = 0xffffffffu - (uint32_t)key1;
+    const uint64_t es = f32 ? 4 : 2;
+    const uint64_t dims[3] = {(uint64_t)ncols, (uint64_t)T, (uint64_t)c.B};
+    const uint64_t strides[2] = {(uint64_t)pitch * row_stride * es, (uint64_t)pitch * out_T * es};
+    const int rc = encode_tmap_out(&e.map, base, f32 ? 1 : 0, dims, strides);
+    if (rc != MB200_OK) { c.err = rc; return false; }
+    c.tmaps.push_back(e);
+    *out = e.map;
+    return true;
+}
+
 // The epilogue variants that exist (gemm_bf16.cuh: everything about the outputs is a template parameter).
-typedef void (*GemmKernel)(CUtensorMap, CUtensorMap, CUtensorMap, GemmBf16Args);
+typedef void (*GemmKernel)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmBf16Args);
 template <int EPI, int FLAGS>
 static GemmKernel gemm_variant(bool f16) { return f16 ? (GemmKernel)gemm_bf16_kernel<EPI, FLAGS, true> : (GemmKernel)gemm_bf16_kernel<EPI, FLAGS, false>; }
 static GemmKernel pick_gemm(int epi, int flags, bool f16) {
@@ -335,7 +353,16 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     const int flags = (res ? kGRes : 0) | (out_f32 ? kGF32 : 0) | (out_b16 ? kGB16 : 0) | (gstats ? kGStats : 0);
     const GemmKernel k = pick_gemm(g.fin_n > 0 ? 2 : act, g.fin_n > 0 ? 0 : flags, c.f16 != 0);
     if (!k) { c.err = MB200_ERR_UNSUPPORTED; return; }
-    launch(c, k, grid, kGThreads, kGSmemBytes, ma0, ma1, mb, g);
+    // TMA-store epilogue (one output, no residual): output tensor maps
+    CUtensorMap mo = ma0, mo2 = ma0;
+    if (g.fin_n == 0 && !res && ((out_f32 != nullptr) != (out_b16 != nullptr))) {
+        if (N > kGBiasBytes / 4) { c.err = MB200_ERR_UNSUPPORTED; return; }
+        const int pitch = g.n_split ? g.n_split : N;
+        const void *ob = out_f32 ? (const void *)(out_f32 + (size_t)g.out_off * pitch) : (const void *)(out_b16 + (size_t)g.out_off * pitch);
+        if (!tmap_out_for(c, ob, out_f32 != nullptr, pitch, pitch, T, g.out_T, g.out_stride, &mo)) return;
+        if (g.n_split && !tmap_out_for(c, out2_f32, true, pitch, pitch, T, g.out_T, g.out_stride, &mo2)) return;
+    }
+    launch(c, k, grid, kGThreads, kGSmemBytes, ma0, ma1, mb, mo, mo2, g);
 }
 
 // softmax(q k^T / 8 + mask) v on 16-bit q|k|v rows: tcgen05 kernel (attention_tc.cuh); MB200_ATTN=mma selects the

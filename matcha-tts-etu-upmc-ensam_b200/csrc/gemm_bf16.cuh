@@ -28,8 +28,10 @@ constexpr int kGStageA = kGM * kGK * 2, kGStageB = kGN * kGK * 2;
 constexpr int kGStageBytes = kGStageA + kGStageB;      // 48 KB
 constexpr int kGEpiWarps = 8;                          // two warps per TMEM lane quarter, four 32-column chunks each
 constexpr int kGEpiPitch = 36;                         // floats; 16-byte aligned rows, conflict-free both ways
-constexpr int kGEpiBytes = kGEpiWarps * 32 * kGEpiPitch * 4;    // per-warp transpose buffers
-constexpr int kGSmemBytes = kGStages * kGStageBytes + kGEpiBytes + 256 + 1024;
+constexpr int kGEpiWarpBytes = 8192;                   // per epilogue warp: two 4 KB TMA-store staging tiles, or the transpose buffer
+constexpr int kGEpiBytes = kGEpiWarps * kGEpiWarpBytes;
+constexpr int kGBiasBytes = 4096;                      // bias of every output column (N <= 1024)
+constexpr int kGSmemBytes = kGStages * kGStageBytes + kGEpiBytes + kGBiasBytes + 256 + 1024;
 constexpr int kGThreads = 32 * (2 + kGEpiWarps);
 
 struct GemmBf16Args {
@@ -111,18 +113,23 @@ constexpr int kGRes = 1, kGF32 = 2, kGB16 = 4, kGStats = 8;
 template <int EPI, int FLAGS, bool F16>
 __global__ void __launch_bounds__(kGThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-                 const __grid_constant__ CUtensorMap tmB, const GemmBf16Args g) {
+                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                 const __grid_constant__ CUtensorMap tmO2, const GemmBf16Args g) {
     constexpr bool RES = (FLAGS & kGRes) != 0, F32 = (FLAGS & kGF32) != 0, B16 = (FLAGS & kGB16) != 0, STATS = (FLAGS & kGStats) != 0;
+    // Variants with exactly one output and no residual stay in the TMEM layout (thread = row) and leave through
+    // 128B/64B-swizzled staging tiles and TMA stores; the others transpose through shared memory (below).
+    constexpr bool TMA_EPI = EPI != 2 && !RES && (F32 != B16);
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
     const uint32_t epi_off = kGStages * kGStageBytes;
-    const uint32_t bar_full = base + epi_off + kGEpiBytes;          // [kGStages]  TMA -> MMA
+    float *const sbias = reinterpret_cast<float *>(gbase + epi_off + kGEpiBytes);
+    const uint32_t bar_full = base + epi_off + kGEpiBytes + kGBiasBytes;     // [kGStages]  TMA -> MMA
     const uint32_t bar_empty = bar_full + 8u * kGStages;            // [kGStages]  MMA -> TMA
     const uint32_t bar_tfull = bar_empty + 8u * kGStages;           // [2] accumulator ready   MMA -> epilogue
     const uint32_t bar_tempty = bar_tfull + 16u;                    // [2] accumulator drained epilogue -> MMA
     const uint32_t tmem_slot = bar_tempty + 16u;                    // u32 written by tcgen05.alloc
-    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + epi_off + kGEpiBytes + 16 * kGStages + 32);
+    volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_slot - base));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int chunks = g.c0_chunks + g.c1_chunks;
@@ -213,7 +220,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         const int ew = warp - 2;
         const int q = warp & 3;                         // TMEM lane quarter this warp may touch
         const int jhalf = (ew >> 2) * 4;                // this warp's four 32-column chunks
-        float *tb = reinterpret_cast<float *>(gbase + epi_off) + ew * (32 * kGEpiPitch);
+        float *tb = reinterpret_cast<float *>(gbase + epi_off + ew * kGEpiWarpBytes);
+        const uint32_t stg = base + epi_off + ew * kGEpiWarpBytes;
+        uint32_t n_st = 0;                              // TMA stores issued by this warp
+        if (TMA_EPI) {
+            // every output column's bias once per CTA (weights: no dependency on the predecessor kernel)
+            for (int i = threadIdx.x - 64; i < g.N; i += 32 * kGEpiWarps) {
+                float bv = 0.f;
+                if (g.n_split && i >= g.n_split) { if (g.bias2) bv = g.bias2[i - g.n_split]; }
+                else if (g.bias) bv = g.bias[i];
+                sbias[i] = bv;
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * kGEpiWarps) : "memory");
+            if (lane == 0) { tma_prefetch_desc(&tmO); if (g.n_split) tma_prefetch_desc(&tmO2); }
+        }
         const int rsub = lane >> 3, c4 = (lane & 7) * 4;
         uint32_t lt = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
@@ -231,7 +251,79 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             mbar_wait_parked(bar_tfull + 8u * acc, (lt >> 1) & 1, 2000);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (dbg && lt == 0 && threadIdx.x == 64) g_gemm_dbg[2] = clock64();
-            if (EPI == 2) {
+            if (TMA_EPI) {
+                const int t = trow0 + lane;                     // this thread's output row (TMEM lane)
+                const bool valid = t < g.Tout;
+                float mk = 1.0f;
+                if (B16 && g.omask && valid) mk = g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
+                const CUtensorMap *const om = light ? &tmO2 : &tmO;
+                uint32_t v[2][32];
+                tmem_ld32_issue(tacc + 32 * jhalf, v[0]);
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    const int j = jhalf + jj;
+                    tmem_ld_wait();
+                    if (jj + 1 < 4) tmem_ld32_issue(tacc + 32 * (j + 1), v[(jj + 1) & 1]);
+                    else {
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_tempty + 8u * acc);
+                    }
+                    const float4 *bp = reinterpret_cast<const float4 *>(sbias + n0 + 32 * j);     // broadcast reads
+                    float x[32];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 bb = bp[i];
+                        x[4 * i] = __uint_as_float(v[jj & 1][4 * i]) + bb.x; x[4 * i + 1] = __uint_as_float(v[jj & 1][4 * i + 1]) + bb.y;
+                        x[4 * i + 2] = __uint_as_float(v[jj & 1][4 * i + 2]) + bb.z; x[4 * i + 3] = __uint_as_float(v[jj & 1][4 * i + 3]) + bb.w;
+                    }
+                    if (EPI == 1) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) x[i] = gelu_erf_fast_f(x[i]);
+                    }
+                    if (STATS && !light) {
+                        // this chunk's 32 columns are GroupNorm group (n0 + 32 j) / 32 of sample b: row sums, then the warp
+                        float gs[4] = {0.f, 0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) { gs[i & 3] += x[i]; gq[i & 3] = fmaf(x[i], x[i], gq[i & 3]); }
+                        float s1 = valid ? (gs[0] + gs[1]) + (gs[2] + gs[3]) : 0.f, s2 = valid ? (gq[0] + gq[1]) + (gq[2] + gq[3]) : 0.f;
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+                        }
+                        if (lane == 0) {
+                            double *gp = g.gstats + ((size_t)b * kGroups + (n0 + 32 * j) / kGroupCh) * 2;
+                            atomicAdd(gp, (double)s1);
+                            atomicAdd(gp + 1, (double)s2);
+                        }
+                    }
+                    // staging tile (n_st & 1): free once the store issued two chunks ago has read it
+                    if (lane == 0) tma_store_wait_read<1>();
+                    __syncwarp();
+                    const uint32_t sbuf = stg + (n_st & 1u) * 4096u;
+                    if (F32) {                                  // [32 rows][128 B], 16-byte pieces swizzled by row & 7
+                        const uint32_t srow = sbuf + (uint32_t)lane * 128u;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            sts128(srow + (((uint32_t)i ^ (uint32_t)(lane & 7)) << 4), make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]));
+                    } else {                                    // [32 rows][64 B], pieces swizzled by (row >> 1) & 3
+                        const uint32_t srow = sbuf + (uint32_t)lane * 64u;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(srow + (((uint32_t)i ^ (uint32_t)((lane >> 1) & 3)) << 4)),
+                                         "r"(pack16x2(x[8 * i] * mk, x[8 * i + 1] * mk, F16)), "r"(pack16x2(x[8 * i + 2] * mk, x[8 * i + 3] * mk, F16)),
+                                         "r"(pack16x2(x[8 * i + 4] * mk, x[8 * i + 5] * mk, F16)), "r"(pack16x2(x[8 * i + 6] * mk, x[8 * i + 7] * mk, F16)) : "memory");
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_3d(om, sbuf, ncol0 + 32 * j, trow0, b);     // rows >= Tout are clipped by the map
+                        tma_store_commit();
+                    }
+                    ++n_st;
+                }
+            } else if (EPI == 2) {
                 // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
                 const int t = trow0 + lane;
                 const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
@@ -350,6 +442,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             }
             if (dbg && lt == 0 && threadIdx.x == 64) g_gemm_dbg[3] = clock64();
         }
+        if (TMA_EPI && lane == 0) tma_store_wait_all();        // shared memory must outlive the stores' reads
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
