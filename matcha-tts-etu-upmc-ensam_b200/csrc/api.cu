@@ -64,15 +64,17 @@ int encode_tmap_bf16(CUtensorMap *map, const void *base, int ndim, const uint64_
     return MB200_OK;
 }
 
-// Output tensor map for TMA stores from a [32 rows][32 columns] staging tile: fp32 (128-byte rows, 128B swizzle) or
-// 16-bit (64-byte rows, 64B swizzle); 3-D [d2][d1][d0] with byte strides.
-int encode_tmap_out(CUtensorMap *map, const void *base, int is_f32, const uint64_t *dims, const uint64_t *strides_bytes) {
+// Output tensor map for TMA stores from a [32 rows][box_cols] staging tile with 128-byte rows (128B swizzle) or 64-byte
+// rows (64B swizzle), fp32 or 16-bit elements; 3-D [d2][d1][d0] with byte strides.
+int encode_tmap_out(CUtensorMap *map, const void *base, int is_f32, const uint64_t *dims, const uint64_t *strides_bytes,
+                    int box_cols) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return MB200_ERR_NO_DEVICE;
     cuuint64_t d[3] = {dims[0], dims[1], dims[2]}, st[2] = {strides_bytes[0], strides_bytes[1]};
-    cuuint32_t bx[3] = {32, 32, 1}, es[3] = {1, 1, 1};
+    cuuint32_t bx[3] = {(cuuint32_t)box_cols, 32, 1}, es[3] = {1, 1, 1};
+    const bool sw128 = box_cols * (is_f32 ? 4 : 2) == 128;
     CUresult r = fn(map, is_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(base),
-                    d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, is_f32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                    d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         g_last_cuda_error = (int)r;

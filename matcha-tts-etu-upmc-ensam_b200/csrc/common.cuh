@@ -36,7 +36,8 @@ int encode_tmap_2d_f32(CUtensorMap *map, const void *base, uint64_t rows, uint64
 int encode_tmap_bf16(CUtensorMap *map, const void *base, int ndim, const uint64_t *dims,
                      const uint64_t *strides_bytes, const uint32_t *box);
 
-int encode_tmap_out(CUtensorMap *map, const void *base, int is_f32, const uint64_t *dims, const uint64_t *strides_bytes);
+int encode_tmap_out(CUtensorMap *map, const void *base, int is_f32, const uint64_t *dims, const uint64_t *strides_bytes,
+                    int box_cols);
 
 // ---------------------------------------------------------------- device side
 #ifdef __CUDACC__

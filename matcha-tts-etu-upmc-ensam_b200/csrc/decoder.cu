@@ -16,6 +16,7 @@
 #include "attention_mma.cuh"
 #include "attention_tc.cuh"
 #include "ffn_fused.cuh"
+#include "gemm_abuild.cuh"
 #include "gemm_bf16.cuh"
 
 namespace mb200 {
@@ -275,8 +276,9 @@ static bool tmap_for(Ctx &c, const bf16 *base, int ndim, uint64_t d0, uint64_t d
 
 // Output map for the TMA-store epilogue: rows [B][T][pitch] of fp32 or 16-bit elements, row t of the tile grid at
 // row t * row_stride of the tensor (ConvTranspose phases write every other row).
-static bool tmap_out_for(Ctx &c, const void *base, bool f32, int ncols, int pitch, int T, int out_T, int row_stride, CUtensorMap *out) {
-    const uint64_t key1 = (uint64_t)pitch * 8 + (f32 ? 1 : 0) + 2 + (uint64_t)row_stride * 4;
+static bool tmap_out_for(Ctx &c, const void *base, bool f32, int ncols, int pitch, int T, int out_T, int row_stride, CUtensorMap *out,
+                         int box_cols = 32) {
+    const uint64_t key1 = (uint64_t)pitch * 8 + (f32 ? 1 : 0) + 2 + (uint64_t)row_stride * 4 + (uint64_t)box_cols * 65536;
     for (auto &e : c.tmaps)
         if (e.base == base && e.d0 == (uint64_t)ncols && e.d1 == (uint64_t)T && e.b1 == 0xffffffffu - (uint32_t)key1) { *out = e.map; return true; }
     TmapEntry e;
@@ -284,7 +286,7 @@ static bool tmap_out_for(Ctx &c, const void *base, bool f32, int ncols, int pitc
     const uint64_t es = f32 ? 4 : 2;
     const uint64_t dims[3] = {(uint64_t)ncols, (uint64_t)T, (uint64_t)c.B};
     const uint64_t strides[2] = {(uint64_t)pitch * row_stride * es, (uint64_t)pitch * out_T * es};
-    const int rc = encode_tmap_out(&e.map, base, f32 ? 1 : 0, dims, strides);
+    const int rc = encode_tmap_out(&e.map, base, f32 ? 1 : 0, dims, strides, box_cols);
     if (rc != MB200_OK) { c.err = rc; return false; }
     c.tmaps.push_back(e);
     *out = e.map;
@@ -317,6 +319,10 @@ static int gemm_set_attributes() {
                 const GemmKernel k = pick_gemm(epi, flags, f16 != 0);
                 if (k) MB200_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
             }
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
     MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
     MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
     return MB200_OK;
@@ -390,6 +396,43 @@ static void attention_b(Ctx &c, const bf16 *qkvb, bf16 *out, int T) {
     else launch(c, attention_mma_kernel<false>, agrid, 128, kFaSmemBytes, qkvb, c.mask, c.T, out, T);
 }
 
+// GEMMs that build their A operand from fp32 rows (gemm_abuild.cuh).  MB200_ABUILD=0 keeps the separate GroupNorm / Mish /
+// LayerNorm launches; MB200_ABUILD_DESC=1 sets the descriptor base-offset field of the shifted conv views (experiment: wrong results on
+// sm_100a -- the swizzle is applied to absolute shared-memory address bits, a row-shifted start address needs no hint).
+static int abuild_env(const char *name, int dflt) {
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+static bool abuild_enabled() { static int v = -1; if (v < 0) v = abuild_env("MB200_ABUILD", 1); return v != 0; }
+// mode 1: x1 = Mish(GN(h)) * mask + r, out16 = LN(x1) W^T (N = 768).  mode 2: out_f32 = conv3(Mish(GN(h)) * mask + tb) + bias + sums
+static void abuild_b(Ctx &c, int mode, const float *h, const double *gsum, const float *gamma, const float *beta, int T,
+                     const float *tb, int tb_per_sample, const float *r, const float *ln_g, const float *ln_b, float *x1,
+                     const bf16 *w, int N, const float *bias, bf16 *out16, float *out_f32, double *gstats) {
+    if (c.err) return;
+    static int desc_mode = -1;
+    if (desc_mode < 0) desc_mode = abuild_env("MB200_ABUILD_DESC", 0);
+    CUtensorMap mb, mo;
+    const int K = mode == 2 ? 3 * kC : kC;
+    if (!tmap_for(c, w, 2, (uint64_t)K, (uint64_t)N, 1, kGK, kGN, &mb)) return;
+    if (mode == 1) { if (!tmap_out_for(c, out16, false, N, N, T, T, 1, &mo, 32)) return; }
+    else if (!tmap_out_for(c, out_f32, true, N, N, T, T, 1, &mo, 16)) return;
+    AbuildArgs g;
+    g.B = c.B; g.T = T; g.tiles_per_sample = (T + kGM - 1) / kGM; g.N = N;
+    g.h = h; g.gsum = gsum; g.gamma = gamma; g.beta = beta; g.mask = c.mask; g.mask_T = c.T;
+    g.tb = tb; g.tb_per_sample = tb_per_sample; g.r = r; g.ln_g = ln_g; g.ln_b = ln_b; g.x1 = x1;
+    g.bias = bias; g.gstats = gstats; g.desc_mode = desc_mode;
+    if (N > 1024 || (long long)c.B * T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
+    const int n_mtiles = c.B * g.tiles_per_sample;
+    const int grid = n_mtiles < kNumSMsB200 ? n_mtiles : kNumSMsB200;
+    if (mode == 1) {
+        if (c.f16) launch(c, gemm_abuild_kernel<1, true>, grid, kAbThreads, kAbSmemBytes, mb, mo, g);
+        else launch(c, gemm_abuild_kernel<1, false>, grid, kAbThreads, kAbSmemBytes, mb, mo, g);
+    } else {
+        if (c.f16) launch(c, gemm_abuild_kernel<2, true>, grid, kAbThreads, kAbSmemBytes, mb, mo, g);
+        else launch(c, gemm_abuild_kernel<2, false>, grid, kAbThreads, kAbSmemBytes, mb, mo, g);
+    }
+}
+
 // out = res + W2 gelu(W1 a + b1) + b2 in one kernel (ffn_fused.cuh); MB200_FFN=split keeps the two-GEMM path.
 static bool ffn_use_fused() {
     static int v = -1;
@@ -429,14 +472,22 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
     const int chunks = (c0 + c1) / kGK;
     gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, 2 * kC, s.bc1, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs1, s.br, w.g, chunks, chunks);
     const unsigned rb = (unsigned)((rows + kGmRowsPerBlock - 1) / kGmRowsPerBlock);
-    launch(c, gn_mish_rows_kernel<0>, rb, 256, 0, w.h, gs1, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, nullptr, nullptr,
-           nullptr, w.a1b, c.f16, c.B, T);
-    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs2);
-    // x1 = Mish(GN(h)) * mask + res_conv, and norm1(x1) as the q|k|v operand, in one pass
-    launch(c, gn_mish_rows_kernel<1>, rb, 256, 0, w.h, gs2, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, s.ln1g, s.ln1b, w.x1, w.lnb,
-           c.f16, c.B, T);
     bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
-    gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
+    if (abuild_enabled()) {
+        // block2's conv builds its operand Mish(GN(h)) * mask + time bias itself (its output h2 lives in the fp32 FFN scratch, unused on this path),
+        // the q|k|v projection builds x1 = Mish(GN(h2)) * mask + res_conv and norm1(x1)
+        float *h2 = w.f1;
+        abuild_b(c, 2, w.h, gs1, s.g1, s.be1, T, tb, tb_per_sample, nullptr, nullptr, nullptr, nullptr, sb.wc2, kC, s.bc2, nullptr, h2, gs2);
+        abuild_b(c, 1, h2, gs2, s.g2, s.be2, T, nullptr, 0, w.g, s.ln1g, s.ln1b, w.x1, sb.wqkv, 3 * kC, nullptr, qkvb, nullptr, nullptr);
+    } else {
+        launch(c, gn_mish_rows_kernel<0>, rb, 256, 0, w.h, gs1, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, nullptr, nullptr,
+               nullptr, w.a1b, c.f16, c.B, T);
+        gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs2);
+        // x1 = Mish(GN(h)) * mask + res_conv, and norm1(x1) as the q|k|v operand, in one pass
+        launch(c, gn_mish_rows_kernel<1>, rb, 256, 0, w.h, gs2, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, s.ln1g, s.ln1b, w.x1, w.lnb,
+               c.f16, c.B, T);
+        gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
+    }
     attention_b(c, qkvb, w.attb, T);
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
     if (ffn_use_fused()) {      // norm3 is applied while the kernel builds its A operand
@@ -667,6 +718,21 @@ extern "C" int matcha_b200_debug_ffn(const void *a16, const void *w1_16, const f
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     ffn_b(c, (const bf16 *)a16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, res, out_f32, (bf16 *)out_16, mask != nullptr,
           ln_in, ln_g, ln_b);
+    if (c.err) return c.err;
+    MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+// test aid, not part of the public header: one A-building GEMM (gemm_abuild.cuh) on caller-provided tensors
+extern "C" int matcha_b200_debug_abuild(int mode, const float *h, const double *gsum, const float *gamma, const float *beta,
+                                         const float *mask, const float *tb, const float *r, const float *ln_g,
+                                         const float *ln_b, float *x1, const void *w16, int N, const float *bias, void *out16,
+                                         float *out_f32, double *gstats, int B, int T, int f16, void *stream) {
+    if (!h || !gsum || !gamma || !beta || !mask || !w16 || B < 1 || T < 1 || (mode != 1 && mode != 2)) return MB200_ERR_INVALID_ARG;
+    Ctx c;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16;
+    { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
+    abuild_b(c, mode, h, gsum, gamma, beta, T, tb, 0, r, ln_g, ln_b, x1, (const bf16 *)w16, N, bias, (bf16 *)out16, out_f32, gstats);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;

@@ -35,8 +35,7 @@ __device__ __forceinline__ float mish_f(float x) {
 // Same function in closed form: tanh(log(1+e^x)) = (n^2 + 2n) / (n^2 + 2n + 2), n = e^x  (one exp, one divide;
 // no cancellation for either sign of x).  Used on the 16-bit tensor-core path.
 __device__ __forceinline__ float mish_fast_f(float x) {
-    if (x > 20.0f) return x;
-    const float n = __expf(x);
+    const float n = __expf(fminf(x, 20.0f));      // beyond 20 the ratio below is exactly 1 in fp32 (torch's threshold)
     const float p = fmaf(n, n, 2.0f * n);
     return x * __fdividef(p, p + 2.0f);
 }
