@@ -199,7 +199,7 @@ def decoder_leg(a, dev, world, rank, dist, barrier):
                                f"Matcha-size decoder (BASELINE configs[2])", "precision": a.dec_precision},
         "roofline": {"bound": "tensor", "achieved": flops / (ms / 1e3) / 1e12, "peak": peak, "unit": "TFLOP/s",
                      "frac": flops / (ms / 1e3) / 1e12 / peak, "traffic": None, "peak_source": src,
-                     "algorithmic_flops_per_solve": flops, "kernel": "gemm_bf16_kernel (tcgen05) + attention_tc_kernel (tcgen05)"},
+                     "algorithmic_flops_per_solve": flops, "kernel": "tcgen05 kernels: gemm_bf16_kernel, gemm_abuild_kernel, ffn_fused_kernel, attention_tc_kernel"},
         "e2e": {"value": world * B * T / float(e2e_s.item()), "unit": "mel-frames/s",
                 "h2d_bytes_per_step": int(4 * (2 * B * 80 * T + B * T)), "d2h_bytes_per_step": int(4 * B * 80 * T),
                 "api": "matcha_b200.flow_matching.CFM.solve_ode_euler on pinned host tensors"},
