@@ -14,11 +14,15 @@
 //   warp 1      MMA issuer: S_j = Q K_j^T (M128 x N64 x K64, fp32 in TMEM, double-buffered) and
 //               O += P_j V_j (M128 x N64 x K64; V is consumed MN-major straight from its [key][d] tile),
 //               accumulated in TMEM over all key blocks.
-//   warps 2..5  softmax: thread = one query row (TMEM lane).  Logits, max and exp2 in fp32 registers, P written
-//               16-bit into the 128B-swizzled K-major A-operand layout.  The reference point m of
-//               p = exp(z - m) only moves when a block's max exceeds it by more than 8 octaves (p <= 256 is
-//               harmless in 16 bits); then the row sum and the row's O in TMEM are rescaled (rare after the
-//               first block).  Softmax is invariant to m, so the result is the reference's.
+//   warps 2..9  softmax: two threads per query row (TMEM lane), one for keys 0..31 and one for keys 32..63 of every
+//               64-key block.  The two halves are two INDEPENDENT online-softmax streams (own reference point m,
+//               own row sum, own O accumulator in TMEM: O_lo / O_hi), merged once at the end as in split-KV
+//               attention -- no per-block exchange between the warps of a row, and four softmax warps per scheduler
+//               (two CTAs per SM) to overlap one warp's exp2 phase (MUFU) with the others' logits / pack phases.
+//               Logits, max and exp2 in fp32 registers, P written 16-bit into the 128B-swizzled K-major A-operand
+//               layout.  A stream's reference point m of p = exp(z - m) only moves when a block's max exceeds it by
+//               more than 8 octaves (p <= 256 is harmless in 16 bits); then its row sum and its O in TMEM are
+//               rescaled (rare after the first block).  Softmax is invariant to m, so the result is the reference's.
 // The kernel is MUFU-bound by design: one exp2 per (query, key) at 16 per clock per SM.
 #pragma once
 #include "gemm_bf16.cuh"
@@ -26,16 +30,17 @@
 namespace mb200 {
 
 constexpr int kTaBQ = 128, kTaBK = 64, kTaStages = 3;
-constexpr int kTaThreads = 192;
+constexpr int kTaSmWarps = 8;                               // softmax warps: lane quarter (warp & 3) x key half
+constexpr int kTaThreads = 32 * (2 + kTaSmWarps);
 constexpr int kTaTileQ = kTaBQ * 128;                       // bytes of a 128-row x 64-halfword tile (Q, P)
 constexpr int kTaTileK = kTaBK * 128;                       // bytes of a 64-key tile (K, V)
 constexpr int kTaOffK = kTaTileQ;                           // Q | K x stages | V x stages | P x 2 | mask slices | barriers
 constexpr int kTaOffV = kTaOffK + kTaStages * kTaTileK;
 constexpr int kTaOffP = kTaOffV + kTaStages * kTaTileK;
-constexpr int kTaOffMk = kTaOffP + 2 * kTaTileQ;            // [4 warps][2][64] floats: the block's key-mask slice
+constexpr int kTaOffMk = kTaOffP + 2 * kTaTileQ;            // [8 warps][2][32] floats: the block's key-mask slice of the warp's half
 constexpr int kTaOffBar = kTaOffMk + 4 * 2 * 64 * 4;
 constexpr int kTaSmemBytes = kTaOffBar + 256 + 1024;
-constexpr int kTaTmemCols = 256;                            // S: 2 x 64 columns, O: 64 columns
+constexpr int kTaTmemCols = 256;                            // S: 2 x 64 columns, O_lo / O_hi: 2 x 64 columns
 constexpr float kTaRescale = 5.545177444f;                  // 8 ln 2
 
 struct AttnTcArgs {
@@ -65,6 +70,14 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
           "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
           "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
           "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
+}
+
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+          "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
 }
 
 template <bool F16>
@@ -99,7 +112,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int b = bh / kHeads, h = bh - b * kHeads, q0 = qb * kTaBQ;
     const int n_blk = (T + kTaBK - 1) / kTaBK;
     const int rows_valid = T - q0 < kTaBQ ? T - q0 : kTaBQ;
-    const uint32_t n_sm_warps = (uint32_t)((rows_valid + 31) / 32);          // softmax warps that have rows
+    const uint32_t n_sm_warps = 2u * (uint32_t)((rows_valid + 31) / 32);     // softmax warps that have rows
 
     if (threadIdx.x == 0) {
         mbar_init(bar_q, 1u); mbar_init(bar_pv, 1u); mbar_init(bar_pv + 8u, 1u);
@@ -156,8 +169,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint64_t dp = umma_desc_sw128(base + kTaOffP + a * kTaTileQ);
                 const uint64_t dv = umma_desc_sw128(base + kTaOffV + s * kTaTileK);
-                for (int ks = 0; ks < n16 / 16; ++ks)      // 16 keys per step: P +32 B along its row, V +2048 B
-                    umma_bf16(tmem_o, dp + (uint64_t)(2 * ks), dv + (uint64_t)(128 * ks), idesc_pv, (i | ks) != 0 ? 1u : 0u);
+                for (int ks = 0; ks < n16 / 16; ++ks)      // 16 keys per step: P +32 B along its row, V +2048 B; keys 32.. -> O_hi
+                    umma_bf16(tmem_o + 64u * (uint32_t)(ks >> 1), dp + (uint64_t)(2 * ks), dv + (uint64_t)(128 * ks), idesc_pv,
+                              (i | (ks & 1)) != 0 ? 1u : 0u);
                 umma_commit(bar_pv + 8u * (uint32_t)(i & 1));
                 umma_commit(bar_ve + 8u * s);
             };
@@ -183,100 +197,97 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     } else {
         // ============================ softmax ============================
         const int q = warp & 3;                              // TMEM lane quarter of this warp
+        const int hf = (warp - 2) >> 2;                      // key half of every 64-key block: 0 = keys 0..31, 1 = keys 32..63
         const int row = 32 * q + lane;
         if (32 * q < rows_valid) {
             const uint32_t lane_off = (uint32_t)(32 * q) << 16;
+            const uint32_t tmem_oh = tmem_o + 64u * (uint32_t)hf;               // this stream's O accumulator
             const float kLog2e = 1.4426950408889634f;
-            float *mk = reinterpret_cast<float *>(gbase + kTaOffMk) + (warp - 2) * 128;
-            const float *mrow = g.mask + (size_t)b * g.mask_T;
+            float *mk = reinterpret_cast<float *>(gbase + kTaOffMk) + (warp - 2) * 64;
+            const float *mrow = g.mask + (size_t)b * g.mask_T + 32 * hf;
             float m_ref = -INFINITY, l_run = 0.f;             // p = exp(z - m_ref); l_run = sum of p so far
-            // this warp's copy of the next block's 64 mask values travels global -> registers (one block ahead) -> shared
-            float mk0 = lane < T ? __ldg(mrow + lane) : 0.f;
-            float mk1 = 32 + lane < T ? __ldg(mrow + 32 + lane) : 0.f;
+            bool seen = false;                                // this stream has had at least one key
+            // this warp's copy of the next block's 32 mask values travels global -> registers (one block ahead) -> shared
+            float mk0 = 32 * hf + lane < T ? __ldg(mrow + lane) : 0.f;
             for (int j = 0; j < n_blk; ++j) {
                 const uint32_t a = j & 1;
                 const int k0 = j * kTaBK;
-                const int kvalid = T - k0;                     // keys of this block that exist
-                float *mkb = mk + a * 64;
-                mkb[lane] = mk0; mkb[32 + lane] = mk1;
+                int kvalid = T - k0 - 32 * hf;                 // keys of this half-block that exist
+                kvalid = kvalid < 0 ? 0 : (kvalid > 32 ? 32 : kvalid);
+                float *mkb = mk + a * 32;
+                mkb[lane] = mk0;
                 __syncwarp();
-                if (j + 1 < n_blk) {
-                    mk0 = k0 + kTaBK + lane < T ? __ldg(mrow + k0 + kTaBK + lane) : 0.f;
-                    mk1 = k0 + kTaBK + 32 + lane < T ? __ldg(mrow + k0 + kTaBK + 32 + lane) : 0.f;
-                }
-                // the mask slice goes to registers before the wait on S, so that its latency is off the critical path
-                float z[64];                                   // mask, then logits q.k/8 + mask (natural-log domain)
-                {
-                    const float4 *mk4 = reinterpret_cast<const float4 *>(mkb);
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float4 m = mk4[i];
-                        z[4 * i] = m.x; z[4 * i + 1] = m.y; z[4 * i + 2] = m.z; z[4 * i + 3] = m.w;
-                    }
-                }
+                if (j + 1 < n_blk) mk0 = k0 + kTaBK + 32 * hf + lane < T ? __ldg(mrow + k0 + kTaBK + lane) : 0.f;
                 mbar_wait_parked(bar_sf + 8u * a, (j >> 1) & 1, 100);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (kvalid == 0) {
+                    // ragged tail: nothing for this stream in this block (the MMA warp skips its key steps too); the
+                    // barrier protocol still needs this warp's arrivals
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) { mbar_arrive(bar_se + 8u * a); mbar_arrive(bar_pf + 8u * a); }
+                    continue;
+                }
+                float z[32];                                   // logits q.k/8 + mask (natural-log domain), in place
                 {
-                    uint32_t v0[32], v1[32];
-                    tmem_ld32_issue(tmem_s + a * 64 + lane_off, v0);
-                    tmem_ld32_issue(tmem_s + a * 64 + 32 + lane_off, v1);
-                    tmem_ld_wait();
+                    uint32_t v0[32];
+                    tmem_ld32(tmem_s + a * 64 + 32 * hf + lane_off, v0);
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar_se + 8u * a);
-                    if (kvalid >= 64) {
+                    const float4 *mk4 = reinterpret_cast<const float4 *>(mkb);     // broadcast reads
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            z[i] = fmaf(__uint_as_float(v0[i]), 0.125f, z[i]);
-                            z[32 + i] = fmaf(__uint_as_float(v1[i]), 0.125f, z[32 + i]);
-                        }
-                    } else {                                  // ragged last block: stale TMEM columns must not leak in
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 m = mk4[i];
+                        z[4 * i] = fmaf(__uint_as_float(v0[4 * i]), 0.125f, m.x); z[4 * i + 1] = fmaf(__uint_as_float(v0[4 * i + 1]), 0.125f, m.y);
+                        z[4 * i + 2] = fmaf(__uint_as_float(v0[4 * i + 2]), 0.125f, m.z); z[4 * i + 3] = fmaf(__uint_as_float(v0[4 * i + 3]), 0.125f, m.w);
+                    }
+                    if (kvalid < 32) {                        // ragged last block: stale TMEM columns must not leak in
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            z[i] = i < kvalid ? fmaf(__uint_as_float(v0[i]), 0.125f, z[i]) : -INFINITY;
-                            z[32 + i] = 32 + i < kvalid ? fmaf(__uint_as_float(v1[i]), 0.125f, z[32 + i]) : -INFINITY;
-                        }
+                        for (int i = 0; i < 32; ++i) z[i] = i < kvalid ? z[i] : -INFINITY;
                     }
                 }
                 float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
+                for (int i = 0; i < 8; ++i) {
                     mx[0] = fmaxf(mx[0], z[4 * i]); mx[1] = fmaxf(mx[1], z[4 * i + 1]);
                     mx[2] = fmaxf(mx[2], z[4 * i + 2]); mx[3] = fmaxf(mx[3], z[4 * i + 3]);
                 }
                 const float m_blk = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
                 // move the reference point only when this block would overflow the 8-octave headroom
-                const bool move = m_blk > m_ref + kTaRescale;          // always true on the first block (m_ref = -inf)
+                const bool move = m_blk > m_ref + kTaRescale;          // always true on the stream's first block (m_ref = -inf)
                 if (__any_sync(0xffffffffu, move)) {
                     const float alpha = move ? ex2_approx((m_ref - m_blk) * kLog2e) : 1.0f;   // 0 on the first block
                     if (move) m_ref = m_blk;
                     l_run *= alpha;
-                    if (j > 0) {
+                    if (seen) {
                         // O_row *= alpha in TMEM: every PV issued so far has finished, and PV_j cannot start before this
                         // warp has arrived on bar_pf below
                         mbar_wait_parked(bar_pv + 8u * (uint32_t)((j - 1) & 1), ((j - 1) >> 1) & 1, 100);
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+                        for (int hcol = 0; hcol < 4; ++hcol) {
+                            uint32_t ov[16];
+                            tmem_ld16_issue(tmem_oh + 16 * hcol + lane_off, ov);
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int hcol = 0; hcol < 2; ++hcol) {
-                            uint32_t ov[32];
-                            tmem_ld32(tmem_o + 32 * hcol + lane_off, ov);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
-                            tmem_st32(tmem_o + 32 * hcol + lane_off, ov);
+                            for (int i = 0; i < 16; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+                            tmem_st16(tmem_oh + 16 * hcol + lane_off, ov);
                         }
                         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                     }
                 }
-                // P = exp(z - m_ref) as 16-bit, row `row` of buffer a: K-major, 128B swizzle
+                seen = true;
+                // P = exp(z - m_ref) as 16-bit, this half of row `row` of buffer a: K-major, 128B swizzle
                 const float nm = -m_ref * kLog2e;
                 float ls[4] = {0.f, 0.f, 0.f, 0.f};
                 const uint32_t prow = base + kTaOffP + a * kTaTileQ + row * 128;
 #pragma unroll
-                for (int ch = 0; ch < 8; ++ch) {
+                for (int ch = 0; ch < 4; ++ch) {
                     float p[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) { p[i] = ex2_approx(fmaf(z[8 * ch + i], kLog2e, nm)); ls[i & 3] += p[i]; }
-                    const uint32_t dst = prow + ((ch ^ (row & 7)) << 4);
+                    const uint32_t dst = prow + (((uint32_t)(4 * hf + ch) ^ (uint32_t)(row & 7)) << 4);
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pack16x2(p[0], p[1], F16)),
                                  "r"(pack16x2(p[2], p[3], F16)), "r"(pack16x2(p[4], p[5], F16)), "r"(pack16x2(p[6], p[7], F16)) : "memory");
                 }
@@ -286,22 +297,43 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                 if (lane == 0) mbar_arrive(bar_pf + 8u * a);
                 l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
             }
+            // ---- merge the two streams of a row: (m, l) travel through this warp's (now idle) mask slice, the pair of
+            //      warps of a lane quarter meets on a named barrier; each warp then finishes 32 of the 64 output columns
+            float2 *xch = reinterpret_cast<float2 *>(mk);
+            xch[lane] = make_float2(m_ref, l_run);
+            if (q == 0) asm volatile("bar.sync 1, 64;" ::: "memory");
+            else if (q == 1) asm volatile("bar.sync 2, 64;" ::: "memory");
+            else if (q == 2) asm volatile("bar.sync 3, 64;" ::: "memory");
+            else asm volatile("bar.sync 4, 64;" ::: "memory");
+            const float2 other = reinterpret_cast<const float2 *>(reinterpret_cast<float *>(gbase + kTaOffMk) + ((warp - 2) ^ 4) * 64)[lane];
+            const float m_lo = hf == 0 ? m_ref : other.x, l_lo = hf == 0 ? l_run : other.y;
+            const float m_hi = hf == 0 ? other.x : m_ref, l_hi = hf == 0 ? other.y : l_run;
+            const float m_all = fmaxf(m_lo, m_hi);                             // the lo stream always has keys: finite
+            const float a_lo = ex2_approx((m_lo - m_all) * kLog2e);
+            const float a_hi = l_hi > 0.f ? ex2_approx((m_hi - m_all) * kLog2e) : 0.f;
+            const float inv = 1.0f / fmaf(l_lo, a_lo, l_hi * a_hi);
+            const float w_lo = a_lo * inv, w_hi = a_hi * inv;
             // O is complete when the last PV has been committed
             mbar_wait_parked(bar_pv + 8u * (uint32_t)((n_blk - 1) & 1), ((n_blk - 1) >> 1) & 1, 100);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const float inv = 1.0f / l_run;
 #pragma unroll
-            for (int hcol = 0; hcol < 2; ++hcol) {
-                uint32_t ov[32];
-                tmem_ld32(tmem_o + 32 * hcol + lane_off, ov);
+            for (int part = 0; part < 2; ++part) {             // 16 output columns at a time
+                uint32_t olo[16], ohi[16];
+                tmem_ld16_issue(tmem_o + 32 * hf + 16 * part + lane_off, olo);
+                tmem_ld16_issue(tmem_o + 64 + 32 * hf + 16 * part + lane_off, ohi);
+                tmem_ld_wait();
                 if (q0 + row < T) {
-                    uint4 *po = reinterpret_cast<uint4 *>(g.out + ((size_t)b * T + q0 + row) * kC + h * kDHead + 32 * hcol);
+                    float o[16];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        po[i] = make_uint4(pack16x2(__uint_as_float(ov[8 * i]) * inv, __uint_as_float(ov[8 * i + 1]) * inv, F16),
-                                           pack16x2(__uint_as_float(ov[8 * i + 2]) * inv, __uint_as_float(ov[8 * i + 3]) * inv, F16),
-                                           pack16x2(__uint_as_float(ov[8 * i + 4]) * inv, __uint_as_float(ov[8 * i + 5]) * inv, F16),
-                                           pack16x2(__uint_as_float(ov[8 * i + 6]) * inv, __uint_as_float(ov[8 * i + 7]) * inv, F16));
+                    for (int i = 0; i < 16; ++i) {
+                        const float hi = l_hi > 0.f ? __uint_as_float(ohi[i]) : 0.f;      // never written when T <= 32
+                        o[i] = fmaf(__uint_as_float(olo[i]), w_lo, hi * w_hi);
+                    }
+                    uint4 *po = reinterpret_cast<uint4 *>(g.out + ((size_t)b * T + q0 + row) * kC + h * kDHead + 32 * hf + 16 * part);
+#pragma unroll
+                    for (int i = 0; i < 2; ++i)
+                        po[i] = make_uint4(pack16x2(o[8 * i], o[8 * i + 1], F16), pack16x2(o[8 * i + 2], o[8 * i + 3], F16),
+                                           pack16x2(o[8 * i + 4], o[8 * i + 5], F16), pack16x2(o[8 * i + 6], o[8 * i + 7], F16));
                 }
             }
         }
