@@ -92,6 +92,52 @@ int matcha_b200_mas_apply_mask(float *scores_dev, const float *values_dev, const
  * out[7]=DP warps per CTA. */
 int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int aligned16, int out[8]);
 
+/*
+ * maximum_path plus the compact form of the result: durations_dev [B][T_x] int32 (may be NULL) receives the
+ * number of frames each token owns (= sum_y path[b][x][y], what matcha_tts.py:287 reduces the path to; 0
+ * for x >= t_x and for out-of-domain items).  It comes from the backtrack's start frames, so the dense path
+ * is not re-read.  All other arguments as matcha_b200_mas_compute_batch_alignments.
+ */
+int matcha_b200_mas_align(
+    void *paths_dev, int path_dtype, int *durations_dev,
+    const float *values_dev, const float *mask_dev,
+    const int *t_xs_dev, const int *t_ys_dev,
+    int B, int T_x, int T_y, float penalty,
+    int *status_dev, void *stream);
+
+/* ------------------------------------------------------------------ callers either side of MAS / the decoder
+ * (SURVEY.md §8f rows 1-3).  Reference code replaced:
+ *   matcha_b200_align_log_prior <- the no_grad block of MatchaTTS.forward            matcha_tts.py:277-282
+ *   matcha_b200_align_expand    <- generate_path (utils/model.py:77-114), mu_y = attn^T mu_x
+ *                                  (matcha_tts.py:227-228, 314-315), logw_ (:287), prior loss sums (:320-321)
+ *   matcha_b200_cfm_loss_mix    <- phi_t of compute_loss                              flow_matching.py:138
+ *   matcha_b200_cfm_loss_mse    <- u_target, mse_loss(sum), sum(mask)                 flow_matching.py:142-149
+ *
+ * log_prior: mu_x [B][C][T_x], y [B][C][T_y] fp32 channels-first -> log_prior [B][T_x][T_y].  With
+ * t_xs/t_ys (both or neither) tiles that lie entirely outside an item's valid block are not written
+ * (MAS never reads them).
+ *
+ * expand: durations [B][T_x] int32 (dur_is_int) or fp32, >= 0.  Every output pointer may be NULL:
+ *   attn [B][T_x][T_y] fp32 0/1 (fully written), mu_y [B][C][T_y] (fully written, 0 past t_y),
+ *   logw [B][T_x], prior_sums double[2] = {sum 0.5*((y-mu_y)^2+log 2pi)*y_mask, sum y_mask}
+ *   (needs y_dev; zeroed inside the call).  t_xs/t_ys NULL = full lengths.
+ *
+ * cfm_loss_mix: phi = (1-(1-sigma_min)*t[b])*z + t[b]*x1 over B samples of per_sample floats.
+ * cfm_loss_mse: sums double[2] = {sum (u_pred-(x1-(1-sigma_min)*z))^2 over n, sum mask over n_mask}.
+ */
+int matcha_b200_align_log_prior(float *log_prior_dev, const float *mu_x_dev, const float *y_dev,
+                                const int *t_xs_dev, const int *t_ys_dev,
+                                int B, int C, int T_x, int T_y, void *stream);
+int matcha_b200_align_expand(const void *durations_dev, int dur_is_int, const float *mu_x_dev,
+                             const float *y_dev, const int *t_xs_dev, const int *t_ys_dev,
+                             float *attn_dev, float *mu_y_dev, float *logw_dev, double *prior_sums_dev,
+                             int B, int C, int T_x, int T_y, void *stream);
+int matcha_b200_cfm_loss_mix(float *phi_dev, const float *x1_dev, const float *z_dev, const float *t_dev,
+                             double sigma_min, int B, long long per_sample, void *stream);
+int matcha_b200_cfm_loss_mse(double *sums_dev, const float *u_pred_dev, const float *x1_dev,
+                             const float *z_dev, const float *mask_dev, double sigma_min,
+                             long long n, long long n_mask, void *stream);
+
 /* ------------------------------------------------------------------ CFM decoder
  * Reference interfaces replaced (matcha/models/components/):
  *   matcha_b200_decoder_forward  <- Decoder.forward(x, mask, mu, t)               decoder.py:271-371

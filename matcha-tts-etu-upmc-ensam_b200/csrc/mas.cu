@@ -51,6 +51,7 @@ struct MasParams {
     const int *t_xs;
     const int *t_ys;
     int *status;
+    int *durations;      // optional [B][T_x]: frames owned by each token (0 for x >= t_x)
     int B, T_x, T_y;
     float penalty;
     uint32_t one_bits;   // bit pattern of "1" in the output element type
@@ -448,6 +449,10 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
             mbar_wait_parked(bar_bfull + 8u * buf, (k >> 1) & 1u, 20000);
             if (ww == 0) MAS_STAMP(24);
             const int tx = info_g[buf].valid ? info_g[buf].tx : 0;
+            if (p.durations != nullptr) {                         // compact form of the path (1 int per token)
+                int *d = p.durations + (size_t)b * p.T_x;
+                for (int x = wt; x < p.T_x; x += WT) d[x] = (x < tx) ? cs[x + 1] - cs[x] : 0;
+            }
             if (p.early_zero) {
                 zero_fill(0, head);
                 // every zero is ordered before the ones dropped on top of it
@@ -609,10 +614,10 @@ static int mas_grid(MasKernelFn fn, const MasPlan &pl, int B, int *ctas_per_sm) 
 
 using namespace mb200;
 
-extern "C" int matcha_b200_mas_compute_batch_alignments(
+static int mas_launch(
     void *paths_dev, int path_dtype, const float *values_dev, const float *mask_dev,
     const int *t_xs_dev, const int *t_ys_dev, int B, int T_x, int T_y, float penalty,
-    int *status_dev, void *stream) {
+    int *status_dev, int *durations_dev, void *stream) {
     if (B < 0 || T_x <= 0 || T_y <= 0) return MB200_ERR_INVALID_ARG;
     if (B == 0) return MB200_OK;
     if (!paths_dev || !values_dev || !t_xs_dev || !t_ys_dev) return MB200_ERR_INVALID_ARG;
@@ -644,7 +649,7 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
 
     MasParams p;
     p.value = values_dev; p.mask = mask_dev; p.out = (uint32_t *)paths_dev;
-    p.t_xs = t_xs_dev; p.t_ys = t_ys_dev; p.status = status_dev;
+    p.t_xs = t_xs_dev; p.t_ys = t_ys_dev; p.status = status_dev; p.durations = durations_dev;
     p.B = B; p.T_x = T_x; p.T_y = T_y; p.penalty = penalty;
     p.one_bits = (path_dtype == MB200_PATH_F32) ? 0x3f800000u : 1u;
     p.ndp = pl.ndp; p.nstage = pl.nstage; p.txp = pl.txp; p.n_chunks = pl.n_chunks;
@@ -655,6 +660,22 @@ extern "C" int matcha_b200_mas_compute_batch_alignments(
     fn<<<grid, pl.threads, pl.smem, (cudaStream_t)stream>>>(tm_v, tm_m, p);
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
+}
+
+extern "C" int matcha_b200_mas_compute_batch_alignments(
+    void *paths_dev, int path_dtype, const float *values_dev, const float *mask_dev,
+    const int *t_xs_dev, const int *t_ys_dev, int B, int T_x, int T_y, float penalty,
+    int *status_dev, void *stream) {
+    return mas_launch(paths_dev, path_dtype, values_dev, mask_dev, t_xs_dev, t_ys_dev, B, T_x, T_y, penalty,
+                      status_dev, nullptr, stream);
+}
+
+extern "C" int matcha_b200_mas_align(
+    void *paths_dev, int path_dtype, int *durations_dev, const float *values_dev, const float *mask_dev,
+    const int *t_xs_dev, const int *t_ys_dev, int B, int T_x, int T_y, float penalty,
+    int *status_dev, void *stream) {
+    return mas_launch(paths_dev, path_dtype, values_dev, mask_dev, t_xs_dev, t_ys_dev, B, T_x, T_y, penalty,
+                      status_dev, durations_dev, stream);
 }
 
 extern "C" int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int aligned16, int out[8]) {

@@ -52,6 +52,22 @@ def load_library():
     lib.matcha_b200_mas_apply_mask.restype = c_int
     lib.matcha_b200_mas_apply_mask.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_void_p]
     ll = ctypes.c_longlong
+    lib.matcha_b200_mas_align.restype = c_int
+    lib.matcha_b200_mas_align.argtypes = [
+        c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_int, c_int, c_int, c_float, c_void_p, c_void_p]
+    lib.matcha_b200_align_log_prior.restype = c_int
+    lib.matcha_b200_align_log_prior.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                c_int, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_align_expand.restype = c_int
+    lib.matcha_b200_align_expand.argtypes = [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                             c_void_p, c_void_p, c_void_p, c_void_p,
+                                             c_int, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_cfm_loss_mix.restype = c_int
+    lib.matcha_b200_cfm_loss_mix.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_double, c_int, ll, c_void_p]
+    lib.matcha_b200_cfm_loss_mse.restype = c_int
+    lib.matcha_b200_cfm_loss_mse.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_double,
+                                             ll, ll, c_void_p]
     lib.matcha_b200_decoder_blob_floats.restype = ll
     lib.matcha_b200_decoder_workspace_bytes.restype = ll
     lib.matcha_b200_decoder_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
@@ -89,6 +105,11 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_maximum_path_host",
     "matcha_b200_mas_query_launch",
     "matcha_b200_mas_apply_mask",
+    "matcha_b200_mas_align",
+    "matcha_b200_align_log_prior",
+    "matcha_b200_align_expand",
+    "matcha_b200_cfm_loss_mix",
+    "matcha_b200_cfm_loss_mse",
     "matcha_b200_decoder_blob_floats",
     "matcha_b200_decoder_workspace_bytes",
     "matcha_b200_decoder_blob_bf16_bytes",
