@@ -303,6 +303,12 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                 rb_chunk_range(r0, r1, tx, ty, c0, c1);
                 if (w > 0) rb_chunk_range(r0 - RB, r0, tx, ty, c0p, c1p);
                 const bool has_prev = w > 0, has_next = (w + 1 < n_act);
+                // Row r0-1 leaves the band at frame y_e = r0-1+ty-tx; cell (r0, y_e+1) still reads Q[y_e][r0-1]
+                // (core.pyx:66).  When y_e is the last frame of chunk c1p that cell opens chunk c1p+1, in which
+                // the previous warp no longer runs: it sends one extra "tail" message carrying that value.
+                int c0x = 0, c1x = -1;
+                if (has_next) rb_chunk_range(r0 + RB, min(r0 + 2 * RB, tx), tx, ty, c0x, c1x);
+                const bool tail_out = has_next && (c1 + 1 <= c1x);
                 const int c0n = (r0 + RB) / kChunk;     // first chunk of the next warp
                 const int cd = (r1 - 1) / kChunk;       // last chunk that holds a diagonal cell
                 float q[R];
@@ -313,7 +319,7 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                 for (int c = c0; c <= c1; ++c, ++it) {
                     const uint32_t s = it % (uint32_t)nstage, ph = (it / (uint32_t)nstage) & 1u;
                     const uint32_t stage = base + L.stages + s * L.stage_bytes + (uint32_t)r0 * 128u;
-                    const bool in_h = has_prev && c <= c1p;
+                    const bool in_h = has_prev && c <= c1p + 1;   // c1p + 1: the tail message
                     const bool out_h = has_next && c >= c0n;
                     const uint32_t din = hin % kBndDepth, dout = hout % kBndDepth;
                     const uint32_t bin = base + L.bnd + (((w - 1) * kBndDepth + din) * kBndFloats) * 4u;
@@ -329,10 +335,10 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                     __syncwarp();
                     if (c <= cd)
                         dp_chunk<R, HAS_MASK, true>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
-                                                    has_prev, bin, out_h, bout);
+                                                    in_h, bin, out_h, bout);
                     else
                         dp_chunk<R, HAS_MASK, false>(q, bits, stage, mask_off, p.txp - r0, lane, kChunk * c, x0, p.penalty,
-                                                     has_prev, bin, out_h, bout);
+                                                     in_h, bin, out_h, bout);
                     __syncwarp();                               // all lanes are done reading the stage
                     if (lane == 0 && in_h) mbar_arrive(bar_bdempty + 8u * ((w - 1) * kBndDepth + din));
                     if (lane == 31 && out_h) mbar_arrive(bar_bdfull + 8u * (w * kBndDepth + dout));
@@ -343,6 +349,19 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
                         if (x0 + r < p.T_x) wd[r] = bits[r];
                     hin += in_h ? 1u : 0u;
                     hout += out_h ? 1u : 0u;
+                }
+                if (tail_out) {
+                    const uint32_t dout = hout % kBndDepth;
+                    mbar_wait_parked(bar_bdempty + 8u * (w * kBndDepth + dout), ((hout / kBndDepth) & 1u) ^ 1u, 2000);
+                    __syncwarp();
+                    if (lane == 31) {
+                        float *bo = reinterpret_cast<float *>(
+                            __cvta_shared_to_generic(base + L.bnd + ((w * kBndDepth + dout) * kBndFloats) * 4u));
+                        bo[0] = q[R - 1];
+                        for (int i = 1; i < 32; ++i) bo[i] = p.penalty;   // row r0-1 is outside the band from here on
+                        mbar_arrive(bar_bdfull + 8u * (w * kBndDepth + dout));
+                    }
+                    ++hout;
                 }
             }
             MAS_STAMP(2 + 2 * w);

@@ -63,10 +63,11 @@ def maximum_path_with_durations(value, t_xs, t_ys, max_neg_val=-1e9):
     dur = torch.empty((B, T_x), dtype=torch.int32, device=dev)
     if B == 0:
         return path, dur
+    tx, ty = _i32(t_xs, dev), _i32(t_ys, dev)        # named: the buffers must outlive the launch
     with torch.cuda.device(dev):
         check(load_library().matcha_b200_mas_align(
             path.data_ptr(), PATH_F32, dur.data_ptr(), value.data_ptr(), None,
-            _i32(t_xs, dev).data_ptr(), _i32(t_ys, dev).data_ptr(), B, T_x, T_y,
+            tx.data_ptr(), ty.data_ptr(), B, T_x, T_y,
             ctypes.c_float(max_neg_val), None, _stream_ptr(dev)), "mas_align")
     return path, dur
 

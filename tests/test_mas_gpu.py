@@ -145,3 +145,46 @@ def test_full_size_properties_and_sampled_parity(ma, shape):
     want = np.zeros(vs.shape, np.int32)
     omas.oracle_compute_batch_alignments(want, vs, t_x[idx], t_y[idx])
     assert np.array_equal(sub, want)
+
+
+# Paths that run along the band edges: a strongly preferred token keeps the optimum on one row until the
+# band (core.pyx:58) forces it off, and log-prior-sized scores (-150 per cell, matcha_tts.py:277-282) make
+# the sentinel arithmetic non-absorbing.  (t_y - t_x) % 32 == 0 puts the hand-over between two DP warps
+# exactly on a chunk boundary (regression: the value the lower row block reads there was never sent).
+BAND_SHAPES = [(1, 128, 800), (4, 128, 800), (3, 200, 1000), (2, 64, 200), (2, 96, 96 + 64), (1, 400, 2000),
+               (2, 160, 160 + 32), (3, 130, 130 + 320), (2, 33, 65)]
+
+
+@pytest.mark.parametrize("shape", BAND_SHAPES)
+@pytest.mark.parametrize("kind", ["bonus_row", "log_prior_scale", "both", "late_bonus"])
+def test_band_edge_paths_vs_oracle(ma, shape, kind):
+    B, T_x, T_y = shape
+    rng = np.random.default_rng(hash((B, T_x, T_y, kind)) % (2 ** 31))
+    v = rng.standard_normal((B, T_x, T_y), dtype=np.float32)
+    if kind in ("log_prior_scale", "both"):
+        v = (v * 10 - 150).astype(np.float32)
+    if kind in ("bonus_row", "both"):
+        v[:, T_x // 3, :] += 30.0 if kind == "both" else 5.0
+    if kind == "late_bonus":                      # the optimum hugs the upper edge (x == y), then one row
+        v[:, T_x - 2, :] += 5.0
+    m = np.ones_like(v)
+    m[1:] = gen.ragged_mask(rng, B, T_x, T_y, lo=0.6)[1:]          # item 0 keeps the full lengths
+    want = omas.maximum_path_oracle(v, m)
+    for mode in ("prefix", "full"):
+        got = _run(ma, v, m, mask_mode=mode)
+        assert np.array_equal(got, want), f"{shape} {kind} mode={mode}"
+
+
+def test_band_edge_all_offsets(ma):
+    """t_y - t_x swept over a whole chunk period with a preferred row: every alignment of the band edge to the
+    32-frame chunks and to the row blocks."""
+    rng = np.random.default_rng(123)
+    T_x, B = 100, 33
+    T_y = T_x + 64 + B
+    v = rng.standard_normal((B, T_x, T_y), dtype=np.float32)
+    v[:, 20, :] += 4.0
+    m = np.zeros_like(v)
+    for b in range(B):
+        m[b, :T_x, : T_x + 64 + b] = 1
+    want = omas.maximum_path_oracle(v, m)
+    assert np.array_equal(_run(ma, v, m, mask_mode="prefix"), want)
