@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel-only", action="store_true", help="profiling aid: skip the e2e and CPU-baseline legs")
     ap.add_argument("--no-decoder", action="store_true", help="skip the CFM-decoder leg (BASELINE configs[2])")
+    ap.add_argument("--no-pipeline-legs", action="store_true", help="skip the training-step / synthesis legs (configs[3], [4])")
+    ap.add_argument("--synth-utterances", type=int, default=512, help="utterances per GPU in the synthesis leg")
     ap.add_argument("--dec-batch", type=int, default=32)
     ap.add_argument("--dec-T", type=int, default=800)
     ap.add_argument("--dec-steps", type=int, default=10, help="Euler steps per solve")
@@ -228,6 +230,168 @@ def decoder_leg(a, dev, world, rank, dist, barrier):
     return res
 
 
+def _dec_params():
+    return dict(channels=(256, 256), dropout=0.05, attention_head_dim=64, n_blocks=1, num_mid_blocks=2, num_heads=4)
+
+
+def training_leg(a, dev, world, rank, dist, barrier):
+    """BASELINE configs[3]: the training-step hot path after the text encoder (out of scope):
+    mu_x -> log-prior -> MAS -> logw_ / mu_y / prior loss -> CFM flow-matching loss forward, synthetic
+    LJSpeech-shaped batch 32 per GPU (T_text 128, T_mel 800, ragged 0.7-1.0)."""
+    import torch
+    from types import SimpleNamespace
+    from matcha_b200 import alignment as al
+    from matcha_b200.flow_matching import CFM
+    B, T_x, T_y = a.dec_batch, 128, a.dec_T
+    cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), _dec_params(), precision=a.dec_precision)
+    cfm.estimator.initialize_weights(seed=0)
+    rng = np.random.default_rng(3000 + rank)
+    xl_h, yl_h = ragged_lengths(rng, B, T_x, T_y)
+    g = torch.Generator(device=dev); g.manual_seed(3000 + rank)
+    mu_x = torch.randn(B, 80, T_x, device=dev, generator=g)
+    y = torch.randn(B, 80, T_y, device=dev, generator=g)
+    logw = torch.randn(B, 1, T_x, device=dev, generator=g)
+    xl, yl = torch.from_numpy(xl_h).to(dev), torch.from_numpy(yl_h).to(dev)
+    y_mask = (torch.arange(T_y, device=dev)[None, :] < yl[:, None]).float().unsqueeze(1)
+    x_mask = (torch.arange(T_x, device=dev)[None, :] < xl[:, None]).float().unsqueeze(1)
+
+    def step(mu_x, y, logw):
+        r = al.align(mu_x, y, xl, yl)                                             # matcha_tts.py:277-287, 314-321
+        dur_loss = torch.sum((logw * x_mask - r["logw_"]) ** 2) / torch.sum(xl)    # utils/model.py:117-135
+        diff_loss, _ = cfm.compute_loss(y, y_mask, r["mu_y"])                     # flow_matching.py:106-151
+        return torch.stack([dur_loss, r["prior_loss"], diff_loss])
+
+    for _ in range(3):
+        losses = step(mu_x, y, logw)
+    barrier()
+    K = 10
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    for _ in range(K):
+        losses = step(mu_x, y, logw)
+    ev[1].record()
+    barrier()
+    ms = torch.tensor([ev[0].elapsed_time(ev[1]) / K], device=dev, dtype=torch.float64)
+    # stage split (device time of each stage alone, same inputs)
+    def timed(fn, n=10):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+    lp = al.log_prior(mu_x, y, xl, yl)
+    _, dur = al.maximum_path_with_durations(lp, xl, yl)
+    split = {"log_prior_ms": timed(lambda: al.log_prior(mu_x, y, xl, yl)),
+             "mas_ms": timed(lambda: al.maximum_path_with_durations(lp, xl, yl)),
+             "expand_ms": timed(lambda: al.expand(dur, mu_x, xl, yl, y=y, want_logw=True, want_prior=True)),
+             "cfm_loss_ms": timed(lambda: cfm.compute_loss(y, y_mask, y))}
+    # e2e: pinned host tensors in, the three losses out
+    mu_h, y_h, lw_h = mu_x.cpu().pin_memory(), y.cpu().pin_memory(), logw.cpu().pin_memory()
+    def e2e_once():
+        return step(mu_h.to(dev, non_blocking=True), y_h.to(dev, non_blocking=True), lw_h.to(dev, non_blocking=True)).cpu()
+    e2e_once(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        e2e_once()
+    barrier()
+    e2e_s = torch.tensor([(time.perf_counter() - t0) / 5], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        return None
+    ms = float(ms.item())
+    res = {"metric": "training_hot_path_utterances_per_sec", "value": world * B / (ms / 1e3), "unit": "utterances/s",
+           "ms_per_step": ms, "n_gpus": world, "scaling": "weak", "dtype": a.dec_precision, "data": "synthetic",
+           "config": {"workload": f"mu_x -> log-prior -> MAS -> mu_y/logw_/prior loss -> CFM loss forward, B={B}/GPU "
+                                  f"T_text={T_x} T_mel={T_y} ragged 0.7-1.0 (BASELINE configs[3]); text encoder and "
+                                  f"backward pass out of scope"},
+           "stage_ms": split, "losses": [float(v) for v in losses.cpu()],
+           "e2e": {"value": world * B / float(e2e_s.item()), "unit": "utterances/s",
+                   "h2d_bytes_per_step": int(4 * (mu_x.numel() + y.numel() + logw.numel())), "d2h_bytes_per_step": 12,
+                   "api": "matcha_b200.alignment.align + matcha_b200.flow_matching.CFM.compute_loss on pinned host tensors"}}
+    if not a.no_cpu_baseline:
+        from oracle import alignment as oal, decoder as odec       # the checker, timed as the CPU baseline only
+        torch.set_num_threads(os.cpu_count() or 1)
+        mc, yc = mu_x.cpu(), y.cpu()
+        t1 = time.perf_counter()
+        r = oal.align(mc, yc, xl.cpu(), yl.cpu(), use_ref=oal.omas.ref_available())
+        t_align = time.perf_counter() - t1
+        bs = min(4, B)
+        w = cfm.estimator.state_dict()
+        tt, zz = torch.rand(bs, 1, 1), torch.randn(bs, 80, T_y)
+        t1 = time.perf_counter()
+        odec.compute_loss(w, yc[:bs], y_mask[:bs].cpu(), r["mu_y"][:bs], tt, zz)
+        t_loss = (time.perf_counter() - t1) * B / bs
+        res["cpu_baseline"] = {"value": B / (t_align + t_loss), "unit": "utterances/s", "cores": torch.get_num_threads(),
+                               "kind": "reference" if oal.omas.ref_available() else "port",
+                               "sample": f"torch CPU restatement of matcha_tts.py:277-321 with the compiled core.pyx on the "
+                                         f"full batch ({t_align * 1e3:.0f} ms) + decoder loss forward on {bs} items scaled to {B}"}
+    return res
+
+
+def synthesis_leg(a, dev, world, rank, dist, barrier):
+    """BASELINE configs[4]: batched synthesis throughput, 512 synthetic utterances per GPU (4096 over 8 GPUs) in
+    batches of 32, MAS-free inference: durations -> generate_path / mu_y (matcha_tts.py:218-229) -> CFM Euler
+    solve with n_timesteps 2 / 4 / 10, then one all-gather of the mels over NCCL when N > 1."""
+    import torch
+    from types import SimpleNamespace
+    from matcha_b200 import alignment as al
+    from matcha_b200.flow_matching import CFM
+    n_utt, bs, T_x, T_max = a.synth_utterances, a.dec_batch, 128, a.dec_T
+    cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), _dec_params(), precision=a.dec_precision)
+    cfm.estimator.initialize_weights(seed=0)
+    rng = np.random.default_rng(4000 + rank)
+    g = torch.Generator(device=dev); g.manual_seed(4000 + rank)
+    batches = []
+    for _ in range(n_utt // bs):
+        xl_h, yl_h = ragged_lengths(rng, bs, T_x, T_max)
+        yl_h[0], xl_h[0] = T_max, T_x                       # every batch pads to T_mel = 800, as LJSpeech-length text does
+        d = np.zeros((bs, T_x), np.float32)
+        for i in range(bs):                                 # integer durations >= 1 summing to the utterance's mel length
+            cuts = np.sort(rng.choice(np.arange(1, yl_h[i]), xl_h[i] - 1, replace=False))
+            d[i, : xl_h[i]] = np.diff(np.concatenate([[0], cuts, [yl_h[i]]]))
+        logw = torch.from_numpy(np.log(np.maximum(d, 1.0) - 0.5)).unsqueeze(1).to(dev)     # ceil(exp(logw)) == d
+        x_mask = (torch.arange(T_x, device=dev)[None, :] < torch.from_numpy(xl_h).to(dev)[:, None]).float().unsqueeze(1)
+        batches.append((torch.randn(bs, 80, T_x, device=dev, generator=g), logw, x_mask, int(yl_h.sum())))
+    frames = sum(b[3] for b in batches)
+    mels = torch.empty(n_utt, 80, T_max, device=dev)
+    gathered = torch.empty(world * n_utt, 80, T_max, device=dev) if world > 1 else None
+
+    def run_all(n):
+        for i, (mu_x, logw, x_mask, _) in enumerate(batches):
+            pre = al.synthesis_prestep(mu_x, logw, x_mask, 1.0)                   # matcha_tts.py:218-229
+            out = cfm(pre["mu_y"], pre["y_mask"], n, 1.0)                         # :234 (randn + Euler solve)
+            mels[i * bs:(i + 1) * bs, :, : out.shape[-1]] = out
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, mels)
+
+    per_n = {}
+    for n in (2, 4, 10):
+        run_all(n); barrier()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        run_all(n)
+        ev[1].record()
+        barrier()
+        ms = torch.tensor([ev[0].elapsed_time(ev[1])], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms.item())
+        per_n[f"n_timesteps_{n}"] = {"ms_per_pass": ms, "utterances_per_sec": world * n_utt / (ms / 1e3),
+                                    "mel_frames_per_sec": world * frames / (ms / 1e3)}
+    if rank != 0:
+        return None
+    return {"metric": "synthesis_utterances_per_sec", "value": per_n["n_timesteps_10"]["utterances_per_sec"],
+            "unit": "utterances/s", "n_gpus": world, "scaling": "weak", "dtype": a.dec_precision, "data": "synthetic",
+            "config": {"workload": f"{n_utt} utterances/GPU in batches of {bs}, T_text={T_x}, T_mel<={T_max} (valid frames "
+                                   f"counted), durations -> generate_path/mu_y -> CFM solve, all-gather of mels at N>1 "
+                                   f"(BASELINE configs[4]); text encoder and vocoder out of scope"},
+            "by_n_timesteps": per_n}
+
+
 def run_reference(a):
     """--impl reference: the reference's own CPU implementation of the path on the host cores."""
     rank = int(os.environ.get("RANK", "0"))
@@ -382,10 +546,18 @@ def run_ours(a):
         del value, path
         torch.cuda.empty_cache()
         dec = decoder_leg(a, dev, world, rank, dist, barrier)
+    train = synth = None
+    if not a.no_decoder and not a.no_pipeline_legs:
+        train = training_leg(a, dev, world, rank, dist, barrier)
+        synth = synthesis_leg(a, dev, world, rank, dist, barrier)
     if rank == 0:
         if dec is not None:
             line["cfm_decoder"] = dec
             line["gpu_launches"] = a.steps + 5 * dec["gpu_launches_per_solve"]
+        if train is not None:
+            line["training_step"] = train
+        if synth is not None:
+            line["synthesis"] = synth
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

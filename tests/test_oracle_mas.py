@@ -71,3 +71,19 @@ def test_oracle_matches_compiled_reference_random(seed):
     omas.oracle_compute_batch_alignments(got, got_scores, t_x, t_y)
     assert np.array_equal(got, want)
     assert np.array_equal(got_scores.view(np.uint32), want_scores.view(np.uint32))
+
+
+@pytest.mark.parametrize("kind", ["bonus_row", "log_prior_scale"])
+def test_oracle_matches_compiled_reference_band_edges(kind):
+    """Paths that run along the band edges (core.pyx:58-59) with log-prior-sized scores: the shapes that
+    exposed a kernel bug in round 1 (tests/test_mas_gpu.py::test_band_edge_paths_vs_oracle)."""
+    if not omas.ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rng = np.random.default_rng(7)
+    v = rng.standard_normal((3, 128, 800), dtype=np.float32)
+    if kind == "log_prior_scale":
+        v = (v * 10 - 150).astype(np.float32)
+    v[:, 40, :] += 5.0
+    m = gen.ragged_mask(rng, 3, 128, 800)
+    m[0] = 1
+    assert np.array_equal(omas.maximum_path_oracle(v, m), omas.maximum_path_ref(v, m))
