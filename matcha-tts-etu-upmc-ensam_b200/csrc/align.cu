@@ -33,6 +33,7 @@ log_prior_kernel(float *__restrict__ out, const float *__restrict__ mu, const fl
                  const int *__restrict__ t_xs, const int *__restrict__ t_ys,
                  int C, int T_x, int T_y, float cst) {
     __shared__ __align__(16) float s_mu[kLpCk][kLpTx];
+    __shared__ __align__(16) float s_a[kLpCk][kLpTx];
     __shared__ __align__(16) float s_y[kLpCk][kLpTy];
     __shared__ float s_musq[kLpTx];
     __shared__ float s_ysq[kLpTy];
@@ -53,7 +54,9 @@ log_prior_kernel(float *__restrict__ out, const float *__restrict__ mu, const fl
         __syncthreads();
         for (int i = tid; i < kLpCk * kLpTx; i += 256) {
             const int c = i / kLpTx, x = i % kLpTx;
-            s_mu[c][x] = (c0 + c < C && x0 + x < T_x) ? __ldg(mub + (size_t)(c0 + c) * T_x + x0 + x) : 0.f;
+            const float m = (c0 + c < C && x0 + x < T_x) ? __ldg(mub + (size_t)(c0 + c) * T_x + x0 + x) : 0.f;
+            s_mu[c][x] = m;
+            s_a[c][x] = __fmul_rn(2.0f, __fmul_rn(-0.5f, m));          // 2.0 * (factor * mu_x), once per element
         }
         for (int i = tid; i < kLpCk * kLpTy; i += 256) {
             const int c = i / kLpTy, yy = i % kLpTy;
@@ -77,12 +80,12 @@ log_prior_kernel(float *__restrict__ out, const float *__restrict__ mu, const fl
 #pragma unroll
         for (int c = 0; c < kLpCk; ++c) {
             const float4 yv = *reinterpret_cast<const float4 *>(&s_y[c][lane * 4]);
-            const float4 m0 = *reinterpret_cast<const float4 *>(&s_mu[c][warp * 8]);
-            const float4 m1 = *reinterpret_cast<const float4 *>(&s_mu[c][warp * 8 + 4]);
+            const float4 m0 = *reinterpret_cast<const float4 *>(&s_a[c][warp * 8]);
+            const float4 m1 = *reinterpret_cast<const float4 *>(&s_a[c][warp * 8 + 4]);
             const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const float a = __fmul_rn(2.0f, __fmul_rn(-0.5f, m[i]));     // 2.0 * (factor * mu_x)
+                const float a = m[i];
                 acc[i][0] = fmaf(a, yv.x, acc[i][0]);
                 acc[i][1] = fmaf(a, yv.y, acc[i][1]);
                 acc[i][2] = fmaf(a, yv.z, acc[i][2]);
@@ -215,14 +218,26 @@ expand_kernel(const ExpandParams p) {
         const float *mub = p.mu_x + (size_t)b * p.C * p.T_x;
         const float kLog2Pi = 1.8378770664093453f;             // (float) math.log(2*math.pi)
         if (yy < p.T_y) {
-            for (int c = 0; c < p.C; ++c) {
-                const float m = idx >= 0 ? __ldg(mub + (size_t)c * p.T_x + idx) : 0.f;
-                const size_t o = ((size_t)b * p.C + c) * p.T_y + yy;
-                if (p.mu_y != nullptr) p.mu_y[o] = m;
-                if (p.prior != nullptr && yy < ty) {
-                    const float d = __fsub_rn(__ldg(p.y + o), m);
-                    acc += (double)__fmul_rn(0.5f, __fadd_rn(__fmul_rn(d, d), kLog2Pi));
+            const bool want_prior = p.prior != nullptr && yy < ty;
+            for (int c0 = 0; c0 < p.C; c0 += 8) {                // 8 channels per pass: 16 loads in flight per thread
+                float m[8], yv[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int c = c0 + j;
+                    m[j] = (idx >= 0 && c < p.C) ? __ldg(mub + (size_t)c * p.T_x + idx) : 0.f;
+                    yv[j] = (want_prior && c < p.C) ? __ldcs(p.y + ((size_t)b * p.C + c) * p.T_y + yy) : 0.f;
                 }
+                double dpart = 0.0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int c = c0 + j;
+                    if (c < p.C) {
+                        if (p.mu_y != nullptr) __stcs(p.mu_y + ((size_t)b * p.C + c) * p.T_y + yy, m[j]);
+                        const float d = __fsub_rn(yv[j], m[j]);
+                        dpart += (double)__fmul_rn(0.5f, __fadd_rn(__fmul_rn(d, d), kLog2Pi));
+                    }
+                }
+                if (want_prior) acc += dpart;
             }
         }
     }
