@@ -428,7 +428,7 @@ def run_reference(a):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.perf_counter() - t0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def run_ours(a):
@@ -487,8 +487,7 @@ def run_ours(a):
 
     if a.kernel_only:
         if rank == 0:
-            print(json.dumps({"metric": METRIC, "value": value_rate, "unit": UNIT, "ms_per_step": ms_per_step,
-                              "kernel_only": True}), flush=True)
+            _emit({"metric": METRIC, "value": value_rate, "unit": UNIT, "ms_per_step": ms_per_step, "kernel_only": True})
         if world > 1:
             dist.destroy_process_group()
         return
@@ -558,13 +557,22 @@ def run_ours(a):
             line["training_step"] = train
         if synth is not None:
             line["synthesis"] = synth
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def _emit(obj):
+    """The one JSON line goes to the process's ORIGINAL stdout; everything else any library prints to fd 1
+    during the run (NCCL prints its version banner there) has been redirected to stderr."""
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
 if __name__ == "__main__":
     args = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
