@@ -64,6 +64,18 @@ def workload_name(a):
     return f"maximum_path B={a.batch}/GPU T_text={a.tx} T_mel={a.ty} ragged 0.7-1.0 (BASELINE configs[1])"
 
 
+def mas_traffic(a):
+    """DRAM bytes per launch from the committed ncu --set full capture of THIS workload (profiles/r1_traffic.json), else None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            t = json.load(f)["mas_kernel"]
+        if t["workload"] == f"B={a.batch} T_text={a.tx} T_mel={a.ty} ragged 0.7-1.0":
+            return float(t["bytes"])
+    except Exception:
+        pass
+    return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -528,7 +540,7 @@ def run_ours(a):
                                   "stages": out[4], "tma": out[5], "ctas_per_sm": out[6]},
                        "parallelism": f"batch-sharded x{world}, no collective in the timed region"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                         "traffic": mas_traffic(a), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                          "kernel_ms": k_ms, "kernel": "mas_kernel<R,HAS_MASK=false>"},
             "e2e": {"value": e2e_rate, "unit": UNIT,
                     "h2d_bytes_per_step": int(4 * int((t_x_h.astype(np.int64) * t_y_h).sum()) + 8 * B),
