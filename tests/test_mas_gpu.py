@@ -188,3 +188,16 @@ def test_band_edge_all_offsets(ma):
         m[b, :T_x, : T_x + 64 + b] = 1
     want = omas.maximum_path_oracle(v, m)
     assert np.array_equal(_run(ma, v, m, mask_mode="prefix"), want)
+
+
+def test_band_edge_many_utterances_per_cta(ma):
+    """More utterances than resident CTAs (the steady-state writer path, bit words recycled between utterances)
+    with every item on the chunk-aligned band edge."""
+    rng = np.random.default_rng(77)
+    B, T_x, T_y = 700, 64, 192
+    v = (rng.standard_normal((B, T_x, T_y), dtype=np.float32) * 10 - 150).astype(np.float32)
+    v[np.arange(B), rng.integers(0, T_x, B), :] += 25.0
+    m = np.ones_like(v)
+    m[::3] = gen.ragged_mask(rng, B, T_x, T_y, lo=0.6)[::3]
+    want = omas.maximum_path_oracle(v, m)
+    assert np.array_equal(_run(ma, v, m, mask_mode="prefix"), want)
