@@ -623,6 +623,20 @@ static int solve_split(int B) {
     return s;
 }
 static long long ws_align(long long n) { return (n + 1023) & ~1023LL; }
+// side streams and fork / join events, created once per process
+static cudaStream_t g_side[kMaxSplit] = {};
+static cudaEvent_t g_ev_fork = nullptr, g_ev_join[kMaxSplit] = {};
+static int split_resources() {
+    if (g_ev_fork) return MB200_OK;
+    cudaEvent_t f;
+    MB200_CUDA_TRY(cudaEventCreateWithFlags(&f, cudaEventDisableTiming));
+    for (int i = 1; i < kMaxSplit; ++i) {
+        MB200_CUDA_TRY(cudaStreamCreateWithFlags(&g_side[i], cudaStreamNonBlocking));
+        MB200_CUDA_TRY(cudaEventCreateWithFlags(&g_ev_join[i], cudaEventDisableTiming));
+    }
+    g_ev_fork = f;
+    return MB200_OK;
+}
 
 extern "C" long long matcha_b200_decoder_workspace_bytes(int B, int T, int n_rows, int precision) {
     if (B <= 0 || T <= 0 || n_rows <= 0) return MB200_ERR_INVALID_ARG;
@@ -675,15 +689,42 @@ extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_d
     int rc = check_common(x_dev, mu_dev, mask_dev, t_dev, out_dev, blob_dev, B, T);
     if (rc != MB200_OK) return rc;
     if (!ws_dev || (n_t != 1 && n_t != B)) return MB200_ERR_INVALID_ARG;
-    Ctx c; DecW W; DecWb Wb;
-    rc = prepare(c, W, Wb, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, mask_dev, B, T, n_t, precision, stream);
-    if (rc != MB200_OK) return rc;
-    launch(c, time_embed1_kernel, dim3(n_t, 16), 256, 0, time_weights(W), t_dev, c.ws.th2);
-    launch(c, time_embed2_kernel, dim3(n_t, 24), 256, 0, time_weights(W), c.ws.th2, n_t, c.ws.tb);
-    eval_any(c, W, Wb, precision, x_dev, mu_dev, c.ws.tb, n_t, n_t == B && B > 1 ? 1 : 0, nullptr, 0.f, out_dev);
-    if (c.err) return c.err;
+    // same sub-batch streams as the Euler solve (one eval is a latency-bound chain of 46 launches at B = 32)
+    const int S = solve_split(B);
+    if (S > 1) { rc = split_resources(); if (rc != MB200_OK) return rc; }
+    Ctx c[kMaxSplit]; DecW W; DecWb Wb;
+    int b0[kMaxSplit + 1] = {};
+    char *wsp = (char *)ws_dev;
+    long long left = ws_bytes;
+    for (int i = 0; i < S; ++i) {
+        const int Bi = B / S + (i < B % S ? 1 : 0);
+        b0[i + 1] = b0[i] + Bi;
+        const long long need = S == 1 ? 0 : ws_align(carve_workspace(nullptr, Bi, T, n_t, precision, nullptr));
+        rc = prepare(c[i], W, Wb, blob_dev, blob_bf16_dev, wsp, left, mask_dev + (size_t)b0[i] * T, Bi, T, n_t, precision,
+                     i == 0 ? stream : (void *)g_side[i]);
+        if (rc != MB200_OK) return rc;
+        wsp += need; left -= need;
+    }
+    launch(c[0], time_embed1_kernel, dim3(n_t, 16), 256, 0, time_weights(W), t_dev, c[0].ws.th2);
+    launch(c[0], time_embed2_kernel, dim3(n_t, 24), 256, 0, time_weights(W), c[0].ws.th2, n_t, c[0].ws.tb);
+    if (S > 1) {
+        MB200_CUDA_TRY(cudaEventRecord(g_ev_fork, c[0].st));
+        for (int i = 1; i < S; ++i) MB200_CUDA_TRY(cudaStreamWaitEvent(c[i].st, g_ev_fork, 0));
+    }
+    const int per_sample = n_t == B && B > 1 ? 1 : 0;
+    for (int i = 0; i < S; ++i) {
+        const size_t off = (size_t)b0[i] * kMel * T;
+        const float *tb = c[0].ws.tb + (per_sample ? (size_t)b0[i] * kC : 0);     // rows of this sub-batch's samples
+        eval_any(c[i], W, Wb, precision, x_dev + off, mu_dev + off, tb, n_t, per_sample, nullptr, 0.f, out_dev + off);
+    }
+    int launches = 0;
+    for (int i = 0; i < S; ++i) { if (c[i].err) return c[i].err; launches += c[i].launches; }
+    for (int i = 1; i < S; ++i) {
+        MB200_CUDA_TRY(cudaEventRecord(g_ev_join[i], c[i].st));
+        MB200_CUDA_TRY(cudaStreamWaitEvent(c[0].st, g_ev_join[i], 0));
+    }
     MB200_CUDA_TRY(cudaGetLastError());
-    return c.launches;
+    return launches;
 }
 
 extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,
@@ -694,16 +735,9 @@ extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_
     if (rc != MB200_OK) return rc;
     if (!ws_dev || !dt_host || n_steps < 1 || n_steps > 64) return MB200_ERR_INVALID_ARG;
     const int S = solve_split(B);
-    // side streams and fork / join events, created once per process
-    static cudaStream_t side[kMaxSplit] = {};
-    static cudaEvent_t ev_fork = nullptr, ev_join[kMaxSplit] = {};
-    if (S > 1 && !ev_fork) {
-        MB200_CUDA_TRY(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-        for (int i = 1; i < kMaxSplit; ++i) {
-            MB200_CUDA_TRY(cudaStreamCreateWithFlags(&side[i], cudaStreamNonBlocking));
-            MB200_CUDA_TRY(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
-        }
-    }
+    if (S > 1) { rc = split_resources(); if (rc != MB200_OK) return rc; }
+    cudaStream_t *side = g_side;
+    cudaEvent_t ev_fork = g_ev_fork, *ev_join = g_ev_join;
     Ctx c[kMaxSplit]; DecW W; DecWb Wb;
     int b0[kMaxSplit + 1] = {};
     char *wsp = (char *)ws_dev;

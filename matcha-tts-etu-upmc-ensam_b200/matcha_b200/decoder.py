@@ -120,7 +120,9 @@ class Decoder(torch.nn.Module):
         self._blob16 = {}             # device -> bf16 GEMM weights (bf16 mode)
         self._ws = {}                 # (device, B, T, rows) -> workspace
         self._graphs = {}             # captured Euler solves
+        self._fwd_graphs = {}         # captured single evals (forward)
         self.use_graph = True
+        self.graph_forward = True     # replay forward() from a graph too (off: plain launches, e.g. for one-off shapes)
 
     # -- weights ----------------------------------------------------------------------------
     def initialize_weights(self, seed=0):
@@ -164,6 +166,8 @@ class Decoder(torch.nn.Module):
         self._weights = OrderedDict((k, sd[k].detach().to("cpu", torch.float32).clone()) for k in exp)
         self._blob.clear()
         self._blob16.clear()
+        self._graphs = {}             # captured graphs hold pointers into the old weight blobs
+        self._fwd_graphs = {}
         return self
 
     def state_dict(self, *a, **k):
@@ -212,14 +216,42 @@ class Decoder(torch.nn.Module):
         mf = mask.float().reshape(B, T).contiguous()
         tf = t.detach().to(dev, torch.float32).reshape(-1).contiguous()
         assert tf.numel() in (1, B)
-        out = torch.empty_like(xf)
-        blob, b16, ws = self._blob_on(dev), self._blob16_on(dev), self._workspace(dev, B, T, tf.numel())
-        with torch.cuda.device(dev):
-            check(lib.matcha_b200_decoder_forward(xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), tf.data_ptr(), tf.numel(),
-                                                  out.data_ptr(), blob.data_ptr(), b16.data_ptr() if b16 is not None else None,
-                                                  ws.data_ptr(), ws.numel(), B, T,
-                                                  _PRECISIONS[self.precision], _stream_ptr(dev)), "decoder_forward")
-        return out.to(x.dtype)
+        n_t = tf.numel()
+        blob, b16 = self._blob_on(dev), self._blob16_on(dev)
+
+        def launch(xf, muf, mf, tf, out, ws):
+            with torch.cuda.device(dev):
+                self.last_launches = check(lib.matcha_b200_decoder_forward(
+                    xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), tf.data_ptr(), n_t,
+                    out.data_ptr(), blob.data_ptr(), b16.data_ptr() if b16 is not None else None,
+                    ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision], _stream_ptr(dev)), "decoder_forward")
+
+        if not (self.use_graph and self.graph_forward) or torch.cuda.is_current_stream_capturing():
+            out = torch.empty_like(xf)
+            launch(xf, muf, mf, tf, out, self._workspace(dev, B, T, n_t))
+            return out.to(x.dtype)
+        # One eval is ~46 launches on each of 4 sub-batch streams: replayed from a CUDA graph per (B, T, n_t) like
+        # the solve (t is read from device memory, so one graph serves every time value).
+        key = (str(dev), B, T, n_t, self.precision)
+        entry = self._fwd_graphs.get(key)
+        if entry is None:
+            n_ws = int(lib.matcha_b200_decoder_workspace_bytes(B, T, n_t, _PRECISIONS[self.precision]))
+            st = {"x": xf.clone(), "mu": muf.clone(), "mask": mf.clone(), "t": tf.clone(), "out": torch.empty_like(xf),
+                  "ws": torch.empty(n_ws, dtype=torch.uint8, device=dev)}
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                launch(st["x"], st["mu"], st["mask"], st["t"], st["out"], st["ws"])   # warm-up outside the capture
+            torch.cuda.current_stream(dev).wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                launch(st["x"], st["mu"], st["mask"], st["t"], st["out"], st["ws"])
+            entry = (graph, st)
+            self._fwd_graphs = {key: entry}                            # keep one shape alive
+        graph, st = entry
+        st["x"].copy_(xf); st["mu"].copy_(muf); st["mask"].copy_(mf); st["t"].copy_(tf)
+        graph.replay()
+        return st["out"].to(x.dtype, copy=True)
 
     @torch.no_grad()
     def solve_euler(self, x, t_span, mu, mask, use_graph=None):
