@@ -73,10 +73,11 @@ def maximum_path_from_lengths(value, t_xs, t_ys, mask=None, out_dtype=torch.floa
         assert mask.is_cuda and mask.dtype == torch.float32 and mask.is_contiguous() and mask.shape == value.shape
         mptr = mask.data_ptr()
     status = torch.zeros(1, dtype=torch.int32, device=value.device) if check_lengths else None
+    t_xs, t_ys = t_xs.contiguous(), t_ys.contiguous()      # named: a temporary would be freed before the kernel reads it
     with torch.cuda.device(value.device):
         check(lib.matcha_b200_mas_compute_batch_alignments(
             path.data_ptr(), PATH_F32 if out_dtype == torch.float32 else PATH_I32,
-            value.data_ptr(), mptr, t_xs.contiguous().data_ptr(), t_ys.contiguous().data_ptr(),
+            value.data_ptr(), mptr, t_xs.data_ptr(), t_ys.data_ptr(),
             B, T_x, T_y, ctypes.c_float(max_neg_val),
             status.data_ptr() if status is not None else None, _stream_ptr(value.device)),
             "mas_compute_batch_alignments")
