@@ -567,6 +567,7 @@ def run_ours(a):
             line["gpu_launches"] = a.steps + 5 * dec["gpu_launches_per_solve"]
         if train is not None:
             line["training_step"] = train
+            line["gpu_launches"] += 10 * (3 + 2 + 185)      # 10 timed steps: align kernels, loss kernels, one graph-replayed eval
         if synth is not None:
             line["synthesis"] = synth
         _emit(line)

@@ -31,7 +31,6 @@ def test_no_cpu_fallback():
 
 
 def test_argument_validation_needs_no_gpu(lib):
-    INVALID = -1
     assert lib.matcha_b200_align_log_prior(None, None, None, None, None, 1, 80, 4, 8, None) < 0
     assert lib.matcha_b200_align_log_prior(None, None, None, None, None, -1, 80, 4, 8, None) < 0
     assert lib.matcha_b200_align_log_prior(None, None, None, None, None, 0, 80, 4, 8, None) == 0      # empty batch
@@ -42,4 +41,3 @@ def test_argument_validation_needs_no_gpu(lib):
     assert lib.matcha_b200_cfm_loss_mse(None, None, None, None, None, ctypes.c_double(1e-4), 10, 2, None) < 0
     assert lib.matcha_b200_mas_align(None, 1, None, None, None, None, None, 1, 4, 8, ctypes.c_float(-1e9), None, None) < 0
     assert lib.matcha_b200_mas_align(None, 1, None, None, None, None, None, 0, 4, 8, ctypes.c_float(-1e9), None, None) == 0
-    assert INVALID < 0
