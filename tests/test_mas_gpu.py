@@ -152,7 +152,9 @@ def test_full_size_properties_and_sampled_parity(ma, shape):
 # the sentinel arithmetic non-absorbing.  (t_y - t_x) % 32 == 0 puts the hand-over between two DP warps
 # exactly on a chunk boundary (regression: the value the lower row block reads there was never sent).
 BAND_SHAPES = [(1, 128, 800), (4, 128, 800), (3, 200, 1000), (2, 64, 200), (2, 96, 96 + 64), (1, 400, 2000),
-               (2, 160, 160 + 32), (3, 130, 130 + 320), (2, 33, 65)]
+               (2, 160, 160 + 32), (3, 130, 130 + 320), (2, 33, 65),
+               # larger rows-per-lane variants of the kernel (T_x 450 / 900 / 1300), chunk-aligned band edges
+               (2, 450, 450 + 96), (1, 900, 900 + 640), (1, 1300, 1300 + 32)]
 
 
 @pytest.mark.parametrize("shape", BAND_SHAPES)
