@@ -544,8 +544,8 @@ def run_ours(a):
                          "kernel_ms": k_ms, "kernel": "mas_kernel<R,HAS_MASK=false>"},
             "e2e": {"value": e2e_rate, "unit": UNIT,
                     "h2d_bytes_per_step": int(4 * int((t_x_h.astype(np.int64) * t_y_h).sum()) + 8 * B),
-                    "d2h_bytes_per_step": int(4 * int((t_x_h.astype(np.int64) * t_y_h).sum()) + 4), "steps": a.e2e_steps,
-                    "note": "valid [t_x][t_y] blocks only, sliced H2D / kernel / D2H pipeline; paths pre-zeroed by the caller as in the reference",
+                    "d2h_bytes_per_step": int(4 * B * T_x + 4), "steps": a.e2e_steps,
+                    "note": "valid [t_x][t_y] value blocks in, per-token durations out (expanded into the caller's pre-zeroed int32 paths on the host), sliced H2D / kernel / D2H pipeline",
                     "api": "matcha_b200.monotonic_align.compute_batch_alignments(numpy pinned) -> matcha_b200_mas_maximum_path_host",
                     "matches_device_result": same},
             "gpu_launches": a.steps, "clocks": clocks,

@@ -70,9 +70,10 @@ int matcha_b200_mas_lengths_from_mask(
 /*
  * Host buffers with the reference's C-level contract (core.pyx:101-107): `paths_host` must be
  * zero-initialised by the caller, exactly as the reference requires (__init__.py:49 passes np.zeros);
- * only the valid [t_x][t_y] block of every utterance is written.  Values and lengths go to the device
- * and int32 paths come back in slices through a three-stream pipeline (H2D, kernel and D2H overlap);
- * pinned host memory makes the copies asynchronous.  Returns the number of out-of-domain items (>= 0,
+ * only the ones of every utterance's path are written.  Values and lengths go to the device in slices
+ * through a three-stream pipeline (H2D, kernel and D2H overlap; pinned host memory makes the copies
+ * asynchronous); the alignment comes back in its compact form (per-token durations, [B][T_x] int32) and is
+ * expanded into paths_host on the host, one slice behind the GPU.  Returns the number of out-of-domain items (>= 0,
  * their paths stay zero) or a negative error.  Device scratch is allocated and freed inside the call.
  */
 int matcha_b200_mas_maximum_path_host(

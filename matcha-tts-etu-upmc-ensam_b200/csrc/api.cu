@@ -105,6 +105,24 @@ extern "C" const char *matcha_b200_version(void) { return "0.1.0"; }
 // Host-buffer MAS: the batch is cut into slices that flow through a three-stream pipeline (H2D of slice
 // i+1, kernel of slice i, D2H of slice i-1 run concurrently; PCIe is full duplex).  Only the valid
 // [t_x][t_y] block of every utterance crosses the bus in either direction, as 2-D copies.
+// path[b][x][y] = 1 for the dur[b][x] frames token x owns, in order (core.pyx:87-92 written forwards); the buffer
+// is pre-zeroed by the caller (__init__.py:49).  Items outside the DP's domain have all-zero durations.
+static void expand_durations_host(int *paths, const int *dur, const int *t_xs, const int *t_ys, int b_lo, int b_hi,
+                                  int T_x, int T_y) {
+    for (int b = b_lo; b < b_hi; ++b) {
+        const int tx = t_xs[b], ty = t_ys[b];
+        if (tx < 1 || ty < 1 || tx > ty || tx > T_x || ty > T_y) continue;
+        int *p = paths + (size_t)b * T_x * T_y;
+        const int *d = dur + (size_t)b * T_x;
+        int y = 0;
+        for (int x = 0; x < tx; ++x) {
+            int *row = p + (size_t)x * T_y;
+            const int e = y + d[x] < ty ? y + d[x] : ty;
+            for (; y < e; ++y) row[y] = 1;
+        }
+    }
+}
+
 extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *values_host,
                                                   const int *t_xs_host, const int *t_ys_host,
                                                   int B, int T_x, int T_y, float penalty) {
@@ -120,10 +138,10 @@ extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *v
     if (item * sizeof(float) * B < (64u << 20)) n_slices = 1;        // small batches: one shot
     const int Bs = (B + n_slices - 1) / n_slices;
     float *d_val[2] = {nullptr, nullptr};
-    int *d_path[2] = {nullptr, nullptr}, *d_len = nullptr;
+    int *d_path[2] = {nullptr, nullptr}, *d_len = nullptr, *d_dur = nullptr, *h_dur = nullptr;
     cudaStream_t st[3] = {nullptr, nullptr, nullptr};                // h2d, compute, d2h
     cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {};
-    int rc = MB200_OK, bad = 0;
+    int rc = MB200_OK, bad = 0, last_b0 = 0;
     cudaError_t e;
 #define HOST_TRY(x) do { e = (x); if (e != cudaSuccess) { rc = cuda_fail(e); goto done; } } while (0)
     for (int i = 0; i < 3; ++i) HOST_TRY(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
@@ -135,6 +153,11 @@ extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *v
         HOST_TRY(cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming));
     }
     HOST_TRY(cudaMalloc(&d_len, (2 * (size_t)B + 1) * sizeof(int)));
+    // The alignment crosses PCIe in its compact form: the kernel's per-token durations ([B][T_x] int32, 1.6 KB per
+    // utterance instead of up to 3.2 MB of 0/1 ints); the ones are written into the caller's pre-zeroed buffer here,
+    // one slice behind the GPU.
+    HOST_TRY(cudaMalloc(&d_dur, (size_t)B * T_x * sizeof(int)));
+    HOST_TRY(cudaMallocHost(&h_dur, (size_t)B * T_x * sizeof(int)));
     HOST_TRY(cudaMemcpyAsync(d_len, t_xs_host, B * sizeof(int), cudaMemcpyHostToDevice, st[1]));
     HOST_TRY(cudaMemcpyAsync(d_len + B, t_ys_host, B * sizeof(int), cudaMemcpyHostToDevice, st[1]));
     HOST_TRY(cudaMemsetAsync(d_len + 2 * B, 0, sizeof(int), st[1]));
@@ -155,26 +178,23 @@ extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *v
         }
         HOST_TRY(cudaEventRecord(ev_in[buf], st[0]));
         HOST_TRY(cudaStreamWaitEvent(st[1], ev_in[buf], 0));
-        if (s >= 2) HOST_TRY(cudaStreamWaitEvent(st[1], ev_out[buf], 0));   // path buffer drained
-        rc = matcha_b200_mas_compute_batch_alignments(d_path[buf], MB200_PATH_I32, d_val[buf], nullptr, d_len + b0,
-                                                      d_len + B + b0, nb, T_x, T_y, penalty, d_len + 2 * B, st[1]);
+        // d_path is the kernel's dense output / bit-word scratch; it stays on the device
+        rc = matcha_b200_mas_align(d_path[buf], MB200_PATH_I32, d_dur + (size_t)b0 * T_x, d_val[buf], nullptr, d_len + b0,
+                                   d_len + B + b0, nb, T_x, T_y, penalty, d_len + 2 * B, st[1]);
         if (rc != MB200_OK) goto done;
         HOST_TRY(cudaEventRecord(ev_k[buf], st[1]));
         HOST_TRY(cudaStreamWaitEvent(st[2], ev_k[buf], 0));
-        for (int i = 0; i < nb; ++i) {
-            const int tx = t_xs_host[b0 + i], ty = t_ys_host[b0 + i];
-            if (tx < 1 || ty < 1 || tx > ty || tx > T_x || ty > T_y) continue;   // invalid items: all-zero path
-            if (rows_only)
-                HOST_TRY(cudaMemcpyAsync(paths_host + (size_t)(b0 + i) * item, d_path[buf] + (size_t)i * item,
-                                         (size_t)tx * T_y * sizeof(int), cudaMemcpyDeviceToHost, st[2]));
-            else
-                HOST_TRY(cudaMemcpy2DAsync(paths_host + (size_t)(b0 + i) * item, (size_t)T_y * sizeof(int),
-                                           d_path[buf] + (size_t)i * item, (size_t)T_y * sizeof(int),
-                                           (size_t)ty * sizeof(int), (size_t)tx, cudaMemcpyDeviceToHost, st[2]));
-        }
+        HOST_TRY(cudaMemcpyAsync(h_dur + (size_t)b0 * T_x, d_dur + (size_t)b0 * T_x, (size_t)nb * T_x * sizeof(int),
+                                 cudaMemcpyDeviceToHost, st[2]));
         HOST_TRY(cudaEventRecord(ev_out[buf], st[2]));
+        if (s >= 1) {                                              // expand slice s-1 while slice s is in flight
+            HOST_TRY(cudaEventSynchronize(ev_out[buf ^ 1]));
+            expand_durations_host(paths_host, h_dur, t_xs_host, t_ys_host, b0 - Bs, b0, T_x, T_y);
+        }
+        last_b0 = b0;
     }
     HOST_TRY(cudaStreamSynchronize(st[2]));
+    expand_durations_host(paths_host, h_dur, t_xs_host, t_ys_host, last_b0, B, T_x, T_y);
     HOST_TRY(cudaMemcpyAsync(&bad, d_len + 2 * B, sizeof(int), cudaMemcpyDeviceToHost, st[1]));
     HOST_TRY(cudaStreamSynchronize(st[1]));
 #undef HOST_TRY
@@ -188,6 +208,8 @@ done:
         if (ev_out[i]) cudaEventDestroy(ev_out[i]);
     }
     if (d_len) cudaFree(d_len);
+    if (d_dur) cudaFree(d_dur);
+    if (h_dur) cudaFreeHost(h_dur);
     for (int i = 0; i < 3; ++i) if (st[i]) cudaStreamDestroy(st[i]);
     return rc != MB200_OK ? rc : bad;
 }
