@@ -5,7 +5,10 @@
  * success or a negative MB200_ERR_* code; matcha_b200_error_string() names it.
  * All *_dev pointers are device pointers on the current CUDA device; `stream` is a
  * cudaStream_t passed as void* (NULL = legacy default stream).  Device entry points
- * are asynchronous on `stream`, re-entrant, keep no global state and allocate nothing.
+ * are asynchronous on `stream`, thread-safe and allocate no device memory.  The MAS / alignment entry points keep no
+ * state at all.  The decoder entry points keep, per DEVICE and behind a mutex, the opt-in shared-memory attribute of
+ * their kernels and the side streams + events of the sub-batch split (created on first use; a call holds the device's
+ * mutex while it enqueues, so two host threads driving one device queue their calls one after the other).
  *
  * Reference interfaces replaced (paths under /root/reference):
  *   matcha_b200_mas_compute_batch_alignments  <- compute_batch_alignments,
@@ -74,12 +77,24 @@ int matcha_b200_mas_lengths_from_mask(
  * through a three-stream pipeline (H2D, kernel and D2H overlap; pinned host memory makes the copies
  * asynchronous); the alignment comes back in its compact form (per-token durations, [B][T_x] int32) and is
  * expanded into paths_host on the host, one slice behind the GPU.  Returns the number of out-of-domain items (>= 0,
- * their paths stay zero) or a negative error.  Device scratch is allocated and freed inside the call.
+ * their paths stay zero) or a negative error.  Synchronous, like the reference call.
+ *
+ * Scratch (three streams, six events, four device slabs, a pinned durations buffer) lives in a handle and is reused
+ * across calls: grown when a larger batch arrives, never shrunk, freed by _destroy.  One call at a time per handle
+ * (internal mutex).  The handle-less form uses a process-wide default handle (matcha_b200_mas_host_release frees its
+ * scratch; the next call re-creates it).
  */
+void *matcha_b200_mas_host_create(void);
+int matcha_b200_mas_host_destroy(void *handle);
+int matcha_b200_mas_maximum_path_host_h(
+    void *handle, int *paths_host, const float *values_host,
+    const int *t_xs_host, const int *t_ys_host,
+    int B, int T_x, int T_y, float penalty);
 int matcha_b200_mas_maximum_path_host(
     int *paths_host, const float *values_host,
     const int *t_xs_host, const int *t_ys_host,
     int B, int T_x, int T_y, float penalty);
+int matcha_b200_mas_host_release(void);
 
 /* scores[i] = values[i] * mask[i] (__init__.py:45), for callers whose shape is too large for the
  * fused-mask variant of the MAS kernel (query_launch with has_mask=1 returns MB200_ERR_UNSUPPORTED):

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-shared", "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
+         "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
 
 
 def sources():
@@ -33,8 +33,24 @@ def build(force=False, verbose=False):
         return lib_file()
     os.makedirs(os.path.join(HERE, "lib"), exist_ok=True)
     extra = os.environ.get("MB200_NVCC_EXTRA", "").split()          # e.g. -DSOME_PROFILING_SWITCH=1
-    cmd = [NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", lib_file()] + sources()
-    subprocess.run(cmd, check=True, cwd=HERE)
+    # one nvcc -c per source, side by side (objects under build/, git-ignored), then one link
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    hdr_deps = glob.glob(os.path.join(HERE, "csrc", "*.cuh")) + glob.glob(os.path.join(HERE, "..", "include", "*.h")) + \
+        [os.path.abspath(__file__)]
+    jobs, objs = [], []
+    for src in sources():
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
+        objs.append(obj)
+        fresh = os.path.exists(obj) and all(os.path.getmtime(d) <= os.path.getmtime(obj) for d in [src] + hdr_deps)
+        if fresh and not force and not extra and not verbose:
+            continue
+        cmd = [NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
+        jobs.append((cmd, subprocess.Popen(cmd, cwd=HERE)))
+    for cmd, p in jobs:
+        if p.wait() != 0:
+            raise subprocess.CalledProcessError(p.returncode, cmd)
+    subprocess.run([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib_file()] + objs, check=True, cwd=HERE)
     return lib_file()
 
 

@@ -4,6 +4,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+#include <new>
+
 #include "common.cuh"
 
 namespace mb200 {
@@ -123,12 +126,91 @@ static void expand_durations_host(int *paths, const int *dur, const int *t_xs, c
     }
 }
 
-extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *values_host,
-                                                  const int *t_xs_host, const int *t_ys_host,
-                                                  int B, int T_x, int T_y, float penalty) {
+// Scratch of the host-buffer entry, kept across calls: three streams (h2d, compute, d2h), the events between them, two
+// value slabs + two path slabs on the device, the lengths and the durations buffers (device + pinned host).  Grown on
+// demand, never shrunk; one call at a time per handle (mutex).
+struct MasHost {
+    std::mutex mu;
+    int dev = -1;
+    cudaStream_t st[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {};
+    float *d_val[2] = {nullptr, nullptr};
+    int *d_path[2] = {nullptr, nullptr};
+    size_t slab_bytes = 0;
+    int *d_len = nullptr; size_t len_cap = 0;
+    int *d_dur = nullptr, *h_dur = nullptr; size_t dur_cap = 0;
+    bool ready = false;
+};
+
+static void mas_host_free(MasHost &h) {
+    for (int i = 0; i < 3; ++i) if (h.st[i]) { cudaStreamSynchronize(h.st[i]); }
+    for (int i = 0; i < 2; ++i) {
+        if (h.d_val[i]) cudaFree(h.d_val[i]);
+        if (h.d_path[i]) cudaFree(h.d_path[i]);
+        if (h.ev_in[i]) cudaEventDestroy(h.ev_in[i]);
+        if (h.ev_k[i]) cudaEventDestroy(h.ev_k[i]);
+        if (h.ev_out[i]) cudaEventDestroy(h.ev_out[i]);
+        h.d_val[i] = nullptr; h.d_path[i] = nullptr; h.ev_in[i] = h.ev_k[i] = h.ev_out[i] = nullptr;
+    }
+    if (h.d_len) cudaFree(h.d_len);
+    if (h.d_dur) cudaFree(h.d_dur);
+    if (h.h_dur) cudaFreeHost(h.h_dur);
+    for (int i = 0; i < 3; ++i) if (h.st[i]) { cudaStreamDestroy(h.st[i]); h.st[i] = nullptr; }
+    h.d_len = h.d_dur = h.h_dur = nullptr;
+    h.slab_bytes = h.len_cap = h.dur_cap = 0;
+    h.ready = false;
+}
+
+static int mas_host_ensure(MasHost &h, size_t slab_bytes, size_t n_len, size_t n_dur) {
+    int dev = -1;
+    MB200_CUDA_TRY(cudaGetDevice(&dev));
+    if (h.ready && h.dev != dev) mas_host_free(h);            // the handle follows the caller's current device
+    if (!h.ready) {
+        h.dev = dev;
+        for (int i = 0; i < 3; ++i) MB200_CUDA_TRY(cudaStreamCreateWithFlags(&h.st[i], cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            MB200_CUDA_TRY(cudaEventCreateWithFlags(&h.ev_in[i], cudaEventDisableTiming));
+            MB200_CUDA_TRY(cudaEventCreateWithFlags(&h.ev_k[i], cudaEventDisableTiming));
+            MB200_CUDA_TRY(cudaEventCreateWithFlags(&h.ev_out[i], cudaEventDisableTiming));
+        }
+        h.ready = true;
+    }
+    if (slab_bytes > h.slab_bytes) {
+        for (int i = 0; i < 2; ++i) {
+            if (h.d_val[i]) cudaFree(h.d_val[i]);
+            if (h.d_path[i]) cudaFree(h.d_path[i]);
+            h.d_val[i] = nullptr; h.d_path[i] = nullptr;
+        }
+        h.slab_bytes = 0;
+        for (int i = 0; i < 2; ++i) {
+            MB200_CUDA_TRY(cudaMalloc(&h.d_val[i], slab_bytes));
+            MB200_CUDA_TRY(cudaMalloc(&h.d_path[i], slab_bytes));
+        }
+        h.slab_bytes = slab_bytes;
+    }
+    if (n_len > h.len_cap) {
+        if (h.d_len) cudaFree(h.d_len);
+        h.d_len = nullptr; h.len_cap = 0;
+        MB200_CUDA_TRY(cudaMalloc(&h.d_len, n_len * sizeof(int)));
+        h.len_cap = n_len;
+    }
+    if (n_dur > h.dur_cap) {
+        if (h.d_dur) cudaFree(h.d_dur);
+        if (h.h_dur) cudaFreeHost(h.h_dur);
+        h.d_dur = h.h_dur = nullptr; h.dur_cap = 0;
+        MB200_CUDA_TRY(cudaMalloc(&h.d_dur, n_dur * sizeof(int)));
+        MB200_CUDA_TRY(cudaMallocHost(&h.h_dur, n_dur * sizeof(int)));
+        h.dur_cap = n_dur;
+    }
+    return MB200_OK;
+}
+
+static int mas_host_run(MasHost &h, int *paths_host, const float *values_host, const int *t_xs_host, const int *t_ys_host,
+                        int B, int T_x, int T_y, float penalty) {
     if (B < 0 || T_x <= 0 || T_y <= 0) return MB200_ERR_INVALID_ARG;
     if (B == 0) return 0;
     if (!paths_host || !values_host || !t_xs_host || !t_ys_host) return MB200_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lock(h.mu);
     const size_t item = (size_t)T_x * T_y;
     const char *envm = getenv("MB200_MAS_HOST_MODE");     // experiments: 1 = contiguous [t_x][T_y] row blocks instead of 2-D copies
     const bool rows_only = envm && envm[0] == '1';
@@ -137,27 +219,19 @@ extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *v
     if (n_slices < 1) n_slices = 1;
     if (item * sizeof(float) * B < (64u << 20)) n_slices = 1;        // small batches: one shot
     const int Bs = (B + n_slices - 1) / n_slices;
-    float *d_val[2] = {nullptr, nullptr};
-    int *d_path[2] = {nullptr, nullptr}, *d_len = nullptr, *d_dur = nullptr, *h_dur = nullptr;
-    cudaStream_t st[3] = {nullptr, nullptr, nullptr};                // h2d, compute, d2h
-    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {};
-    int rc = MB200_OK, bad = 0, last_b0 = 0;
+    int rc = mas_host_ensure(h, (size_t)Bs * item * sizeof(float), 2 * (size_t)B + 1, (size_t)B * T_x);
+    if (rc != MB200_OK) return rc;
+    float *const *d_val = h.d_val;
+    int *const *d_path = h.d_path;
+    int *d_len = h.d_len, *d_dur = h.d_dur, *h_dur = h.h_dur;
+    cudaStream_t *st = h.st;                                         // h2d, compute, d2h
+    cudaEvent_t *ev_in = h.ev_in, *ev_k = h.ev_k, *ev_out = h.ev_out;
+    int bad = 0, last_b0 = 0;
     cudaError_t e;
 #define HOST_TRY(x) do { e = (x); if (e != cudaSuccess) { rc = cuda_fail(e); goto done; } } while (0)
-    for (int i = 0; i < 3; ++i) HOST_TRY(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
-    for (int i = 0; i < 2; ++i) {
-        HOST_TRY(cudaMalloc(&d_val[i], (size_t)Bs * item * sizeof(float)));
-        HOST_TRY(cudaMalloc(&d_path[i], (size_t)Bs * item * sizeof(int)));
-        HOST_TRY(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
-        HOST_TRY(cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming));
-        HOST_TRY(cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming));
-    }
-    HOST_TRY(cudaMalloc(&d_len, (2 * (size_t)B + 1) * sizeof(int)));
     // The alignment crosses PCIe in its compact form: the kernel's per-token durations ([B][T_x] int32, 1.6 KB per
     // utterance instead of up to 3.2 MB of 0/1 ints); the ones are written into the caller's pre-zeroed buffer here,
     // one slice behind the GPU.
-    HOST_TRY(cudaMalloc(&d_dur, (size_t)B * T_x * sizeof(int)));
-    HOST_TRY(cudaMallocHost(&h_dur, (size_t)B * T_x * sizeof(int)));
     HOST_TRY(cudaMemcpyAsync(d_len, t_xs_host, B * sizeof(int), cudaMemcpyHostToDevice, st[1]));
     HOST_TRY(cudaMemcpyAsync(d_len + B, t_ys_host, B * sizeof(int), cudaMemcpyHostToDevice, st[1]));
     HOST_TRY(cudaMemsetAsync(d_len + 2 * B, 0, sizeof(int), st[1]));
@@ -199,17 +273,43 @@ extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *v
     HOST_TRY(cudaStreamSynchronize(st[1]));
 #undef HOST_TRY
 done:
-    for (int i = 0; i < 3; ++i) if (st[i]) cudaStreamSynchronize(st[i]);
-    for (int i = 0; i < 2; ++i) {
-        if (d_val[i]) cudaFree(d_val[i]);
-        if (d_path[i]) cudaFree(d_path[i]);
-        if (ev_in[i]) cudaEventDestroy(ev_in[i]);
-        if (ev_k[i]) cudaEventDestroy(ev_k[i]);
-        if (ev_out[i]) cudaEventDestroy(ev_out[i]);
-    }
-    if (d_len) cudaFree(d_len);
-    if (d_dur) cudaFree(d_dur);
-    if (h_dur) cudaFreeHost(h_dur);
-    for (int i = 0; i < 3; ++i) if (st[i]) cudaStreamDestroy(st[i]);
+    for (int i = 0; i < 3; ++i) if (st[i]) cudaStreamSynchronize(st[i]);     // the call is synchronous, like the reference
     return rc != MB200_OK ? rc : bad;
+}
+
+static MasHost &default_mas_host() {
+    static MasHost h;
+    return h;
+}
+
+extern "C" void *matcha_b200_mas_host_create(void) { return new (std::nothrow) MasHost(); }
+
+extern "C" int matcha_b200_mas_host_destroy(void *handle) {
+    if (!handle) return MB200_ERR_INVALID_ARG;
+    MasHost *h = static_cast<MasHost *>(handle);
+    { std::lock_guard<std::mutex> lock(h->mu); mas_host_free(*h); }
+    delete h;
+    return MB200_OK;
+}
+
+extern "C" int matcha_b200_mas_maximum_path_host_h(void *handle, int *paths_host, const float *values_host,
+                                                    const int *t_xs_host, const int *t_ys_host,
+                                                    int B, int T_x, int T_y, float penalty) {
+    if (!handle) return MB200_ERR_INVALID_ARG;
+    return mas_host_run(*static_cast<MasHost *>(handle), paths_host, values_host, t_xs_host, t_ys_host, B, T_x, T_y, penalty);
+}
+
+// The handle-less form of the reference's call shape: a process-wide default handle, created on first use.
+extern "C" int matcha_b200_mas_maximum_path_host(int *paths_host, const float *values_host,
+                                                  const int *t_xs_host, const int *t_ys_host,
+                                                  int B, int T_x, int T_y, float penalty) {
+    return mas_host_run(default_mas_host(), paths_host, values_host, t_xs_host, t_ys_host, B, T_x, T_y, penalty);
+}
+
+// Frees the default handle's device / pinned scratch (it is re-created on the next call).
+extern "C" int matcha_b200_mas_host_release(void) {
+    MasHost &h = default_mas_host();
+    std::lock_guard<std::mutex> lock(h.mu);
+    mas_host_free(h);
+    return MB200_OK;
 }

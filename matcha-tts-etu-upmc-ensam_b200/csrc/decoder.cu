@@ -11,6 +11,7 @@
 // implicit-GEMM loader.
 #include <stdlib.h>
 
+#include <mutex>
 #include <vector>
 
 #include "attention_mma.cuh"
@@ -589,14 +590,6 @@ int prepare(Ctx &c, DecW &W, DecWb &Wb, const float *blob, const void *blob_bf16
     if ((uintptr_t)ws % 16 != 0 || (uintptr_t)blob % 16 != 0 || (uintptr_t)blob_bf16 % 16 != 0) return MB200_ERR_INVALID_ARG;
     carve_workspace((float *)ws, B, T, n_rows, precision, &c.ws);
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = precision == MB200_PREC_F16 ? 1 : 0;
-    static bool attr_set = false;
-    if (!attr_set) {
-        MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
-        { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
-        MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
-        MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
-        attr_set = true;
-    }
     return MB200_OK;
 }
 void eval_any(Ctx &c, const DecW &W, const DecWb &Wb, int precision, const float *x, const float *mu,
@@ -623,18 +616,48 @@ static int solve_split(int B) {
     return s;
 }
 static long long ws_align(long long n) { return (n + 1023) & ~1023LL; }
-// side streams and fork / join events, created once per process
-static cudaStream_t g_side[kMaxSplit] = {};
-static cudaEvent_t g_ev_fork = nullptr, g_ev_join[kMaxSplit] = {};
-static int split_resources() {
-    if (g_ev_fork) return MB200_OK;
-    cudaEvent_t f;
-    MB200_CUDA_TRY(cudaEventCreateWithFlags(&f, cudaEventDisableTiming));
-    for (int i = 1; i < kMaxSplit; ++i) {
-        MB200_CUDA_TRY(cudaStreamCreateWithFlags(&g_side[i], cudaStreamNonBlocking));
-        MB200_CUDA_TRY(cudaEventCreateWithFlags(&g_ev_join[i], cudaEventDisableTiming));
+
+// The only state the decoder entry points keep: per DEVICE, created on first use and cached -- the opt-in shared-memory
+// attribute of the kernels (a per-device function attribute) and the side streams + fork / join events of the sub-batch
+// split.  DevGuard holds the device's mutex for the whole enqueue of one call, so two host threads driving the same
+// device queue their calls one after the other (the event record / stream wait pairs of one call are never interleaved
+// with another call's); different devices do not share anything.
+constexpr int kMaxDevices = 64;
+struct DevRes {
+    std::mutex mu;
+    bool attr_set = false, split_ready = false;
+    cudaStream_t side[kMaxSplit] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxSplit] = {};
+};
+static DevRes g_dev[kMaxDevices];
+struct DevGuard {
+    DevRes *r = nullptr;
+    int rc = MB200_OK;
+    DevGuard() {
+        int dev = -1;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) { rc = MB200_ERR_NO_DEVICE; return; }
+        r = &g_dev[dev];
+        r->mu.lock();
     }
-    g_ev_fork = f;
+    ~DevGuard() { if (r) r->mu.unlock(); }
+};
+static int set_attributes(DevRes &r) {
+    if (r.attr_set) return MB200_OK;
+    MB200_CUDA_TRY(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
+    { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
+    MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmemBytes));
+    r.attr_set = true;
+    return MB200_OK;
+}
+static int split_resources(DevRes &r) {
+    if (r.split_ready) return MB200_OK;
+    MB200_CUDA_TRY(cudaEventCreateWithFlags(&r.ev_fork, cudaEventDisableTiming));
+    for (int i = 1; i < kMaxSplit; ++i) {
+        MB200_CUDA_TRY(cudaStreamCreateWithFlags(&r.side[i], cudaStreamNonBlocking));
+        MB200_CUDA_TRY(cudaEventCreateWithFlags(&r.ev_join[i], cudaEventDisableTiming));
+    }
+    r.split_ready = true;
     return MB200_OK;
 }
 
@@ -691,7 +714,13 @@ extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_d
     if (!ws_dev || (n_t != 1 && n_t != B)) return MB200_ERR_INVALID_ARG;
     // same sub-batch streams as the Euler solve (one eval is a latency-bound chain of 46 launches at B = 32)
     const int S = solve_split(B);
-    if (S > 1) { rc = split_resources(); if (rc != MB200_OK) return rc; }
+    DevGuard guard;
+    if (guard.rc != MB200_OK) return guard.rc;
+    DevRes &dr = *guard.r;
+    rc = set_attributes(dr); if (rc != MB200_OK) return rc;
+    if (S > 1) { rc = split_resources(dr); if (rc != MB200_OK) return rc; }
+    cudaStream_t *g_side = dr.side;
+    cudaEvent_t g_ev_fork = dr.ev_fork, *g_ev_join = dr.ev_join;
     Ctx c[kMaxSplit]; DecW W; DecWb Wb;
     int b0[kMaxSplit + 1] = {};
     char *wsp = (char *)ws_dev;
@@ -735,9 +764,13 @@ extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_
     if (rc != MB200_OK) return rc;
     if (!ws_dev || !dt_host || n_steps < 1 || n_steps > 64) return MB200_ERR_INVALID_ARG;
     const int S = solve_split(B);
-    if (S > 1) { rc = split_resources(); if (rc != MB200_OK) return rc; }
-    cudaStream_t *side = g_side;
-    cudaEvent_t ev_fork = g_ev_fork, *ev_join = g_ev_join;
+    DevGuard guard;
+    if (guard.rc != MB200_OK) return guard.rc;
+    DevRes &dr = *guard.r;
+    rc = set_attributes(dr); if (rc != MB200_OK) return rc;
+    if (S > 1) { rc = split_resources(dr); if (rc != MB200_OK) return rc; }
+    cudaStream_t *side = dr.side;
+    cudaEvent_t ev_fork = dr.ev_fork, *ev_join = dr.ev_join;
     Ctx c[kMaxSplit]; DecW W; DecWb Wb;
     int b0[kMaxSplit + 1] = {};
     char *wsp = (char *)ws_dev;

@@ -47,6 +47,12 @@ def load_library():
     lib.matcha_b200_mas_lengths_from_mask.argtypes = [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]
     lib.matcha_b200_mas_maximum_path_host.restype = c_int
     lib.matcha_b200_mas_maximum_path_host.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float]
+    lib.matcha_b200_mas_host_create.restype = c_void_p
+    lib.matcha_b200_mas_host_destroy.restype = c_int
+    lib.matcha_b200_mas_host_destroy.argtypes = [c_void_p]
+    lib.matcha_b200_mas_maximum_path_host_h.restype = c_int
+    lib.matcha_b200_mas_maximum_path_host_h.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float]
+    lib.matcha_b200_mas_host_release.restype = c_int
     lib.matcha_b200_mas_query_launch.restype = c_int
     lib.matcha_b200_mas_query_launch.argtypes = [c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int * 8)]
     lib.matcha_b200_mas_apply_mask.restype = c_int
@@ -103,6 +109,10 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_compute_batch_alignments",
     "matcha_b200_mas_lengths_from_mask",
     "matcha_b200_mas_maximum_path_host",
+    "matcha_b200_mas_host_create",
+    "matcha_b200_mas_host_destroy",
+    "matcha_b200_mas_maximum_path_host_h",
+    "matcha_b200_mas_host_release",
     "matcha_b200_mas_query_launch",
     "matcha_b200_mas_apply_mask",
     "matcha_b200_mas_align",

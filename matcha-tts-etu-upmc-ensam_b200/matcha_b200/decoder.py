@@ -118,9 +118,11 @@ class Decoder(torch.nn.Module):
         self._weights = None          # reference-named fp32 tensors (CPU)
         self._blob = {}               # device -> packed fp32 blob
         self._blob16 = {}             # device -> bf16 GEMM weights (bf16 mode)
-        self._ws = {}                 # (device, B, T, rows) -> workspace
-        self._graphs = {}             # captured Euler solves
-        self._fwd_graphs = {}         # captured single evals (forward)
+        self._ws = {}                 # (device, B, T, rows) -> workspace of the plain-launch path (one shape kept)
+        self._graphs = OrderedDict()      # captured Euler solves, LRU; every entry OWNS its workspace and I/O tensors
+        self._fwd_graphs = OrderedDict()  # captured single evals (forward), LRU, same ownership
+        self._fwd_seen = {}           # forward() shapes seen once: captured only when they come back
+        self.graph_cache_size = 4     # shapes kept per cache
         self.use_graph = True
         self.graph_forward = True     # replay forward() from a graph too (off: plain launches, e.g. for one-off shapes)
 
@@ -166,8 +168,9 @@ class Decoder(torch.nn.Module):
         self._weights = OrderedDict((k, sd[k].detach().to("cpu", torch.float32).clone()) for k in exp)
         self._blob.clear()
         self._blob16.clear()
-        self._graphs = {}             # captured graphs hold pointers into the old weight blobs
-        self._fwd_graphs = {}
+        self._graphs.clear()          # captured graphs hold pointers into the old weight blobs
+        self._fwd_graphs.clear()
+        self._fwd_seen.clear()
         return self
 
     def state_dict(self, *a, **k):
@@ -196,12 +199,28 @@ class Decoder(torch.nn.Module):
             self._blob16[key] = buf
         return self._blob16[key]
 
+    def _new_workspace(self, device, B, T, rows):
+        n = int(load_library().matcha_b200_decoder_workspace_bytes(B, T, rows, _PRECISIONS[self.precision]))
+        return torch.empty(n, dtype=torch.uint8, device=device)
+
     def _workspace(self, device, B, T, rows):
+        """Scratch of the plain-launch path only.  Captured graphs never point here: each graph entry owns its own
+        workspace (a pointer baked into a graph must outlive every replay), so replacing this one is always safe."""
         key = (str(device), B, T, rows, self.precision)
         if key not in self._ws:
-            n = int(load_library().matcha_b200_decoder_workspace_bytes(B, T, rows, _PRECISIONS[self.precision]))
-            self._ws = {key: torch.empty(n, dtype=torch.uint8, device=device)}      # keep one shape alive
+            self._ws = {key: self._new_workspace(device, B, T, rows)}               # keep one shape alive
         return self._ws[key]
+
+    def _cache_get(self, cache, key):
+        entry = cache.get(key)
+        if entry is not None:
+            cache.move_to_end(key)
+        return entry
+
+    def _cache_put(self, cache, key, entry):
+        cache[key] = entry
+        while len(cache) > max(1, int(self.graph_cache_size)):
+            cache.popitem(last=False)          # least recently used; its graph, workspace and I/O tensors go together
 
     # -- forward ----------------------------------------------------------------------------
     @torch.no_grad()
@@ -226,18 +245,25 @@ class Decoder(torch.nn.Module):
                     out.data_ptr(), blob.data_ptr(), b16.data_ptr() if b16 is not None else None,
                     ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision], _stream_ptr(dev)), "decoder_forward")
 
-        if not (self.use_graph and self.graph_forward) or torch.cuda.is_current_stream_capturing():
+        # One eval is ~46 launches on each of 4 sub-batch streams: replayed from a CUDA graph per (B, T, n_t) like
+        # the solve (t is read from device memory, so one graph serves every time value).  A shape is captured the
+        # second time it is seen: a one-off shape (variable-length training batches through compute_loss) costs a
+        # warm-up launch + capture + fresh buffers, more than the launches a single replay saves.
+        key = (str(dev), B, T, n_t, self.precision)
+        graphable = self.use_graph and self.graph_forward and not torch.cuda.is_current_stream_capturing()
+        entry = self._cache_get(self._fwd_graphs, key) if graphable else None
+        if graphable and entry is None and self._fwd_seen.get(key, 0) < 1:
+            if len(self._fwd_seen) > 64:
+                self._fwd_seen.clear()
+            self._fwd_seen[key] = 1
+            graphable = False
+        if not graphable:
             out = torch.empty_like(xf)
             launch(xf, muf, mf, tf, out, self._workspace(dev, B, T, n_t))
             return out.to(x.dtype)
-        # One eval is ~46 launches on each of 4 sub-batch streams: replayed from a CUDA graph per (B, T, n_t) like
-        # the solve (t is read from device memory, so one graph serves every time value).
-        key = (str(dev), B, T, n_t, self.precision)
-        entry = self._fwd_graphs.get(key)
         if entry is None:
-            n_ws = int(lib.matcha_b200_decoder_workspace_bytes(B, T, n_t, _PRECISIONS[self.precision]))
             st = {"x": xf.clone(), "mu": muf.clone(), "mask": mf.clone(), "t": tf.clone(), "out": torch.empty_like(xf),
-                  "ws": torch.empty(n_ws, dtype=torch.uint8, device=dev)}
+                  "ws": self._new_workspace(dev, B, T, n_t)}
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
@@ -247,7 +273,7 @@ class Decoder(torch.nn.Module):
             with torch.cuda.graph(graph):
                 launch(st["x"], st["mu"], st["mask"], st["t"], st["out"], st["ws"])
             entry = (graph, st)
-            self._fwd_graphs = {key: entry}                            # keep one shape alive
+            self._cache_put(self._fwd_graphs, key, entry)
         graph, st = entry
         st["x"].copy_(xf); st["mu"].copy_(muf); st["mask"].copy_(mf); st["t"].copy_(tf)
         graph.replay()
@@ -265,11 +291,11 @@ class Decoder(torch.nn.Module):
         n = len(ts)
         if use_graph is None:
             use_graph = self.use_graph
-        blob, b16, ws = self._blob_on(dev), self._blob16_on(dev), self._workspace(dev, B, T, n)
+        blob, b16 = self._blob_on(dev), self._blob16_on(dev)
         t_arr = (ctypes.c_float * n)(*[float(v) for v in ts])
         dt_arr = (ctypes.c_float * n)(*[float(v) for v in dts])
 
-        def launch(xf, muf, mf, out):
+        def launch(xf, muf, mf, out, ws):
             with torch.cuda.device(dev):
                 self.last_launches = check(lib.matcha_b200_cfm_solve_euler(
                     xf.data_ptr(), muf.data_ptr(), mf.data_ptr(), out.data_ptr(), t_arr, dt_arr, n, blob.data_ptr(),
@@ -280,25 +306,26 @@ class Decoder(torch.nn.Module):
             xf, muf = x.float().contiguous(), mu.float().contiguous()
             mf = mask.float().reshape(B, T).contiguous()
             out = torch.empty_like(xf)
-            launch(xf, muf, mf, out)
+            launch(xf, muf, mf, out, self._workspace(dev, B, T, n))
             return out.to(x.dtype)
 
         key = (str(dev), B, T, tuple(float(v) for v in ts), tuple(float(v) for v in dts), self.precision)
-        entry = self._graphs.get(key)
+        entry = self._cache_get(self._graphs, key)
         if entry is None:
             st = {"x": torch.empty(B, 80, T, device=dev), "mu": torch.empty(B, 80, T, device=dev),
-                  "mask": torch.empty(B, T, device=dev), "out": torch.empty(B, 80, T, device=dev)}
+                  "mask": torch.empty(B, T, device=dev), "out": torch.empty(B, 80, T, device=dev),
+                  "ws": self._new_workspace(dev, B, T, n)}            # owned by the graph entry (see _workspace)
             st["x"].copy_(x); st["mu"].copy_(mu); st["mask"].copy_(mask.reshape(B, T))
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
-                launch(st["x"], st["mu"], st["mask"], st["out"])      # warm-up outside the capture (sets attributes)
+                launch(st["x"], st["mu"], st["mask"], st["out"], st["ws"])      # warm-up outside the capture (sets attributes)
             torch.cuda.current_stream(dev).wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                launch(st["x"], st["mu"], st["mask"], st["out"])
+                launch(st["x"], st["mu"], st["mask"], st["out"], st["ws"])
             entry = (graph, st)
-            self._graphs = {key: entry}                                # keep one shape alive
+            self._cache_put(self._graphs, key, entry)
         graph, st = entry
         st["x"].copy_(x); st["mu"].copy_(mu); st["mask"].copy_(mask.reshape(B, T))
         graph.replay()

@@ -116,7 +116,7 @@ def sinusoidal_embedding(t, dim=IN_CH, scale=1000):
     half = dim // 2
     emb = torch.log(torch.tensor(10000.0)) / (half - 1)
     emb = torch.exp(torch.arange(half, dtype=torch.float32) * -emb)
-    emb = scale * t.unsqueeze(1) * emb.unsqueeze(0).to(t.dtype)
+    emb = scale * t.unsqueeze(1) * emb.unsqueeze(0).to(device=t.device, dtype=t.dtype)
     return torch.cat((emb.sin(), emb.cos()), dim=-1)
 
 
@@ -138,6 +138,12 @@ def resnet1d(w, p, x, mask, temb):
     return h + F.conv1d(x * mask, w[p + ".res_conv.weight"], w[p + ".res_conv.bias"])       # :85 (unmasked)
 
 
+# True: the attention core goes through F.scaled_dot_product_attention with the float mask as attn_mask, which is
+# how diffusers' AttnProcessor2_0 calls it (the same-box GPU baseline of bench.py uses this form so that torch may
+# pick its fused kernels); False: the explicit softmax below (the form the golden fixtures pin).  Same arithmetic.
+USE_SDPA = False
+
+
 def transformer_block(w, p, x, mask_bt):
     """x [B,T,C]; mask_bt [B,T] float 0/1 (transformer.py:316-368 with attn2=None)."""
     B, T, _ = x.shape
@@ -145,8 +151,11 @@ def transformer_block(w, p, x, mask_bt):
     q = F.linear(h, w[p + ".attn1.to_q.weight"]).view(B, T, HEADS, DHEAD).transpose(1, 2)
     k = F.linear(h, w[p + ".attn1.to_k.weight"]).view(B, T, HEADS, DHEAD).transpose(1, 2)
     v = F.linear(h, w[p + ".attn1.to_v.weight"]).view(B, T, HEADS, DHEAD).transpose(1, 2)
-    logits = q @ k.transpose(-1, -2) * (DHEAD ** -0.5) + mask_bt[:, None, None, :]          # float mask is ADDED
-    a = torch.softmax(logits, dim=-1) @ v
+    if USE_SDPA:
+        a = F.scaled_dot_product_attention(q, k, v, attn_mask=mask_bt[:, None, None, :].to(q.dtype), dropout_p=0.0, is_causal=False)
+    else:
+        logits = q @ k.transpose(-1, -2) * (DHEAD ** -0.5) + mask_bt[:, None, None, :]      # float mask is ADDED
+        a = torch.softmax(logits, dim=-1) @ v
     a = a.transpose(1, 2).reshape(B, T, C)
     x = x + F.linear(a, w[p + ".attn1.to_out.0.weight"], w[p + ".attn1.to_out.0.bias"])
     h = F.layer_norm(x, (C,), w[p + ".norm3.weight"], w[p + ".norm3.bias"], eps=1e-5)
@@ -215,8 +224,8 @@ def solve_euler(w, x, t_span, mu, mask):
     """solve_ode_euler (flow_matching.py:67-104); time arithmetic stays in t_span's dtype."""
     ts, dts = euler_time_grid(t_span)
     for t, dt in zip(ts, dts):
-        v = decoder_forward(w, x, mask, mu, t.to(x.dtype))
-        x = x + dt.to(x.dtype) * v
+        v = decoder_forward(w, x, mask, mu, t.to(device=x.device, dtype=x.dtype))
+        x = x + dt.to(device=x.device, dtype=x.dtype) * v
     return x
 
 

@@ -76,6 +76,35 @@ def ref_compute_batch_alignments(paths, values, t_xs, t_ys, max_neg_val=-1e9):
     _ref_core.compute_batch_alignments(paths, values, t_xs, t_ys, max_neg_val)
 
 
+def set_omp_threads(n):
+    """Sets the OpenMP team size the compiled core.pyx (prange, core.pyx:121) and the C restatement will use, on the
+    libgomp the process has loaded, and returns the value now in force.  Needed because launchers such as
+    torch.distributed.run export OMP_NUM_THREADS=1 to every rank."""
+    os.environ["OMP_NUM_THREADS"] = str(int(n))
+    try:
+        gomp = ctypes.CDLL("libgomp.so.1")
+        gomp.omp_set_num_threads(int(n))
+        return int(gomp.omp_get_max_threads())
+    except OSError:
+        return int(n)
+
+
+def maximum_path_ref_torch(value, mask):
+    """The reference WRAPPER on torch tensors, restated line by line from
+    /root/reference/matcha/utils/monotonic_align/__init__.py:40-55 (value*mask, .cpu().numpy() copies, np.zeros paths,
+    the two mask reductions, the compiled core, torch.from_numpy back to the caller's device and dtype)."""
+    import torch
+    value = value * mask                                                        # :45
+    device, dtype = value.device, value.dtype                                   # :46-47
+    value = value.data.cpu().numpy().astype(np.float32)                         # :48
+    path = np.zeros_like(value).astype(np.int32)                                # :49
+    mask = mask.data.cpu().numpy()                                              # :50
+    t_x_max = mask.sum(1)[:, 0].astype(np.int32)                                # :52
+    t_y_max = mask.sum(2)[:, 0].astype(np.int32)                                # :53
+    ref_compute_batch_alignments(path, value, t_x_max, t_y_max)                 # :54
+    return torch.from_numpy(path).to(device=device, dtype=dtype)                # :55
+
+
 def _lengths_from_mask(mask):
     # __init__.py:52-53
     t_x = mask.sum(1)[:, 0].astype(np.int32)

@@ -121,7 +121,9 @@ def test_state_dict_ingest_rejects_wrong_shapes(weights):
 # BASELINE.json north_star: relative L2 <= 2e-3 against the fp32 reference for the tensor-core mode.
 # "fp16" (IEEE half operands, fp32 accumulate/residual/statistics) meets it; plain "bf16" operands
 # measure 5e-3..9e-3 (8 mantissa bits per operand, ~1.6e-3 per GEMM, ~50 GEMMs deep) and are held
-# to a functional bound only -- see DESIGN.md §Decoder precision.
+# to a FUNCTIONAL bound only (1.5e-2: catches a broken kernel, not the north_star bar) -- see DESIGN.md §Decoder
+# precision; the 2e-3 assertion for bf16 lives in tests/test_decoder_t800_gpu.py as xfail(strict=True), so the suite
+# says so the day a bf16 path meets it.
 TOL_16 = {"fp16": 2e-3, "bf16": 1.5e-2}
 
 

@@ -75,3 +75,40 @@ def test_euler_time_grid_is_the_reference_loop():
         t = t + dt
         if k < 9:
             dt = t_span[k + 2] - t
+
+
+def test_sdpa_form_equals_explicit_softmax(weights):
+    """oracle.decoder.USE_SDPA (the form diffusers' AttnProcessor2_0 calls, used by bench.py's same-box GPU baseline)
+    is the same arithmetic as the explicit softmax the golden fixtures pin."""
+    g = torch.Generator().manual_seed(3)
+    x, mu = torch.randn(2, 80, 40, generator=g), torch.randn(2, 80, 40, generator=g)
+    mask = torch.ones(2, 1, 40); mask[1, :, 29:] = 0
+    t = torch.tensor(0.3)
+    a = odec.decoder_forward(weights, x, mask, mu, t)
+    odec.USE_SDPA = True
+    try:
+        b = odec.decoder_forward(weights, x, mask, mu, t)
+    finally:
+        odec.USE_SDPA = False
+    assert rel_l2(b, a) < 2e-6
+
+
+def test_t800_golden_matches_reference():
+    """The benchmarked configuration's size (T_mel = 800, 10 Euler steps): the restatement against the output of the
+    reference's own modules (tests/golden/decoder_golden_T800.npz, make_decoder_golden.py --t800)."""
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "decoder_golden_T800.npz"))
+    w = odec.make_weights(int(gold["weight_seed"][0]), "rich")
+    z, mu, mask, t_span = t800_inputs(gold)
+    torch.set_num_threads(os.cpu_count() or 4)
+    out = odec.solve_euler(w, z, t_span, mu, mask)
+    assert rel_l2(out, torch.from_numpy(gold["out"])) < 2e-6
+
+
+def t800_inputs(gold):
+    g = torch.Generator().manual_seed(int(gold["seed"][0]))
+    B, T = len(gold["lengths"]), 800
+    mu, z = torch.randn(B, 80, T, generator=g), torch.randn(B, 80, T, generator=g)
+    mask = torch.zeros(B, 1, T)
+    for i, n in enumerate(gold["lengths"]):
+        mask[i, :, : int(n)] = 1
+    return z, mu, mask, torch.linspace(0, 1, int(gold["n_timesteps"][0]) + 1)
