@@ -8,8 +8,8 @@ hot path (configs[3]) and batched synthesis (configs[4]) ride along as extra key
 
 A "step" is one monotonic-alignment pass over one batch of B utterances (per GPU; weak scaling: every rank
 owns its own batch slice).  At N > 1 the step also all-gathers the alignment over NCCL in its compact form
-(the kernel's per-token durations), overlapped with the next step's kernel; the dense forms of the gather are
-timed beside it under "mas_gather".  `value` is timed with inputs resident in HBM (C ABI, device pointers);
+(the kernel's per-token durations) right behind the kernel; the dense forms of the gather are timed beside it
+under "mas_gather".  `value` is timed with inputs resident in HBM (C ABI, device pointers);
 `e2e` goes through the host-buffer entry that mirrors core.pyx's compute_batch_alignments(paths, values,
 t_xs, t_ys) with pinned numpy buffers, H2D and D2H inside the timed region.  Prints ONE JSON line on rank 0.
 """
@@ -812,27 +812,21 @@ def run_ours(a):
     lib = load_library()
     if world > 1:
         # N > 1: the kernel also emits the per-token durations (matcha_b200_mas_align) and every step all-gathers them over
-        # NCCL on a side stream, overlapping the next step's kernel (double-buffered); the gathers are inside the timed region
-        dur = [torch.empty(B, T_x, dtype=torch.int32, device=dev) for _ in range(2)]
-        dur_all = [torch.empty(world * B, T_x, dtype=torch.int32, device=dev) for _ in range(2)]
-        comm = torch.cuda.Stream(device=dev)
+        # NCCL right behind the kernel, on the same stream and inside the timed region.  (Measured at N = 2: the gather adds
+        # ~10 us to a step; putting it on a side stream to overlap the next kernel was slower -- the persistent MAS kernel
+        # fills every SM, so the NCCL kernel only gets in at a kernel boundary anyway, and the stream hand-offs cost more.)
+        dur = torch.empty(B, T_x, dtype=torch.int32, device=dev)
+        dur_all = torch.empty(world * B, T_x, dtype=torch.int32, device=dev)
         stream_ptr = lambda: ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        counter = [0]
 
         def step():
-            k = counter[0] & 1
-            counter[0] += 1
-            main = torch.cuda.current_stream(dev)
-            main.wait_stream(comm) if counter[0] > 2 else None       # buffer k's previous gather has finished
-            rc = lib.matcha_b200_mas_align(path.data_ptr(), 1, dur[k].data_ptr(), value.data_ptr(), None, t_x.data_ptr(), t_y.data_ptr(),
+            rc = lib.matcha_b200_mas_align(path.data_ptr(), 1, dur.data_ptr(), value.data_ptr(), None, t_x.data_ptr(), t_y.data_ptr(),
                                            B, T_x, T_y, ctypes.c_float(-1e9), None, stream_ptr())
             assert rc == 0, rc
-            comm.wait_stream(main)
-            with torch.cuda.stream(comm):
-                dist.all_gather_into_tensor(dur_all[k], dur[k])
+            dist.all_gather_into_tensor(dur_all, dur)
 
         def finish():
-            torch.cuda.current_stream(dev).wait_stream(comm)
+            pass
     else:
         def step():
             ma.maximum_path_from_lengths(value, t_x, t_y, out=path)
@@ -946,8 +940,8 @@ def run_ours(a):
                        "l2": "inputs+outputs 6.5 GB per step >> 126 MB L2, no flush needed",
                        "launch": {"grid": out[0], "block": out[1], "smem": out[2], "rows_per_lane": out[3],
                                   "stages": out[4], "tma": out[5], "ctas_per_sm": out[6]},
-                       "parallelism": (f"batch-sharded x{world}; every step all-gathers the alignment (compact: int32 durations) over NCCL, "
-                                       f"overlapped with the next step's kernel, inside the timed region") if world > 1 else "single GPU, no collective"},
+                       "parallelism": (f"batch-sharded x{world}; every step all-gathers the alignment (compact: int32 durations) over NCCL "
+                                       f"right behind the kernel, inside the timed region") if world > 1 else "single GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                          "kernel_ms": k_ms, "kernel": "mas_kernel<R,HAS_MASK=false>"},
