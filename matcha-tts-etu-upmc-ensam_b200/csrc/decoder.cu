@@ -324,8 +324,10 @@ static int gemm_set_attributes() {
     MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
     MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
     MB200_CUDA_TRY(cudaFuncSetAttribute(gemm_abuild_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmemBytes));
-    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
-    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(ffn_fused_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
     return MB200_OK;
 }
 
@@ -440,23 +442,38 @@ static bool ffn_use_fused() {
     if (v < 0) { const char *e = getenv("MB200_FFN"); v = (e && e[0] == 's') ? 0 : 1; }
     return v != 0;
 }
+// With wo / bo (the OUTPROJ variant): a = the 16-bit attention rows, res = the block's input stream x1; the kernel computes
+// x2 = a Wo^T + bo + res, norm3 and the feed-forward, out = x2 + FFN(norm3(x2)).  MB200_OUTPROJ=0 keeps the separate GEMM.
+static bool outproj_fused() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("MB200_OUTPROJ"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v != 0;
+}
 static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1, const bf16 *w2, const float *b2,
                   const float *res, float *out_f32, bf16 *out_b16, bool omask, const float *ln_in = nullptr,
-                  const float *ln_g = nullptr, const float *ln_b = nullptr) {
+                  const float *ln_g = nullptr, const float *ln_b = nullptr, const bf16 *wo = nullptr, const float *bo = nullptr) {
     if (c.err) return;
-    CUtensorMap ma, m1, m2;
+    CUtensorMap ma, m1, m2, mo;
     if (!tmap_for(c, a, 3, (uint64_t)kC, (uint64_t)T, (uint64_t)c.B, 64, kFfM, &ma)) return;
     if (!tmap_for(c, w1, 2, (uint64_t)kC, (uint64_t)kFfHid, 1, 64, kFfChunk, &m1)) return;
     if (!tmap_for(c, w2, 2, (uint64_t)kFfHid, (uint64_t)kC, 1, 64, kC, &m2)) return;
+    mo = m2;
+    if (wo && !tmap_for(c, wo, 2, (uint64_t)kC, (uint64_t)kC, 1, 64, kC, &mo)) return;
     FfnArgs g;
     g.B = c.B; g.T = T; g.tiles_per_sample = (T + kFfM - 1) / kFfM;
     g.b1 = b1; g.b2 = b2; g.res = res; g.out_f32 = out_f32; g.out_b16 = out_b16;
     g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.debug = c.debug;
-    g.ln_in = ln_in; g.ln_g = ln_g; g.ln_b = ln_b;
+    g.ln_in = ln_in; g.ln_g = ln_g; g.ln_b = ln_b; g.bo = bo;
     if ((long long)c.B * T * kC >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
     const int grid = c.B * g.tiles_per_sample;
-    if (c.f16) launch(c, ffn_fused_kernel<true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, g);
-    else launch(c, ffn_fused_kernel<false>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, g);
+    if (wo) {
+        if (!bo || !ln_g || !ln_b || !res) { c.err = MB200_ERR_INVALID_ARG; return; }
+        if (c.f16) launch(c, ffn_fused_kernel<true, true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, mo, g);
+        else launch(c, ffn_fused_kernel<false, true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, mo, g);
+        return;
+    }
+    if (c.f16) launch(c, ffn_fused_kernel<true, false>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, mo, g);
+    else launch(c, ffn_fused_kernel<false, false>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, mo, g);
 }
 
 static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb, const bf16 *in0, int c0, const bf16 *in1,
@@ -490,6 +507,10 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
         gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
     }
     attention_b(c, qkvb, w.attb, T);
+    if (ffn_use_fused() && outproj_fused()) {      // to_out[0] + residual + norm3 + feed-forward + residual in one kernel
+        ffn_b(c, w.attb, T, sb.w1, s.b1, sb.w2, s.b2, w.x1, out_f32, out_b16, true, nullptr, s.ln3g, s.ln3b, sb.wo, s.bo);
+        return;
+    }
     gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
     if (ffn_use_fused()) {      // norm3 is applied while the kernel builds its A operand
         ffn_b(c, w.lnb, T, sb.w1, s.b1, sb.w2, s.b2, w.x2, out_f32, out_b16, true, w.x2, s.ln3g, s.ln3b);
@@ -852,6 +873,23 @@ extern "C" int matcha_b200_debug_abuild(int mode, const float *h, const double *
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16;
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     abuild_b(c, mode, h, gsum, gamma, beta, T, tb, 0, r, ln_g, ln_b, x1, (const bf16 *)w16, N, bias, (bf16 *)out16, out_f32, gstats);
+    if (c.err) return c.err;
+    MB200_CUDA_TRY(cudaGetLastError());
+    return MB200_OK;
+}
+
+// test aid, not part of the public header: the transformer block's tail in one kernel (ffn_fused.cuh, OUTPROJ variant):
+// out = x2 + FFN(LayerNorm(x2)), x2 = att16 Wo^T + bo + x1
+extern "C" int matcha_b200_debug_ffn_outproj(const void *att16, const void *wo_16, const float *bo, const float *x1,
+                                              const float *ln_g, const float *ln_b, const void *w1_16, const float *b1,
+                                              const void *w2_16, const float *b2, float *out_f32, void *out_16,
+                                              const float *mask, int B, int T, int f16, void *stream) {
+    if (!att16 || !wo_16 || !bo || !x1 || !ln_g || !ln_b || !w1_16 || !w2_16 || !b1 || !b2 || B < 1 || T < 1) return MB200_ERR_INVALID_ARG;
+    Ctx c;
+    c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16; c.debug = 1;
+    { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
+    ffn_b(c, (const bf16 *)att16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, x1, out_f32, (bf16 *)out_16, mask != nullptr,
+          nullptr, ln_g, ln_b, (const bf16 *)wo_16, bo);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;

@@ -13,6 +13,19 @@
 //     as two boxes, or 256 output rows x 64 hidden of W2).
 //   * Final epilogue: acc2 + b2 + residual -> fp32 rows and/or 16-bit rows * mask (the next conv's operand).
 // TMEM: acc2 256 + acc1 2 x 128 = 512 columns.  Shared: A 64 KB + H 2 x 32 KB + ring 96 KB = 224 KB.
+//
+// OUTPROJ variant (round 2): the attention out-projection and norm3 ride in the same kernel, so the whole tail of the
+// transformer block (transformer.py:320-368: to_out[0], the residual add, norm3, FeedForward, the second residual add) is
+// ONE launch and the intermediate stream x2 never reaches memory:
+//   acc2 = att . Wo^T                       (the 16-bit attention rows arrive by TMA in the A region; Wo streams through
+//                                            the weight ring ahead of W1)
+//   x2   = acc2 + bo + x1                   (epilogue warps, thread = row; written BACK into acc2 with tcgen05.st)
+//   A    = LayerNorm(x2) * g + b            (row statistics from per-thread 32-column partials merged with Chan's
+//                                            formula across the four warps of a lane quarter; 16-bit into the A region,
+//                                            which GEMM0 has finished reading)
+//   acc2 += gelu(A W1^T + b1) W2^T          (FFN2 accumulates ON TOP of x2: the second residual add is free)
+//   out  = acc2 + b2
+// It removes one launch, one 128x256 fp32 round trip and one CTA life cycle per block from the solve's dependent chain.
 #pragma once
 #include "gemm_bf16.cuh"
 
@@ -30,6 +43,7 @@ constexpr int kFfEpiPitch = 36;                               // floats, final-e
 
 struct FfnArgs {
     int B, T, tiles_per_sample;
+    const float *bo;                   // OUTPROJ: to_out[0] bias [256]; res is then the block's input stream x1
     const float *b1, *b2;              // [1024], [256]
     const float *res;                  // fp32 [B][T][256]
     float *out_f32;                    // fp32 [B][T][256] or nullptr
@@ -63,10 +77,10 @@ constexpr uint32_t kFfIdesc1Bf16 = kFfIdesc1F16 | (1u << 7) | (1u << 10);
 // epilogue; [8 + 5c ..] chunk c in epilogue warp 0: acc1 ready, TMEM read, GELU done, H free, H written
 __device__ long long g_ffn_dbg[64];
 
-template <bool F16>
+template <bool F16, bool OUTPROJ>
 __global__ void __launch_bounds__(kFfThreads, 1)
 ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW1,
-                 const __grid_constant__ CUtensorMap tmW2, const FfnArgs g) {
+                 const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmWo, const FfnArgs g) {
     extern __shared__ uint8_t ffsm_raw[];
     const uint32_t base = (smem_u32(ffsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = ffsm_raw + (base - smem_u32(ffsm_raw));
@@ -79,14 +93,17 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t bar_hf = bar_a1e + 16;                     // [2] H chunk written
     const uint32_t bar_he = bar_hf + 16;                      // [2] H chunk consumed by FFN2
     const uint32_t bar_a2f = bar_he + 16;                     // acc2 complete
-    const uint32_t tmem_slot = bar_a2f + 8;
+    const uint32_t bar_att = bar_a2f + 8;                     // OUTPROJ: attention rows landed
+    const uint32_t bar_g0 = bar_att + 8;                      // OUTPROJ: att . Wo^T complete
+    const uint32_t tmem_slot = bar_g0 + 8;
     volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_slot - base));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x - b * g.tiles_per_sample) * kFfM;
 
     if (threadIdx.x == 0) {
-        mbar_init(bar_a, g.ln_in ? (uint32_t)kFfEpiWarps : 1u); mbar_init(bar_a2f, 1u);
+        mbar_init(bar_a, (OUTPROJ || g.ln_in) ? (uint32_t)kFfEpiWarps : 1u); mbar_init(bar_a2f, 1u);
+        mbar_init(bar_att, 1u); mbar_init(bar_g0, 1u);
         for (int s = 0; s < kFfStages; ++s) { mbar_init(bar_full + 8u * s, 1u); mbar_init(bar_empty + 8u * s, 1u); }
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_a1f + 8u * a, 1u); mbar_init(bar_a1e + 8u * a, kFfEpiWarps);
@@ -94,6 +111,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         mbar_fence_init();
         tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
+        if (OUTPROJ) tma_prefetch_desc(&tmWo);
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512) : "memory");
@@ -128,12 +146,28 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tma_load_2d(base + kFfOffRing + s * kFfStageBytes, &tmW2, bar_full + 8u * s, c * kFfChunk + kb * 64, 0);
                 ++it;
             };
+            auto stage_wo = [&](int kb) {                      // Wo all 256 rows, k in [64 kb, +64): same stage shape as W2
+                const uint32_t s = it % kFfStages;
+                mbar_wait_parked(bar_empty + 8u * s, ((it / kFfStages) & 1) ^ 1, 500);
+                mbar_arrive_expect_tx(bar_full + 8u * s, kFfStageBytes);
+                tma_load_2d(base + kFfOffRing + s * kFfStageBytes, &tmWo, bar_full + 8u * s, kb * 64, 0);
+                ++it;
+            };
             // the weights do not depend on the predecessor kernel: the first stages are in flight before the wait
-            stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
-            pdl_wait();
-            if (!g.ln_in) {
-                mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
-                for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
+            if (OUTPROJ) {
+                stage_wo(0); stage_wo(1); stage_wo(2);
+                pdl_wait();
+                mbar_arrive_expect_tx(bar_att, 4 * kFfKb);
+                for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_att, kb * 64, t0, b);
+                stage_wo(3);
+                stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
+            } else {
+                stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
+                pdl_wait();
+                if (!g.ln_in) {
+                    mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
+                    for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
+                }
             }
             stage_w1(1, 1);
             for (int s = 2; s < kFfNChunks; ++s) {            // same order as the MMA warp: FFN1 runs two chunks ahead of FFN2
@@ -180,11 +214,27 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const uint64_t db = umma_desc_sw128(base + kFfOffRing + s * kFfStageBytes);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16(tmem_acc2, da + 2u * k, db + 2u * k, idesc2, (c | kb | k) != 0 ? 1u : 0u);
+                        umma_bf16(tmem_acc2, da + 2u * k, db + 2u * k, idesc2, (OUTPROJ || (c | kb | k) != 0) ? 1u : 0u);
                     umma_commit(bar_empty + 8u * s);
                 }
                 umma_commit(bar_he + 8u * buf);
             };
+            if (OUTPROJ) {
+                // GEMM0: acc2 = att . Wo^T (K = 256: four K-blocks of the A region against four ring stages)
+                mbar_wait_parked(bar_att, 0, 500);
+                for (int kb = 0; kb < 4; ++kb, ++it) {
+                    const uint32_t s = it % kFfStages;
+                    mbar_wait_parked(bar_full + 8u * s, (it / kFfStages) & 1, 200);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint64_t da = umma_desc_sw128(base + kFfOffA + kb * kFfKb);
+                    const uint64_t db = umma_desc_sw128(base + kFfOffRing + s * kFfStageBytes);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16(tmem_acc2, da + 2u * k, db + 2u * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit(bar_empty + 8u * s);
+                }
+                umma_commit(bar_g0);
+            }
             mbar_wait_parked(bar_a, 0, 500);
             // FFN1 runs two chunks ahead of FFN2: the GELU of chunk c has FFN2(c-2), FFN1(c+1), FFN2(c-1) and FFN1(c+2)
             // (4 x 1024 tensor-pipe cycles) to finish before FFN2(c) needs H(c), so the epilogue warps are bound by their
@@ -201,7 +251,93 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int cg = ew >> 2;                              // column group
         const int row = 32 * q + lane;                       // tile row = TMEM lane
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
-        if (g.ln_in) {
+        if (OUTPROJ) {
+            // ---- x2 = att Wo^T + bo + x1 (back into acc2), then A = LayerNorm(x2): thread = row, columns [64 cg, +64)
+            pdl_wait();
+            const bool ok = t0 + row < g.T;
+            const float *x1p = g.res + ((size_t)b * g.T + (ok ? t0 + row : 0)) * kC + cg * 64;
+            float4 rv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rv[i] = ok ? *reinterpret_cast<const float4 *>(x1p + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (dbg && threadIdx.x == 64) g_ffn_dbg[4] = clock64();
+            mbar_wait_parked(bar_g0, 0, 200);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (dbg && threadIdx.x == 64) g_ffn_dbg[5] = clock64();
+            float pm[2], pq[2];                              // per 32-column half: mean and centred sum of squares
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                uint32_t v[32];
+                tmem_ld32(tmem_acc2 + cg * 64 + hh * 32 + lane_off, v);
+                const float4 *bo4 = reinterpret_cast<const float4 *>(g.bo + cg * 64 + hh * 32);
+                float sum = 0.f;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 bb = __ldg(bo4 + i);
+                    const float x0 = __uint_as_float(v[4 * i]) + bb.x + rv[i].x, x1 = __uint_as_float(v[4 * i + 1]) + bb.y + rv[i].y;
+                    const float x2 = __uint_as_float(v[4 * i + 2]) + bb.z + rv[i].z, x3 = __uint_as_float(v[4 * i + 3]) + bb.w + rv[i].w;
+                    v[4 * i] = __float_as_uint(x0); v[4 * i + 1] = __float_as_uint(x1); v[4 * i + 2] = __float_as_uint(x2); v[4 * i + 3] = __float_as_uint(x3);
+                    sum += (x0 + x1) + (x2 + x3);
+                }
+                if (hh == 0) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) rv[i] = ok ? *reinterpret_cast<const float4 *>(x1p + 32 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                tmem_st32(tmem_acc2 + cg * 64 + hh * 32 + lane_off, v);
+                const float m = sum * (1.0f / 32.0f);
+                float qq = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) { const float d = __uint_as_float(v[i]) - m; qq = fmaf(d, d, qq); }
+                pm[hh] = m; pq[hh] = qq;
+            }
+            // merge the eight 32-column partials of a row (two here, six in the other three warps of the lane quarter):
+            // equal counts, so mean = average of the means and M2 = sum M2_i + 32 sum (mean_i - mean)^2  (Chan et al.)
+            float4 *red = reinterpret_cast<float4 *>(gbase + kFfOffH);          // [128 rows][4 column groups], H is idle
+            if (dbg && threadIdx.x == 64) g_ffn_dbg[6] = clock64();
+            red[row * 4 + cg] = make_float4(pm[0], pq[0], pm[1], pq[1]);
+            if (q == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+            else if (q == 1) asm volatile("bar.sync 2, 128;" ::: "memory");
+            else if (q == 2) asm volatile("bar.sync 3, 128;" ::: "memory");
+            else asm volatile("bar.sync 4, 128;" ::: "memory");
+            float mean = 0.f, m2 = 0.f;
+            float4 pr[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { pr[i] = red[row * 4 + i]; mean += pr[i].x + pr[i].z; m2 += pr[i].y + pr[i].w; }
+            mean *= 0.125f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float d0 = pr[i].x - mean, d1 = pr[i].z - mean; m2 = fmaf(32.0f * d0, d0, m2); m2 = fmaf(32.0f * d1, d1, m2); }
+            const float rstd = rsqrtf(m2 * (1.0f / kC) + 1e-5f);
+            // the x2 rows written above must be visible to this thread's own re-read
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            if (dbg && threadIdx.x == 64) g_ffn_dbg[7] = clock64();
+            const uint32_t arow = base + kFfOffA + (uint32_t)cg * kFfKb + (uint32_t)((row >> 3) * 1024 + (row & 7) * 128);
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                uint32_t v[32];
+                tmem_ld32(tmem_acc2 + cg * 64 + hh * 32 + lane_off, v);
+                const float4 *g4 = reinterpret_cast<const float4 *>(g.ln_g + cg * 64 + hh * 32);
+                const float4 *b4 = reinterpret_cast<const float4 *>(g.ln_b + cg * 64 + hh * 32);
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 gg = __ldg(g4 + i), bb = __ldg(b4 + i);
+                    const float y0 = fmaf((__uint_as_float(v[4 * i]) - mean) * rstd, gg.x, bb.x), y1 = fmaf((__uint_as_float(v[4 * i + 1]) - mean) * rstd, gg.y, bb.y);
+                    const float y2 = fmaf((__uint_as_float(v[4 * i + 2]) - mean) * rstd, gg.z, bb.z), y3 = fmaf((__uint_as_float(v[4 * i + 3]) - mean) * rstd, gg.w, bb.w);
+                    pk[2 * i] = ok ? pack16x2(y0, y1, F16) : 0u;
+                    pk[2 * i + 1] = ok ? pack16x2(y2, y3, F16) : 0u;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t piece = (uint32_t)(hh * 4 + i);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(arow + ((piece ^ (uint32_t)(row & 7)) << 4)),
+                                 "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3]) : "memory");
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_a);
+            if (dbg && threadIdx.x == 64) g_ffn_dbg[1] = clock64();
+        } else if (g.ln_in) {
             // ---- A = LayerNorm(256, eps 1e-5) of the tile's rows, one warp per row (8 rows per warp, 4 in flight),
             //      written 16-bit into the four 128B-swizzled K-blocks the UMMA descriptors expect
             pdl_wait();
@@ -316,7 +452,11 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int i = 0; i < 8; ++i)
                 rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
         };
-        load_res(0);                                          // in flight while the last FFN2 chunks complete
+        if (!OUTPROJ) load_res(0);                            // in flight while the last FFN2 chunks complete
+        else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rv[i] = make_float4(0.f, 0.f, 0.f, 0.f);   // the residual already sits in acc2
+        }
         mbar_wait_parked(bar_a2f, 0, 200);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         if (dbg && threadIdx.x == 64) g_ffn_dbg[2] = clock64();
@@ -336,7 +476,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int i = 0; i < 8; ++i) {
                 float4 x = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kFfEpiPitch + c4);
                 x.x += bias.x + rv[i].x; x.y += bias.y + rv[i].y; x.z += bias.z + rv[i].z; x.w += bias.w + rv[i].w;
-                if (jj == 0 && i == 7) load_res(1);
+                if (!OUTPROJ && jj == 0 && i == 7) load_res(1);
                 if (orow[i] >= 0) {
                     if (g.out_f32) *reinterpret_cast<float4 *>(g.out_f32 + orow[i] + n) = x;
                     if (g.out_b16)

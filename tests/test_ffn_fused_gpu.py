@@ -88,3 +88,53 @@ def test_ffn_with_layernorm_folded_in(B, T):
     want, want_term = reference(a.half(), w1, b1, w2, b2, x)
     assert rel(out - x, want_term) < 8e-4
     assert rel(out, want) < 6e-4
+
+
+# ------------------------------------------------------------------ OUTPROJ variant: the whole tail of the transformer block
+def run_outproj(att, wo, bo, x1, ln_g, ln_b, w1, b1, w2, b2, mask, f16):
+    from matcha_b200._lib import check, load_library
+    lib = load_library()
+    B, T, _ = att.shape
+    out = torch.full((B, T, 256), float("nan"), device="cuda")
+    out16 = torch.zeros((B, T, 256), device="cuda", dtype=att.dtype)
+    p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    lib.matcha_b200_debug_ffn_outproj.restype = ctypes.c_int
+    check(lib.matcha_b200_debug_ffn_outproj(p(att), p(wo), p(bo), p(x1), p(ln_g), p(ln_b), p(w1), p(b1), p(w2), p(b2), p(out), p(out16),
+                                            p(mask), B, T, int(f16), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+          "debug_ffn_outproj")
+    torch.cuda.synchronize()
+    return out, out16
+
+
+@pytest.mark.parametrize("B,T,f16", [(2, 200, True), (1, 128, True), (3, 130, True), (2, 5, True), (4, 400, True), (8, 800, True),
+                                     (2, 200, False), (1, 333, False)])
+def test_outproj_norm3_ffn_matches_torch(B, T, f16):
+    """transformer.py:320-368 after the attention core: x2 = x1 + to_out[0](att); out = x2 + FF(norm3(x2)), against
+    plain torch fp32 on the same 16-bit-rounded att / weights.  The row means are offset on purpose (LayerNorm's
+    cancellation case)."""
+    dt = torch.float16 if f16 else torch.bfloat16
+    g = torch.Generator(device="cuda").manual_seed(B * 13 + T)
+    att = torch.randn(B, T, 256, device="cuda", generator=g).to(dt)
+    wo = (torch.randn(256, 256, device="cuda", generator=g) * 0.09).to(dt)
+    bo = torch.randn(256, device="cuda", generator=g) * 0.3
+    x1 = torch.randn(B, T, 256, device="cuda", generator=g) * 2.0 + 3.0 * torch.randn(B, T, 1, device="cuda", generator=g)
+    ln_g = 1.0 + 0.1 * torch.randn(256, device="cuda", generator=g)
+    ln_b = 0.1 * torch.randn(256, device="cuda", generator=g)
+    w1 = (torch.randn(1024, 256, device="cuda", generator=g) * 0.09).to(dt)
+    w2 = (torch.randn(256, 1024, device="cuda", generator=g) * 0.044).to(dt)
+    b1 = torch.randn(1024, device="cuda", generator=g) * 0.5
+    b2 = torch.randn(256, device="cuda", generator=g)
+    mask = torch.ones(B, T, device="cuda")
+    mask[B - 1, (2 * T) // 3:] = 0
+    out, out16 = run_outproj(att, wo, bo, x1, ln_g, ln_b, w1, b1, w2, b2, mask, f16)
+    x2 = x1 + att.float() @ wo.float().t() + bo
+    a = torch.nn.functional.layer_norm(x2, (256,), ln_g, ln_b, eps=1e-5)
+    a16 = a.to(dt).float()                                    # the kernel rounds norm3's output to the operand format
+    h = torch.nn.functional.gelu(a16 @ w1.float().t() + b1)
+    want = x2 + h @ w2.float().t() + b2
+    assert torch.isfinite(out).all()
+    tol = 6e-4 if f16 else 4e-3
+    assert rel(out, want) < tol
+    assert rel(out - x2, want - x2) < (2e-3 if f16 else 1.5e-2)       # the feed-forward term alone
+    assert rel(out16.float(), want * mask[:, :, None]) < (1e-3 if f16 else 6e-3)
+    assert out16[B - 1, (2 * T) // 3:].abs().sum() == 0
