@@ -152,7 +152,7 @@ static void gemm(Ctx &c, const float *a0, int c0, int Ta0, const float *a1, int 
     for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
     g.stride = stride; g.B = c.B; g.Tin = Tin; g.Tout = Tout;
     g.w = w; g.bias = bias; g.N = N; g.K = ntaps * (c0 + c1); g.act = act; g.res = res; g.out = out;
-    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off; g.out_bf16 = nullptr; g.omask = nullptr; g.f16 = 0;
+    g.out_T = out_T; g.out_stride = out_stride; g.out_off = out_off; g.out_bf16 = nullptr; g.omask = nullptr; g.o16_scale = 1.0f; g.f16 = 0;
     const int M = c.B * Tout;
     dim3 grid((M + kBM - 1) / kBM, N / kBN);
     launch(c, gemm_f32_kernel, grid, 256, 0, g);
@@ -333,7 +333,18 @@ static int gemm_set_attributes() {
 
 // out = act(A W^T + bias) + res on the tensor cores.  a0/a1: bf16 [B][T][c0|c1] (already x*mask where the
 // reference multiplies), w: bf16 [N][ntaps*(c0+c1)].
-static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
+//
+// fp16 range guard.  The residual-stream tensors (stage outputs, the inputs of the convs) are the only 16-bit operands whose size
+// the network does not bound itself (everything else sits behind a GroupNorm / LayerNorm / softmax); IEEE half tops out at
+// 65504.  In fp16 mode they are stored multiplied by kStreamDown = 2^-4 (exact, but for values below 1e-3 that turn subnormal)
+// and the GEMM that consumes them multiplies its fp32 accumulator by 2^4 before the bias (one FMA instead of one add), so the mode
+// holds |x| < 1.04e6 on the stream; beyond that the conversion saturates (pack16x2) instead of producing inf.  bf16 mode: scale 1.
+// sflags: kSA = the A rows are a stream tensor, kSO = the 16-bit output is one.
+constexpr int kSA = 1, kSO = 2;
+constexpr float kStreamDown = 1.0f / 16.0f, kStreamUp = 16.0f;
+static inline float stream_down(const Ctx &c) { return c.f16 ? kStreamDown : 1.0f; }
+static inline float stream_up(const Ctx &c) { return c.f16 ? kStreamUp : 1.0f; }
+static void gemm_b(Ctx &c, int sflags, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
                    const bf16 *w, int N, const float *bias, int act, const float *res, float *out_f32,
                    bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0, double *gstats = nullptr,
                    const float *bias2 = nullptr, float *out2_f32 = nullptr, int kb2_begin = 0, int kb2_count = 0) {
@@ -350,6 +361,7 @@ static void gemm_b(Ctx &c, const bf16 *a0, int c0, const bf16 *a1, int c1, int n
     g.c0_chunks = c0 / kGK; g.c1_chunks = c1 / kGK;
     g.bias = bias; g.act = act; g.res = res; g.out_f32 = out_f32; g.out_bf16 = out_b16;
     g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.N = N; g.f16 = c.f16;
+    g.acc_scale = (sflags & kSA) ? stream_up(c) : 1.0f; g.o16_scale = (sflags & kSO) ? stream_down(c) : 1.0f;
     g.out_T = out_T > 0 ? out_T : T; g.out_stride = out_T > 0 ? out_stride : 1; g.out_off = out_T > 0 ? out_off : 0;
     g.fin_n = 0; g.fin_xin = nullptr; g.fin_dt = 0.f; g.fin_out = nullptr;
     if (c.fin_out) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
@@ -451,7 +463,8 @@ static bool outproj_fused() {
 }
 static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1, const bf16 *w2, const float *b2,
                   const float *res, float *out_f32, bf16 *out_b16, bool omask, const float *ln_in = nullptr,
-                  const float *ln_g = nullptr, const float *ln_b = nullptr, const bf16 *wo = nullptr, const float *bo = nullptr) {
+                  const float *ln_g = nullptr, const float *ln_b = nullptr, const bf16 *wo = nullptr, const float *bo = nullptr,
+                  bool o_stream = true) {
     if (c.err) return;
     CUtensorMap ma, m1, m2, mo;
     if (!tmap_for(c, a, 3, (uint64_t)kC, (uint64_t)T, (uint64_t)c.B, 64, kFfM, &ma)) return;
@@ -462,7 +475,7 @@ static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1,
     FfnArgs g;
     g.B = c.B; g.T = T; g.tiles_per_sample = (T + kFfM - 1) / kFfM;
     g.b1 = b1; g.b2 = b2; g.res = res; g.out_f32 = out_f32; g.out_b16 = out_b16;
-    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.debug = c.debug;
+    g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.debug = c.debug; g.o16_scale = o_stream ? stream_down(c) : 1.0f;
     g.ln_in = ln_in; g.ln_g = ln_g; g.ln_b = ln_b; g.bo = bo;
     if ((long long)c.B * T * kC >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
     const int grid = c.B * g.tiles_per_sample;
@@ -488,7 +501,7 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
     double *gs1 = w.gstats + (size_t)(2 * stage) * c.B * kGroups * 2, *gs2 = gs1 + (size_t)c.B * kGroups * 2;
     // block1's conv and res_conv in one GEMM: h = conv(x*mask) (+ GroupNorm sums), g = res_conv(x*mask) (centre tap only)
     const int chunks = (c0 + c1) / kGK;
-    gemm_b(c, in0, c0, in1, c1, 3, taps3, T, sb.wc1, 2 * kC, s.bc1, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs1, s.br, w.g, chunks, chunks);
+    gemm_b(c, kSA, in0, c0, in1, c1, 3, taps3, T, sb.wc1, 2 * kC, s.bc1, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs1, s.br, w.g, chunks, chunks);
     const unsigned rb = (unsigned)((rows + kGmRowsPerBlock - 1) / kGmRowsPerBlock);
     bf16 *qkvb = reinterpret_cast<bf16 *>(w.qkv);      // 16-bit q|k|v rows in the fp32 qkv scratch
     if (abuild_enabled()) {
@@ -500,24 +513,24 @@ static void run_stage_bf16(Ctx &c, int stage, const StageW &s, const StageWb &sb
     } else {
         launch(c, gn_mish_rows_kernel<0>, rb, 256, 0, w.h, gs1, s.g1, s.be1, c.mask, c.T, tb, tb_per_sample, nullptr, nullptr, nullptr,
                nullptr, w.a1b, c.f16, c.B, T);
-        gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs2);
+        gemm_b(c, 0, w.a1b, kC, nullptr, 0, 3, taps3, T, sb.wc2, kC, s.bc2, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gs2);
         // x1 = Mish(GN(h)) * mask + res_conv, and norm1(x1) as the q|k|v operand, in one pass
         launch(c, gn_mish_rows_kernel<1>, rb, 256, 0, w.h, gs2, s.g2, s.be2, c.mask, c.T, nullptr, 0, w.g, s.ln1g, s.ln1b, w.x1, w.lnb,
                c.f16, c.B, T);
-        gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
+        gemm_b(c, 0, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.wqkv, 3 * kC, nullptr, 0, nullptr, nullptr, qkvb, false);
     }
     attention_b(c, qkvb, w.attb, T);
     if (ffn_use_fused() && outproj_fused()) {      // to_out[0] + residual + norm3 + feed-forward + residual in one kernel
         ffn_b(c, w.attb, T, sb.w1, s.b1, sb.w2, s.b2, w.x1, out_f32, out_b16, true, nullptr, s.ln3g, s.ln3b, sb.wo, s.bo);
         return;
     }
-    gemm_b(c, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
+    gemm_b(c, 0, w.attb, kC, nullptr, 0, 1, tap0, T, sb.wo, kC, s.bo, 0, w.x1, w.x2, nullptr, false);
     if (ffn_use_fused()) {      // norm3 is applied while the kernel builds its A operand
         ffn_b(c, w.lnb, T, sb.w1, s.b1, sb.w2, s.b2, w.x2, out_f32, out_b16, true, w.x2, s.ln3g, s.ln3b);
     } else {
         launch(c, layernorm_kernel, (unsigned)((rows + 7) / 8), 256, 0, w.x2, s.ln3g, s.ln3b, nullptr, w.lnb, c.f16, rows);
-        gemm_b(c, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
-        gemm_b(c, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
+        gemm_b(c, 0, w.lnb, kC, nullptr, 0, 1, tap0, T, sb.w1, 4 * kC, s.b1, 1, nullptr, nullptr, w.f1b, false);
+        gemm_b(c, kSO, w.f1b, 4 * kC, nullptr, 0, 1, tap0, T, sb.w2, kC, s.b2, 0, w.x2, out_f32, out_b16, true);
     }
 }
 
@@ -531,39 +544,39 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
     auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
     dim3 pgrid((T + 31) / 32, kInChPad / 32, c.B);
-    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, c.B, T, w.gstats, kGnConvs * c.B * kGroups * 2);
+    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, stream_down(c), c.B, T, w.gstats, kGnConvs * c.B * kGroups * 2);
     // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
     run_stage_bf16(c, 0, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, (T & 1) ? w.s0 : nullptr, w.s0b);
     if ((T & 1) == 0) {
         static const int taps_pair[2] = {-1, 0};
-        gemm_b(c, w.s0b, 2 * kC, nullptr, 0, 2, taps_pair, T2, Wb.st[0].wtail, kC, W.st[0].btail, 0, nullptr, nullptr, w.inb, true);
+        gemm_b(c, kSA | kSO, w.s0b, 2 * kC, nullptr, 0, 2, taps_pair, T2, Wb.st[0].wtail, kC, W.st[0].btail, 0, nullptr, nullptr, w.inb, true);
     } else {
         GemmArgs g;
         g.a0 = w.s0; g.a1 = nullptr; g.c0 = kC; g.c1 = 0; g.Ta0 = T; g.mask = c.mask; g.mask_T = c.T;
         g.ntaps = 3; g.tap_off[0] = -1; g.tap_off[1] = 0; g.tap_off[2] = 1; g.tap_off[3] = 0; g.stride = 2;
         g.B = c.B; g.Tin = T; g.Tout = T2; g.w = W.st[0].wtail; g.bias = W.st[0].btail; g.N = kC; g.K = 3 * kC;
         g.act = 0; g.res = nullptr; g.out = nullptr; g.out_T = T2; g.out_stride = 1; g.out_off = 0;
-        g.out_bf16 = w.inb; g.omask = c.mask; g.f16 = c.f16;
+        g.out_bf16 = w.inb; g.omask = c.mask; g.o16_scale = stream_down(c); g.f16 = c.f16;
         launch(c, gemm_f32_kernel, dim3((c.B * T2 + kBM - 1) / kBM, kC / kBN), 256, 0, g);
     }
     run_stage_bf16(c, 1, W.st[1], Wb.st[1], w.inb, kC, nullptr, 0, T2, tb(1), tb_per_sample, nullptr, w.s1b);
-    gemm_b(c, w.s1b, kC, nullptr, 0, 3, taps3, T2, Wb.st[1].wtail, kC, W.st[1].btail, 0, nullptr, nullptr, w.inb, true);
+    gemm_b(c, kSA | kSO, w.s1b, kC, nullptr, 0, 3, taps3, T2, Wb.st[1].wtail, kC, W.st[1].btail, 0, nullptr, nullptr, w.inb, true);
     run_stage_bf16(c, 2, W.st[2], Wb.st[2], w.inb, kC, nullptr, 0, T2, tb(2), tb_per_sample, nullptr, w.upb);
     run_stage_bf16(c, 3, W.st[3], Wb.st[3], w.upb, kC, nullptr, 0, T2, tb(3), tb_per_sample, nullptr, w.inb);
     run_stage_bf16(c, 4, W.st[4], Wb.st[4], w.inb, kC, w.s1b, kC, T2, tb(4), tb_per_sample, nullptr, w.upb);
     // ConvTranspose1d(4,2,1) (decoder.py:112) as two phase GEMMs on the fp32 kernel, then the nearest
     // resample (odd T) + x*mask into the bf16 operand of the last Resnet1D
-    gemm_b(c, w.upb, kC, nullptr, 0, 2, taps_even, T2, Wb.st[4].wtail, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 0);
-    gemm_b(c, w.upb, kC, nullptr, 0, 2, taps_odd, T2, Wb.st[4].wtail2, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 1);
+    gemm_b(c, kSA, w.upb, kC, nullptr, 0, 2, taps_even, T2, Wb.st[4].wtail, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 0);
+    gemm_b(c, kSA, w.upb, kC, nullptr, 0, 2, taps_odd, T2, Wb.st[4].wtail2, kC, W.st[4].btail, 0, nullptr, w.d, nullptr, false, Tu, 2, 1);
     {
         const long long n4 = (long long)c.B * T * (kC / 4);
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
-        launch(c, resample_mask_bf16_kernel, eb, 256, 0, w.d, Tu, c.mask, w.upb, c.f16, c.B, T);
+        launch(c, resample_mask_bf16_kernel, eb, 256, 0, w.d, Tu, c.mask, w.upb, c.f16, stream_down(c), c.B, T);
     }
     run_stage_bf16(c, 5, W.st[5], Wb.st[5], w.upb, kC, w.s0b, kC, T, tb(5), tb_per_sample, nullptr, w.inb);
-    gemm_b(c, w.inb, kC, nullptr, 0, 3, taps3, T, Wb.st[5].wtail, kC, W.st[5].btail, 0, nullptr, nullptr, w.a1b, true);
+    gemm_b(c, kSA | kSO, w.inb, kC, nullptr, 0, 3, taps3, T, Wb.st[5].wtail, kC, W.st[5].btail, 0, nullptr, nullptr, w.a1b, true);
     double *gsf = w.gstats + (size_t)12 * c.B * kGroups * 2;
-    gemm_b(c, w.a1b, kC, nullptr, 0, 3, taps3, T, Wb.wf, kC, W.bf, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gsf);
+    gemm_b(c, kSA, w.a1b, kC, nullptr, 0, 3, taps3, T, Wb.wf, kC, W.bf, 0, nullptr, w.h, nullptr, false, 0, 1, 0, gsf);
     {   // final_norm + Mish + x*mask into the 16-bit operand, then final_proj + mask + Euler update in the GEMM epilogue
         static const int tap0[1] = {0};
         const long long n4 = (long long)c.B * T * (kC / 4);
@@ -571,7 +584,7 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         launch(c, gn_mish_rows_kernel<0>, (unsigned)(((size_t)c.B * T + kGmRowsPerBlock - 1) / kGmRowsPerBlock), 256, 0, w.h, gsf, W.gf,
                W.bef, c.mask, c.T, nullptr, 0, nullptr, nullptr, nullptr, nullptr, w.a1b, c.f16, c.B, T);
         c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
-        gemm_b(c, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
+        gemm_b(c, 0, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
         c.fin_out = nullptr;
     }
 }
@@ -840,7 +853,7 @@ extern "C" int matcha_b200_debug_gemm_bf16(const void *a0, int c0, const void *a
     Ctx c;
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = 0; c.debug = 1;
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
-    gemm_b(c, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
+    gemm_b(c, 0, (const bf16 *)a0, c0, (const bf16 *)a1, c1, ntaps, taps, T, (const bf16 *)w, N, bias, act, res, out_f32,
            (bf16 *)out_bf16, mask != nullptr);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
@@ -857,7 +870,7 @@ extern "C" int matcha_b200_debug_ffn(const void *a16, const void *w1_16, const f
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16; c.debug = 1;
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     ffn_b(c, (const bf16 *)a16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, res, out_f32, (bf16 *)out_16, mask != nullptr,
-          ln_in, ln_g, ln_b);
+          ln_in, ln_g, ln_b, nullptr, nullptr, false);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
@@ -889,7 +902,7 @@ extern "C" int matcha_b200_debug_ffn_outproj(const void *att16, const void *wo_1
     c.st = (cudaStream_t)stream; c.mask = mask; c.B = B; c.T = T; c.launches = 0; c.err = 0; c.f16 = f16; c.debug = 1;
     { const int rc = gemm_set_attributes(); if (rc != MB200_OK) return rc; }
     ffn_b(c, (const bf16 *)att16, T, (const bf16 *)w1_16, b1, (const bf16 *)w2_16, b2, x1, out_f32, (bf16 *)out_16, mask != nullptr,
-          nullptr, ln_g, ln_b, (const bf16 *)wo_16, bo);
+          nullptr, ln_g, ln_b, (const bf16 *)wo_16, bo, false);
     if (c.err) return c.err;
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;

@@ -54,13 +54,15 @@ __device__ __forceinline__ float gelu_erf_fast_f(float x) {
     return fmaxf(x, 0.0f) - ax * (poly * t * ex);
 }
 // 16-bit GEMM operands: bf16 (f16 == 0) or IEEE fp16 (f16 == 1); both travel as __nv_bfloat16-typed storage
+// The fp16 conversions saturate (cvt.rn.satfinite: |x| > 65504 -> +-65504, never inf), so an out-of-range operand costs accuracy on
+// that element instead of poisoning every row it meets with NaN.
 __device__ __forceinline__ uint32_t pack16x2(float a, float b, int f16) {
-    if (f16) { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t *>(&h); }
+    if (f16) { uint32_t r; asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a)); return r; }   // first source -> high half
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t *>(&h);
 }
 __device__ __forceinline__ __nv_bfloat16 pack16(float a, int f16) {
-    if (f16) { __half h = __float2half_rn(a); return *reinterpret_cast<__nv_bfloat16 *>(&h); }
+    if (f16) { unsigned short r; asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(a)); return *reinterpret_cast<__nv_bfloat16 *>(&r); }
     return __float2bfloat16_rn(a);
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
@@ -170,8 +172,9 @@ struct GemmArgs {
     const float *res;             // same indexing as out, or nullptr
     float *out;                   // fp32 output or nullptr
     int out_T, out_stride, out_off;
-    __nv_bfloat16 *out_bf16;      // optional bf16 copy, multiplied by omask[b][out row] (pitch mask_T)
+    __nv_bfloat16 *out_bf16;      // optional bf16 copy, multiplied by omask[b][out row] (pitch mask_T) and by o16_scale
     const float *omask;
+    float o16_scale;
     int f16;
 };
 
@@ -275,7 +278,7 @@ gemm_f32_kernel(const GemmArgs g) {
         }
         if (g.out) *reinterpret_cast<float4 *>(g.out + o) = v;
         if (g.out_bf16) {
-            const float mk = g.omask ? g.omask[(size_t)b * g.mask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f;
+            const float mk = g.o16_scale * (g.omask ? g.omask[(size_t)b * g.mask_T + (size_t)t * g.out_stride + g.out_off] : 1.0f);
             *reinterpret_cast<uint2 *>(g.out_bf16 + o) = make_uint2(pack16x2(v.x * mk, v.y * mk, g.f16), pack16x2(v.z * mk, v.w * mk, g.f16));
         }
     }
@@ -659,7 +662,7 @@ constexpr int kInChPad = 192;      // 160 input channels padded to three 64-wide
 // X0b[b][t][0:80] = x*mask, [80:160] = mu*mask, [160:192] = 0   (decoder.py:288 + the x*mask of :65,85)
 __global__ void __launch_bounds__(256)
 pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
-                       __nv_bfloat16 *__restrict__ out, int f16, int B, int T, double *__restrict__ gstats, int n_gstats) {
+                       __nv_bfloat16 *__restrict__ out, int f16, float scale, int B, int T, double *__restrict__ gstats, int n_gstats) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float tile[32][33];
@@ -671,7 +674,7 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
         const int c = c0 + i, t = t0 + tx;
         float v = 0.f;
         if (t < T && c < kInCh)
-            v = ((c < kMel) ? x[((size_t)b * kMel + c) * T + t] : mu[((size_t)b * kMel + (c - kMel)) * T + t]) * mask[(size_t)b * T + t];
+            v = ((c < kMel) ? x[((size_t)b * kMel + c) * T + t] : mu[((size_t)b * kMel + (c - kMel)) * T + t]) * (mask[(size_t)b * T + t] * scale);
         tile[i][tx] = v;
     }
     __syncthreads();
@@ -685,7 +688,7 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
 // (identity when Tin == T) followed by the x*mask of the next Resnet1D.
 __global__ void __launch_bounds__(256)
 resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__restrict__ mask,
-                          __nv_bfloat16 *__restrict__ out, int f16, int B, int T) {
+                          __nv_bfloat16 *__restrict__ out, int f16, float o16_scale, int B, int T) {
     pdl_launch_dependents();
     pdl_wait();
     const size_t n4 = (size_t)B * T * (kC / 4);
@@ -696,7 +699,7 @@ resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__
         const int b = (int)(row / T), t = (int)(row % T);
         int ts = t;
         if (Tin != T) { ts = (int)floorf((float)t * scale); if (ts > Tin - 1) ts = Tin - 1; }
-        const float mk = mask[(size_t)b * T + t];
+        const float mk = mask[(size_t)b * T + t] * o16_scale;
         const float4 v = *reinterpret_cast<const float4 *>(in + ((size_t)b * Tin + ts) * kC + c);
         *reinterpret_cast<uint2 *>(out + i * 4) = make_uint2(pack16x2(v.x * mk, v.y * mk, f16), pack16x2(v.z * mk, v.w * mk, f16));
     }

@@ -49,6 +49,7 @@ struct FfnArgs {
     float *out_f32;                    // fp32 [B][T][256] or nullptr
     __nv_bfloat16 *out_b16;            // 16-bit [B][T][256] or nullptr, rows multiplied by omask
     const float *omask; int omask_T;
+    float o16_scale;                   // multiplies the 16-bit output as well (fp16 range guard: stream tensors are stored scaled down)
     // norm3 of the transformer block (transformer.py:352) folded in: when ln_in != nullptr the A operand is
     // LayerNorm(ln_in rows) * ln_g + ln_b, built in shared memory by the epilogue warps (idle until the first FFN1
     // chunk completes) instead of arriving by TMA
@@ -443,7 +444,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int t = t0 + 32 * q + 4 * i + rsub;
             const bool ok = t < g.T;
             orow[i] = ok ? (int)(((long long)b * g.T + t) * kC) : -1;
-            mk[i] = (ok && g.omask) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f;
+            mk[i] = g.o16_scale * ((ok && g.omask) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f);
         }
         float4 rv[8];
         auto load_res = [&](int jj) {

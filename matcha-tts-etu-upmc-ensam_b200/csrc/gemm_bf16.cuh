@@ -48,6 +48,9 @@ struct GemmBf16Args {
     int out_T, out_stride, out_off;    // output row of tile row t: t*out_stride + out_off (ConvTranspose phases)
     int f16;                           // operands are IEEE fp16 instead of bf16
     int debug;
+    // fp16 range guard (decoder.cu kStreamScale): the accumulator is multiplied by acc_scale before the bias (the A rows
+    // were stored scaled down), the 16-bit output by o16_scale (it is a residual-stream tensor, stored scaled down)
+    float acc_scale, o16_scale;
     // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
     // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
     int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
@@ -281,8 +284,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             if (TMA_EPI) {
                 const int t = trow0 + lane;                     // this thread's output row (TMEM lane)
                 const bool valid = t < g.Tout;
-                float mk = 1.0f;
-                if (B16 && g.omask && valid) mk = g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
+                float mk = g.o16_scale;
+                if (B16 && g.omask && valid) mk *= g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
+                const float asc = g.acc_scale;
                 const CUtensorMap *const om = light ? &tmO2 : &tmO;
                 uint32_t v[2][32];
                 tmem_ld32_issue(tacc + 32 * jhalf, v[0]);
@@ -301,8 +305,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         const float4 bb = bp[i];
-                        x[4 * i] = __uint_as_float(v[jj & 1][4 * i]) + bb.x; x[4 * i + 1] = __uint_as_float(v[jj & 1][4 * i + 1]) + bb.y;
-                        x[4 * i + 2] = __uint_as_float(v[jj & 1][4 * i + 2]) + bb.z; x[4 * i + 3] = __uint_as_float(v[jj & 1][4 * i + 3]) + bb.w;
+                        x[4 * i] = fmaf(__uint_as_float(v[jj & 1][4 * i]), asc, bb.x); x[4 * i + 1] = fmaf(__uint_as_float(v[jj & 1][4 * i + 1]), asc, bb.y);
+                        x[4 * i + 2] = fmaf(__uint_as_float(v[jj & 1][4 * i + 2]), asc, bb.z); x[4 * i + 3] = fmaf(__uint_as_float(v[jj & 1][4 * i + 3]), asc, bb.w);
                     }
                     if (EPI == 1) {
 #pragma unroll
@@ -382,8 +386,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const bool ok = t < g.Tout;
                     const long long r = (long long)b * g.out_T + (long long)t * g.out_stride + g.out_off;
                     orow[i] = ok ? (int)(r * ldo) : -1;
-                    mk[i] = 1.0f;
-                    if (B16 && g.omask && ok) mk[i] = g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
+                    mk[i] = g.o16_scale;
+                    if (B16 && g.omask && ok) mk[i] *= g.omask[(size_t)b * g.omask_T + (size_t)t * g.out_stride + g.out_off];
                 }
                 float4 rv[8];
                 auto load_res = [&](int jj) {                    // residual rows of chunk jj (issued one chunk ahead)
@@ -422,7 +426,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         x[i] = *reinterpret_cast<const float4 *>(tb + (4 * i + rsub) * kGEpiPitch + c4);
-                        x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w;
+                        x[i].x = fmaf(x[i].x, g.acc_scale, bias.x); x[i].y = fmaf(x[i].y, g.acc_scale, bias.y);
+                        x[i].z = fmaf(x[i].z, g.acc_scale, bias.z); x[i].w = fmaf(x[i].w, g.acc_scale, bias.w);
                         if (EPI == 1) { x[i].x = gelu_erf_fast_f(x[i].x); x[i].y = gelu_erf_fast_f(x[i].y); x[i].z = gelu_erf_fast_f(x[i].z); x[i].w = gelu_erf_fast_f(x[i].w); }
                         if (RES) { x[i].x += rv[i].x; x[i].y += rv[i].y; x[i].z += rv[i].z; x[i].w += rv[i].w; }
                     }
