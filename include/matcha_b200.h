@@ -180,6 +180,18 @@ int matcha_b200_decoder_forward(const float *x_dev, const float *mu_dev, const f
                                 const void *blob_bf16_dev, void *ws_dev, long long ws_bytes, int B, int T,
                                 int precision, void *stream);
 
+/* BaseConditionalFlowMatching.compute_loss, forward value (flow_matching.py:106-151) in one call:
+ *   phi = (1 - (1 - sigma_min) t_b) z + t_b x1                   (:138), written to phi_dev [B][80][T]
+ *   u_pred = Decoder.forward(phi, mask, mu, t)                    (:145), written to u_pred_dev when it is not NULL
+ *   sums_dev[0] = sum (u_pred - (x1 - (1 - sigma_min) z))^2  over all B*80*T elements, sums_dev[1] = sum(mask)   (:142-148)
+ * (loss = sums[0] / (sums[1] * 80), :149).  t_dev: [B] per-sample times.  ws: workspace_bytes(B, T, n_rows = B, precision).
+ * 16-bit precisions: phi is formed inside the input-packing kernel and the squared error inside the final projection's
+ * epilogue, so u_pred / u_target never reach HBM.  MB200_PREC_F32: separate mix / mse kernels, u_pred_dev is required. */
+int matcha_b200_cfm_loss_forward(const float *x1_dev, const float *z_dev, const float *t_dev, const float *mu_dev,
+                                 const float *mask_dev, double sigma_min, float *phi_dev, float *u_pred_dev,
+                                 double *sums_dev, const float *blob_dev, const void *blob_bf16_dev, void *ws_dev,
+                                 long long ws_bytes, int B, int T, int precision, void *stream);
+
 /* t_host/dt_host: the n_steps (t_k, dt_k) pairs the reference loop produces in fp32
  * (flow_matching.py:85-102); out_dev may not alias x0_dev.  n_steps <= 64. */
 int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,

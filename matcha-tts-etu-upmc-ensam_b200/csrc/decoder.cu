@@ -116,6 +116,9 @@ struct Ctx {
     int err;
     int f16;             // 16-bit operand format of the tensor-core mode: 0 bf16, 1 fp16
     const float *fin_xin = nullptr; float fin_dt = 0.f; float *fin_out = nullptr;   // set around the final-projection GEMM
+    // loss mode (matcha_b200_cfm_loss_forward): x is x1, pack_input forms phi_t, the final projection accumulates the MSE sums
+    const float *loss_z = nullptr, *loss_t = nullptr; float loss_oms = 0.f; float *loss_phi = nullptr; double *loss_sums = nullptr;
+    const float *loss_x1 = nullptr; int fin_loss = 0;
     int debug = 0;
     std::vector<TmapEntry> tmaps;   // tensor maps of this call's bf16 tensors
 };
@@ -364,7 +367,9 @@ static void gemm_b(Ctx &c, int sflags, const bf16 *a0, int c0, const bf16 *a1, i
     g.acc_scale = (sflags & kSA) ? stream_up(c) : 1.0f; g.o16_scale = (sflags & kSO) ? stream_down(c) : 1.0f;
     g.out_T = out_T > 0 ? out_T : T; g.out_stride = out_T > 0 ? out_stride : 1; g.out_off = out_T > 0 ? out_off : 0;
     g.fin_n = 0; g.fin_xin = nullptr; g.fin_dt = 0.f; g.fin_out = nullptr;
-    if (c.fin_out) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
+    g.loss_x1 = nullptr; g.loss_z = nullptr; g.loss_oms = 0.f; g.loss_sum = nullptr;
+    if (c.fin_out || c.fin_loss) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
+    if (c.fin_loss) { g.loss_x1 = c.loss_x1; g.loss_z = c.loss_z; g.loss_oms = c.loss_oms; g.loss_sum = c.loss_sums; }
     const long long n_tiles = (long long)g.tiles_per_sample * c.B * (N / kGN);
     const int grid = (int)(n_tiles < kNumSMsB200 ? n_tiles : kNumSMsB200);      // persistent: one CTA per SM
     g.debug = c.debug;
@@ -544,7 +549,9 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
     const int T = c.T, T2 = (T + 1) / 2, Tu = 2 * T2;
     auto tb = [&](int st) { return tb_rows + (size_t)st * n_rows * kC; };
     dim3 pgrid((T + 31) / 32, kInChPad / 32, c.B);
-    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, stream_down(c), c.B, T, w.gstats, kGnConvs * c.B * kGroups * 2);
+    PackLoss pl;
+    pl.z = c.loss_z; pl.tvec = c.loss_t; pl.one_minus_sigma = c.loss_oms; pl.phi_out = c.loss_phi; pl.sums = c.loss_sums;
+    launch(c, pack_input_bf16_kernel, pgrid, 256, 0, x, mu, c.mask, w.x0b, c.f16, stream_down(c), c.B, T, w.gstats, kGnConvs * c.B * kGroups * 2, pl);
     // down 0 @T; the stride-2 Downsample1D (decoder.py:95) stays on the fp32 implicit-GEMM kernel
     run_stage_bf16(c, 0, W.st[0], Wb.st[0], w.x0b, kInChPad, nullptr, 0, T, tb(0), tb_per_sample, (T & 1) ? w.s0 : nullptr, w.s0b);
     if ((T & 1) == 0) {
@@ -583,9 +590,9 @@ static void decoder_eval_bf16(Ctx &c, const DecW &W, const DecWb &Wb, const floa
         int eb = (int)((n4 + 255) / 256); if (eb > 148 * 16) eb = 148 * 16;
         launch(c, gn_mish_rows_kernel<0>, (unsigned)(((size_t)c.B * T + kGmRowsPerBlock - 1) / kGmRowsPerBlock), 256, 0, w.h, gsf, W.gf,
                W.bef, c.mask, c.T, nullptr, 0, nullptr, nullptr, nullptr, nullptr, w.a1b, c.f16, c.B, T);
-        c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out;
+        c.fin_xin = x_in; c.fin_dt = dt; c.fin_out = out; c.fin_loss = c.loss_z != nullptr; c.loss_x1 = x;
         gemm_b(c, 0, w.a1b, kC, nullptr, 0, 1, tap0, T, Wb.wp, kC, W.bp, 0, nullptr, nullptr, nullptr, false);
-        c.fin_out = nullptr;
+        c.fin_out = nullptr; c.fin_loss = 0;
     }
 }
 
@@ -739,13 +746,16 @@ extern "C" int matcha_b200_decoder_pack_bf16(const float *blob_dev, void *blob_b
     return MB200_OK;
 }
 
-extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_dev, const float *mask_dev,
-                                            const float *t_dev, int n_t, float *out_dev, const float *blob_dev,
-                                            const void *blob_bf16_dev, void *ws_dev, long long ws_bytes, int B, int T,
-                                            int precision, void *stream) {
-    int rc = check_common(x_dev, mu_dev, mask_dev, t_dev, out_dev, blob_dev, B, T);
+// Loss mode of the forward (16-bit precisions): x_dev is x1, phi_t and the two loss sums are produced by the first / last kernel.
+struct LossFwd { const float *z; float one_minus_sigma; float *phi; double *sums; };
+static int forward_impl(const float *x_dev, const float *mu_dev, const float *mask_dev,
+                        const float *t_dev, int n_t, float *out_dev, const float *blob_dev,
+                        const void *blob_bf16_dev, void *ws_dev, long long ws_bytes, int B, int T,
+                        int precision, void *stream, const LossFwd *loss) {
+    int rc = check_common(x_dev, mu_dev, mask_dev, t_dev, loss ? (const void *)loss->phi : (const void *)out_dev, blob_dev, B, T);
     if (rc != MB200_OK) return rc;
     if (!ws_dev || (n_t != 1 && n_t != B)) return MB200_ERR_INVALID_ARG;
+    if (loss && (precision == MB200_PREC_F32 || n_t != B || !loss->z || !loss->sums)) return MB200_ERR_INVALID_ARG;
     // same sub-batch streams as the Euler solve (one eval is a latency-bound chain of 46 launches at B = 32)
     const int S = solve_split(B);
     DevGuard guard;
@@ -778,7 +788,11 @@ extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_d
     for (int i = 0; i < S; ++i) {
         const size_t off = (size_t)b0[i] * kMel * T;
         const float *tb = c[0].ws.tb + (per_sample ? (size_t)b0[i] * kC : 0);     // rows of this sub-batch's samples
-        eval_any(c[i], W, Wb, precision, x_dev + off, mu_dev + off, tb, n_t, per_sample, nullptr, 0.f, out_dev + off);
+        if (loss) {
+            c[i].loss_z = loss->z + off; c[i].loss_t = t_dev + b0[i]; c[i].loss_oms = loss->one_minus_sigma;
+            c[i].loss_phi = loss->phi + off; c[i].loss_sums = loss->sums;
+        }
+        eval_any(c[i], W, Wb, precision, x_dev + off, mu_dev + off, tb, n_t, per_sample, nullptr, 0.f, out_dev ? out_dev + off : nullptr);
     }
     int launches = 0;
     for (int i = 0; i < S; ++i) { if (c[i].err) return c[i].err; launches += c[i].launches; }
@@ -788,6 +802,44 @@ extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_d
     }
     MB200_CUDA_TRY(cudaGetLastError());
     return launches;
+}
+
+extern "C" int matcha_b200_decoder_forward(const float *x_dev, const float *mu_dev, const float *mask_dev,
+                                            const float *t_dev, int n_t, float *out_dev, const float *blob_dev,
+                                            const void *blob_bf16_dev, void *ws_dev, long long ws_bytes, int B, int T,
+                                            int precision, void *stream) {
+    return forward_impl(x_dev, mu_dev, mask_dev, t_dev, n_t, out_dev, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, B, T, precision,
+                        stream, nullptr);
+}
+
+// BaseConditionalFlowMatching.compute_loss, forward value (flow_matching.py:106-151), in one call: phi_t, Decoder.forward with
+// per-sample t, and the two sums of the masked MSE.  16-bit precisions: phi_t is formed inside the input-packing kernel and
+// the squared error inside the final projection's epilogue (u_pred and u_target never reach HBM; u_pred_dev may be NULL).
+// fp32 precision: the separate mix / mse kernels of align.cu around the fp32 forward (u_pred_dev required).
+extern "C" int matcha_b200_cfm_loss_mix(float *, const float *, const float *, const float *, double, int, long long, void *);
+extern "C" int matcha_b200_cfm_loss_mse(double *, const float *, const float *, const float *, const float *, double, long long,
+                                         long long, void *);
+extern "C" int matcha_b200_cfm_loss_forward(const float *x1_dev, const float *z_dev, const float *t_dev, const float *mu_dev,
+                                             const float *mask_dev, double sigma_min, float *phi_dev, float *u_pred_dev,
+                                             double *sums_dev, const float *blob_dev, const void *blob_bf16_dev, void *ws_dev,
+                                             long long ws_bytes, int B, int T, int precision, void *stream) {
+    if (!x1_dev || !z_dev || !t_dev || !mu_dev || !mask_dev || !phi_dev || !sums_dev || B < 1 || T < 1) return MB200_ERR_INVALID_ARG;
+    if (precision == MB200_PREC_F32) {
+        if (!u_pred_dev) return MB200_ERR_INVALID_ARG;
+        int rc = matcha_b200_cfm_loss_mix(phi_dev, x1_dev, z_dev, t_dev, sigma_min, B, (long long)kMel * T, stream);
+        if (rc != MB200_OK) return rc;
+        const int n = forward_impl(phi_dev, mu_dev, mask_dev, t_dev, B, u_pred_dev, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, B, T,
+                                   precision, stream, nullptr);
+        if (n < 0) return n;
+        rc = matcha_b200_cfm_loss_mse(sums_dev, u_pred_dev, x1_dev, z_dev, mask_dev, sigma_min, (long long)B * kMel * T,
+                                      (long long)B * T, stream);
+        return rc != MB200_OK ? rc : n + 2;
+    }
+    MB200_CUDA_TRY(cudaMemsetAsync(sums_dev, 0, 2 * sizeof(double), (cudaStream_t)stream));
+    LossFwd lf;
+    lf.z = z_dev; lf.one_minus_sigma = (float)(1.0 - sigma_min); lf.phi = phi_dev; lf.sums = sums_dev;
+    return forward_impl(x1_dev, mu_dev, mask_dev, t_dev, B, u_pred_dev, blob_dev, blob_bf16_dev, ws_dev, ws_bytes, B, T, precision,
+                        stream, &lf);
 }
 
 extern "C" int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const float *mask_dev,

@@ -660,9 +660,14 @@ final_proj_kernel(const float *__restrict__ hf, const float *__restrict__ stats,
 constexpr int kInChPad = 192;      // 160 input channels padded to three 64-wide K chunks
 
 // X0b[b][t][0:80] = x*mask, [80:160] = mu*mask, [160:192] = 0   (decoder.py:288 + the x*mask of :65,85)
+// Loss mode (flow_matching.py:130-138, z != nullptr): x holds x1, the kernel forms phi_t = (1 - (1-sigma) t_b) z + t_b x1 in the
+// reference's fp32 operation order, stores it channels-first to phi_out (compute_loss returns it) and packs phi_t * mask;
+// the blocks of channel slab 0 add sum(mask) into loss_sums[1] (the denominator of flow_matching.py:149).
+struct PackLoss { const float *z, *tvec; float one_minus_sigma; float *phi_out; double *sums; };
 __global__ void __launch_bounds__(256)
 pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
-                       __nv_bfloat16 *__restrict__ out, int f16, float scale, int B, int T, double *__restrict__ gstats, int n_gstats) {
+                       __nv_bfloat16 *__restrict__ out, int f16, float scale, int B, int T, double *__restrict__ gstats, int n_gstats,
+                       const PackLoss loss) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float tile[32][33];
@@ -670,12 +675,28 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
     if (blockIdx.x == 0 && blockIdx.y == 0)        // first kernel of an eval: clear the GroupNorm accumulators of its 13 convs
         for (int i = blockIdx.z * 256 + threadIdx.x; i < n_gstats; i += gridDim.z * 256) gstats[i] = 0.0;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    float tb = 0.f, ta = 0.f;
+    if (loss.z) { tb = loss.tvec[b]; ta = __fsub_rn(1.f, __fmul_rn(loss.one_minus_sigma, tb)); }
     for (int i = ty; i < 32; i += 8) {
         const int c = c0 + i, t = t0 + tx;
         float v = 0.f;
-        if (t < T && c < kInCh)
-            v = ((c < kMel) ? x[((size_t)b * kMel + c) * T + t] : mu[((size_t)b * kMel + (c - kMel)) * T + t]) * (mask[(size_t)b * T + t] * scale);
+        if (t < T && c < kInCh) {
+            if (c < kMel) {
+                const size_t o = ((size_t)b * kMel + c) * T + t;
+                v = x[o];
+                if (loss.z) { v = __fadd_rn(__fmul_rn(ta, loss.z[o]), __fmul_rn(tb, v)); loss.phi_out[o] = v; }
+            } else {
+                v = mu[((size_t)b * kMel + (c - kMel)) * T + t];
+            }
+            v *= mask[(size_t)b * T + t] * scale;
+        }
         tile[i][tx] = v;
+    }
+    if (loss.z && blockIdx.y == 0 && ty == 0) {
+        float m = t0 + tx < T ? mask[(size_t)b * T + t0 + tx] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
+        if (tx == 0) atomicAdd(loss.sums + 1, (double)m);
     }
     __syncthreads();
     for (int i = ty; i < 32; i += 8) {

@@ -54,6 +54,9 @@ struct GemmBf16Args {
     // final projection mode (decoder.py:369-371 + flow_matching.py:95): the first fin_n columns are written
     // channels-first, v = (acc + bias) * mask, out = x_in + dt * v (or v when x_in == nullptr)
     int fin_n; const float *fin_xin; float fin_dt; float *fin_out;
+    // loss mode of the final projection (flow_matching.py:142-148): *loss_sum += sum over ALL frames t < Tout of
+    // (v - (x1 - (1-sigma) z))^2, v the masked prediction (the reference's target is not masked); fin_out may be nullptr
+    const float *loss_x1, *loss_z; float loss_oms; double *loss_sum;
     // GroupNorm statistics of the fp32 output (kGStats): [B][8 groups][sum, sum of squares], accumulated with atomics
     double *gstats;
     // Second output block (Resnet1D: block1's conv and res_conv read the same input, decoder.py:81,85): the N tiles at
@@ -358,13 +361,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
                 const int t = trow0 + lane;
                 const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
+                float lsum = 0.f;
                 for (int j = jhalf; j < jhalf + 4 && j * 32 < g.fin_n; ++j) {
                     uint32_t v[32];
                     float xin[32];
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {              // all loads of the chunk first
                         const int n = 32 * j + i;
-                        xin[i] = (g.fin_xin && n < g.fin_n && t < g.Tout) ? g.fin_xin[((size_t)b * g.fin_n + n) * g.Tout + t] : 0.f;
+                        const bool ok = n < g.fin_n && t < g.Tout;
+                        const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
+                        xin[i] = 0.f;
+                        if (g.loss_sum) { if (ok) xin[i] = __fsub_rn(g.loss_x1[o], __fmul_rn(g.loss_oms, g.loss_z[o])); }
+                        else if (g.fin_xin && ok) xin[i] = g.fin_xin[o];
                     }
                     tmem_ld32(tacc + 32 * j, v);
 #pragma unroll
@@ -372,9 +380,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         const int n = 32 * j + i;
                         if (n < g.fin_n && t < g.Tout) {
                             const float vel = (__uint_as_float(v[i]) + g.bias[n]) * mk;
-                            g.fin_out[((size_t)b * g.fin_n + n) * g.Tout + t] = g.fin_xin ? __fadd_rn(xin[i], __fmul_rn(g.fin_dt, vel)) : vel;
+                            const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
+                            if (g.loss_sum) {
+                                const float d = __fsub_rn(vel, xin[i]);
+                                lsum = fmaf(d, d, lsum);
+                                if (g.fin_out) g.fin_out[o] = vel;
+                            } else {
+                                g.fin_out[o] = g.fin_xin ? __fadd_rn(xin[i], __fmul_rn(g.fin_dt, vel)) : vel;
+                            }
                         }
                     }
+                }
+                if (g.loss_sum && jhalf * 32 < g.fin_n) {
+                    double ds = (double)lsum;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
+                    if (lane == 0) atomicAdd(g.loss_sum, ds);
                 }
             } else {
                 // output element offsets of this lane's 8 rows (column part added per chunk); -1 = row beyond Tout

@@ -83,6 +83,9 @@ def load_library():
     lib.matcha_b200_decoder_forward.restype = c_int
     lib.matcha_b200_decoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                                 c_void_p, ll, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_cfm_loss_forward.restype = c_int
+    lib.matcha_b200_cfm_loss_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_double, c_void_p, c_void_p,
+                                                 c_void_p, c_void_p, c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
     lib.matcha_b200_cfm_solve_euler.restype = c_int
     lib.matcha_b200_cfm_solve_euler.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                                 c_void_p, c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
@@ -125,5 +128,6 @@ DECLARED_SYMBOLS = (
     "matcha_b200_decoder_blob_bf16_bytes",
     "matcha_b200_decoder_pack_bf16",
     "matcha_b200_decoder_forward",
+    "matcha_b200_cfm_loss_forward",
     "matcha_b200_cfm_solve_euler",
 )

@@ -280,6 +280,34 @@ class Decoder(torch.nn.Module):
         return st["out"].to(x.dtype, copy=True)
 
     @torch.no_grad()
+    def loss_forward(self, x1, z, t, mu, mask, sigma_min, want_pred=False):
+        """compute_loss's device work in ONE C call (flow_matching.py:130-149): phi_t, the decoder eval with per-sample t,
+        and the two sums of the masked MSE.  Returns (sums[2] fp64 on the device = [sum sq. error, sum(mask)], phi_t,
+        u_pred or None).  In the 16-bit modes phi_t is formed by the input-packing kernel and the squared error by the final
+        projection's epilogue: u_pred is only written when ``want_pred`` asks for it."""
+        if not x1.is_cuda:
+            raise RuntimeError("matcha_b200.Decoder needs CUDA tensors (sm_100a); there is no CPU fallback")
+        lib = load_library()
+        B, _, T = x1.shape
+        dev = x1.device
+        x1f, zf, muf = x1.float().contiguous(), z.float().contiguous(), mu.float().contiguous()
+        mf = mask.float().reshape(B, T).contiguous()
+        tf = t.detach().to(dev, torch.float32).reshape(-1).contiguous()
+        assert tf.numel() == B
+        blob, b16 = self._blob_on(dev), self._blob16_on(dev)
+        phi = torch.empty_like(x1f)
+        pred = torch.empty_like(x1f) if (want_pred or self.precision == "fp32") else None
+        sums = torch.empty(2, dtype=torch.float64, device=dev)
+        ws = self._workspace(dev, B, T, B)
+        with torch.cuda.device(dev):
+            self.last_launches = check(lib.matcha_b200_cfm_loss_forward(
+                x1f.data_ptr(), zf.data_ptr(), tf.data_ptr(), muf.data_ptr(), mf.data_ptr(), float(sigma_min), phi.data_ptr(),
+                pred.data_ptr() if pred is not None else None, sums.data_ptr(), blob.data_ptr(),
+                b16.data_ptr() if b16 is not None else None, ws.data_ptr(), ws.numel(), B, T, _PRECISIONS[self.precision],
+                _stream_ptr(dev)), "cfm_loss_forward")
+        return sums, phi, pred
+
+    @torch.no_grad()
     def solve_euler(self, x, t_span, mu, mask, use_graph=None):
         """The whole Euler loop of flow_matching.py:67-104 in one C call.  With ``use_graph`` (default: on for
         CUDA inputs) the ~95 kernel launches per step are captured once per (B, T, n_steps) into a CUDA graph

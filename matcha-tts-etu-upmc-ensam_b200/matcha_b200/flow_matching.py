@@ -6,7 +6,7 @@ Mirrors /root/reference/matcha/models/components/flow_matching.py:
 Same names, argument meaning and results; ``solve_ode_euler`` hands the whole loop to one C call.
 ``compute_loss`` returns the forward value only (the decoder kernels are inference kernels; the
 backward pass of training is outside this path); its phi_t construction and masked-MSE
-reduction are device kernels (csrc/align.cu).
+reduction are fused into the first / last kernel of the decoder eval (csrc/decoder.cu).
 """
 import torch
 
@@ -37,31 +37,18 @@ class BaseConditionalFlowMatching(torch.nn.Module):
     def compute_loss(self, x1, mask, mu, spks=None, cond=None, *, t=None, z=None):
         """flow_matching.py:106-151, forward value.  ``t`` [B,1,1] / ``z`` may be injected (tests share
         them with the oracle); otherwise they are drawn in the reference's RNG order (t, then z).
-        phi_t and the masked-MSE sums are one kernel each (csrc/align.cu); u_target is never stored."""
+        One C call (matcha_b200_cfm_loss_forward): in the 16-bit modes phi_t is formed inside the decoder's input-packing
+        kernel and the squared error inside the final projection's epilogue; u_pred / u_target are never stored."""
         if not x1.is_cuda:
             raise RuntimeError("matcha_b200.CFM needs CUDA tensors (sm_100a); there is no CPU fallback")
-        lib = load_library()
         dev = x1.device
         batch_size = mu.shape[0]
         if t is None:
             t = torch.rand([batch_size, 1, 1], device=dev, dtype=mu.dtype)        # :130
         if z is None:
             z = torch.randn_like(x1)                                              # :133
-        x1f, zf = x1.float().contiguous(), z.float().contiguous()
-        tf = t.float().reshape(batch_size).contiguous()
-        mf = mask.float().contiguous()
-        phi_t = torch.empty_like(x1f)
-        per = x1f.numel() // max(batch_size, 1)
-        with torch.cuda.device(dev):
-            check(lib.matcha_b200_cfm_loss_mix(phi_t.data_ptr(), x1f.data_ptr(), zf.data_ptr(), tf.data_ptr(),
-                                               float(self.sigma_min), batch_size, per, _stream_ptr(dev)), "cfm_loss_mix")  # :138
-        u_pred = self.estimator(phi_t, mask, mu, tf, cond)                        # :145
-        sums = torch.empty(2, dtype=torch.float64, device=dev)
-        with torch.cuda.device(dev):
-            check(lib.matcha_b200_cfm_loss_mse(sums.data_ptr(), u_pred.data_ptr(), x1f.data_ptr(), zf.data_ptr(),
-                                               mf.data_ptr(), float(self.sigma_min), x1f.numel(), mf.numel(),
-                                               _stream_ptr(dev)), "cfm_loss_mse")  # :142-148
-        loss = (sums[0] / (sums[1] * x1f.shape[1])).float()                       # :149
+        sums, phi_t, _ = self.estimator.loss_forward(x1, z, t.reshape(batch_size), mu, mask, self.sigma_min)   # :138-148
+        loss = (sums[0] / (sums[1] * x1.shape[1])).float()                       # :149
         return loss, phi_t.to(x1.dtype)
 
 

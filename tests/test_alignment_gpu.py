@@ -176,3 +176,43 @@ def test_cfm_loss_kernels_vs_oracle():
                              t.double(), z.double())
     full = full[0] if isinstance(full, (tuple, list)) else full
     assert abs(float(loss) - float(full)) < 1e-5 * abs(float(full))
+
+
+@pytest.mark.parametrize("precision", ["fp16", "bf16"])
+@pytest.mark.parametrize("B,T,lengths", [(3, 50, [50, 31, 8]), (9, 131, [131, 120, 99, 80, 64, 50, 33, 9, 2]), (1, 64, [40])])
+def test_cfm_loss_fused_into_decoder_eval(precision, B, T, lengths):
+    """in the tensor-core modes compute_loss is ONE call -- phi_t formed by the decoder's input-packing kernel
+    (bit-exact against flow_matching.py:138), the squared error summed in the final projection's epilogue.  Checked against
+    the same sums formed from the decoder's own stored prediction (tight: only the summation order differs) and against the
+    fp64 oracle's loss (the mode's tolerance).  B = 9 runs the sub-batch streams (uneven split)."""
+    from matcha_b200 import flow_matching as fm
+    g = torch.Generator().manual_seed(B * 100 + T)
+    x1, z = torch.randn(B, 80, T, generator=g), torch.randn(B, 80, T, generator=g)
+    mu = torch.randn(B, 80, T, generator=g)
+    t = torch.rand(B, 1, 1, generator=g)
+    mask = torch.zeros(B, 1, T)
+    for i, n in enumerate(lengths):
+        mask[i, :, :n] = 1
+    w = odec.make_weights(11, "rich")
+    cfm = fm.CFM(in_channels=160, out_channel=80, cfm_params=SimpleNamespace(solver="euler", sigma_min=1e-4),
+                 decoder_params=dict(channels=(256, 256), dropout=0.05, attention_head_dim=64, n_blocks=1,
+                                     num_mid_blocks=2, num_heads=4), precision=precision)
+    cfm.load_state_dict({"estimator." + k: v for k, v in w.items()})
+    loss, phi_t = cfm.compute_loss(x1.cuda(), mask.cuda(), mu.cuda(), t=t.cuda(), z=z.cuda())
+    phi_want, u_want = oal.cfm_mix(x1, z, t)
+    assert torch.equal(phi_t.cpu(), phi_want)
+    # the same call with the prediction written out: identical sums up to atomics order; the stored prediction reproduces them
+    sums, phi2, pred = cfm.estimator.loss_forward(x1.cuda(), z.cuda(), t.reshape(B).cuda(), mu.cuda(), mask.cuda(), 1e-4, want_pred=True)
+    assert torch.equal(phi2.cpu(), phi_want)
+    assert float(sums[1]) == float(mask.sum())
+    want = oal.cfm_mse(pred.cpu(), u_want, mask)
+    torch.testing.assert_close(loss.cpu(), want, rtol=LOSS_RTOL, atol=0)
+    torch.testing.assert_close((sums[0] / (sums[1] * 80)).float().cpu(), want, rtol=LOSS_RTOL, atol=0)
+    # and the separate forward on phi_t gives the same prediction (same kernels, same inputs)
+    u_pred = cfm.estimator(phi_t, mask.cuda(), mu.cuda(), t.reshape(B).cuda())
+    assert float((u_pred - pred).abs().max()) <= 1e-6 * float(pred.abs().max()) + 1e-6
+    torch.set_num_threads(8)
+    full = odec.compute_loss(odec.cast_weights(w, torch.float64), x1.double(), mask.double(), mu.double(), t.double(), z.double())
+    full = full[0] if isinstance(full, (tuple, list)) else full
+    tol = {"fp16": 2e-3, "bf16": 1.5e-2}[precision] * 2       # loss ~ |u_pred - u|^2: twice the relative error of the prediction
+    assert abs(float(loss) - float(full)) < tol * abs(float(full))
