@@ -837,10 +837,12 @@ def run_ours(a):
     for _ in range(a.warmup):
         step()
     finish()
-    barrier()
+    # the clock sampler (rank 0: NVML start-up, a few ms of host time) starts BEFORE the barrier: a rank that enters the timed
+    # region late makes every other rank wait in the first step's collective, inside their timed regions
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    barrier()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps + 1)]
     ev[0].record()
     for i in range(a.steps):
