@@ -19,6 +19,8 @@ import torch
 
 from ._lib import check, load_library
 
+ERR_UNSUPPORTED = -2       # MB200_ERR_UNSUPPORTED (include/matcha_b200.h)
+
 PATH_I32, PATH_F32 = 0, 1
 
 
@@ -35,7 +37,12 @@ def _fused_mask_fits(value):
     out = (ctypes.c_int * 8)()
     B, T_x, T_y = value.shape
     rc = load_library().matcha_b200_mas_query_launch(max(B, 1), T_x, T_y, 1, 1, ctypes.byref(out))
-    return rc == 0
+    if rc == 0:
+        return True
+    if rc == ERR_UNSUPPORTED:          # the fused-mask plan does not fit on chip: the caller forms value*mask first
+        return False
+    check(rc, "mas_query_launch")      # any other code is a real error, not "does not fit"
+    return False
 
 
 def lengths_from_mask(mask):
