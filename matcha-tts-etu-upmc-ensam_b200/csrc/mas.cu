@@ -34,7 +34,7 @@ namespace mb200 {
 constexpr int kChunk = 32;        // mel frames per tile
 constexpr int kBoxRows = 32;      // tokens per TMA box
 constexpr int kBoxBytes = kBoxRows * kChunk * 4;
-constexpr int kWriterWarps = 4;
+constexpr int kWriterWarps = 4;   // 2 writers: 0.869 -> 0.819 of the HBM peak at 400x2000, 1: 0.564 (profiles/r2_exp11_mas_writer_warps.log)
 constexpr int kMaxStages = 8;
 constexpr int kBndDepth = 4;      // boundary-row ring depth between neighbouring DP warps
 constexpr int kBndFloats = 36;    // [0]=Q[32c-1], [1..32]=Q[32c..32c+31], padded to 16 bytes
@@ -618,6 +618,29 @@ static MasKernelFn mas_pick_kernel(int R) {
     return nullptr;
 }
 
+// Multi-wave launches (more utterances than resident CTAs) are latency-bound per CTA -- one utterance's DP is a dependent chain --
+// so HBM throughput comes from utterances in flight per SM, not from ring depth: shrink the ring (down to 2 stages) whenever that
+// lets one more CTA share the SM.  Measured at B = 1024 (profiles/r2_exp8_mas_ctas_per_sm.log): 128x800 3 -> 4 CTAs/SM 0.63 -> 0.69
+// of the HBM peak, 200x1000 2 -> 3 CTAs/SM 0.73 -> 0.78; deeper rings at fewer CTAs/SM only lose (6 stages, 2 CTAs/SM: 0.54).
+// A fifth CTA per SM needs <= 58 registers: the R = 3 kernel then spills inside the DP loop and drops to 0.585 (r2_exp12, reverted).
+static void mas_pick_ring(MasKernelFn fn, bool has_mask, int B, MasPlan *pl) {
+    if (env_int("MB200_MAS_NSTAGE", 0) > 0) return;
+    int dev = 0, sms = kNumSMsB200, occ = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return; }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, pl->threads, pl->smem) != cudaSuccess) { (void)cudaGetLastError(); return; }
+    if ((long long)sms * occ >= B) return;                  // every utterance already has a CTA of its own
+    int best_ns = pl->nstage, best_occ = occ;
+    uint32_t best_smem = pl->smem;
+    for (int ns = pl->nstage - 1; ns >= 2; --ns) {
+        const MasSmem L = mas_smem_layout(has_mask, pl->ndp, ns, pl->txp);
+        int o = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, fn, pl->threads, L.total) != cudaSuccess) { (void)cudaGetLastError(); break; }
+        if (o > best_occ) { best_occ = o; best_ns = ns; best_smem = L.total; }
+    }
+    pl->nstage = best_ns; pl->smem = best_smem;
+}
+
 static int mas_grid(MasKernelFn fn, const MasPlan &pl, int B, int *ctas_per_sm) {
     int dev = 0, sms = kNumSMsB200, occ = 1;
     if (cudaGetDevice(&dev) == cudaSuccess)
@@ -653,6 +676,7 @@ static int mas_launch(
 
     MasKernelFn fn = has_mask ? mas_pick_kernel<true>(pl.R) : mas_pick_kernel<false>(pl.R);
     MB200_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+    mas_pick_ring(fn, has_mask, B, &pl);
 
     CUtensorMap tm_v, tm_m;
     memset(&tm_v, 0, sizeof(tm_v));
@@ -708,6 +732,7 @@ extern "C" int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mas
         (void)cudaGetLastError();   // no device: report the plan, leave grid/occupancy at 0
         out[0] = 0;
     } else {
+        mas_pick_ring(fn, has_mask != 0, B, &pl);
         out[0] = mas_grid(fn, pl, B, &occ);
     }
     out[1] = pl.threads; out[2] = (int)pl.smem; out[3] = pl.R; out[4] = pl.nstage;

@@ -20,7 +20,8 @@ class MatchaB200Error(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_PKG_ROOT, "lib", "libmatcha_b200.so")
+    # MB200_LIB: an alternative build of the same library (A/B timing of a compile-time switch); never a fallback
+    return os.environ.get("MB200_LIB") or os.path.join(_PKG_ROOT, "lib", "libmatcha_b200.so")
 
 
 def load_library():
