@@ -347,18 +347,30 @@ constexpr int kSA = 1, kSO = 2;
 constexpr float kStreamDown = 1.0f / 16.0f, kStreamUp = 16.0f;
 static inline float stream_down(const Ctx &c) { return c.f16 ? kStreamDown : 1.0f; }
 static inline float stream_up(const Ctx &c) { return c.f16 ? kStreamUp : 1.0f; }
+// 32-row slabs per sample (gemm_bf16.cuh::slab_coords).  MB200_FLAT=0 rounds every sample up to whole 128-row tiles (the round-1
+// tiling: tiles never straddle samples).  pad_row: the A-building kernels keep the conv halo in one shared-memory tile and need
+// at least one out-of-range (zero) row between two samples.
+static bool flat_tiling() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("MB200_FLAT"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v != 0;
+}
+static int slabs_per_sample(int T, bool pad_row) {
+    const int rows = T + (pad_row ? 1 : 0);
+    return flat_tiling() ? (rows + 31) / 32 : 4 * ((rows + 127) / 128);
+}
 static void gemm_b(Ctx &c, int sflags, const bf16 *a0, int c0, const bf16 *a1, int c1, int ntaps, const int *taps, int T,
                    const bf16 *w, int N, const float *bias, int act, const float *res, float *out_f32,
                    bf16 *out_b16, bool omask, int out_T = 0, int out_stride = 1, int out_off = 0, double *gstats = nullptr,
                    const float *bias2 = nullptr, float *out2_f32 = nullptr, int kb2_begin = 0, int kb2_count = 0) {
     if (c.err) return;
     CUtensorMap ma0, ma1, mb;
-    if (!tmap_for(c, a0, 3, (uint64_t)c0, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma0)) return;
+    if (!tmap_for(c, a0, 3, (uint64_t)c0, (uint64_t)T, (uint64_t)c.B, kGK, 32, &ma0)) return;
     ma1 = ma0;
-    if (a1 && !tmap_for(c, a1, 3, (uint64_t)c1, (uint64_t)T, (uint64_t)c.B, kGK, kGM, &ma1)) return;
+    if (a1 && !tmap_for(c, a1, 3, (uint64_t)c1, (uint64_t)T, (uint64_t)c.B, kGK, 32, &ma1)) return;
     if (!tmap_for(c, w, 2, (uint64_t)ntaps * (c0 + c1), (uint64_t)N, 1, kGK, kGN, &mb)) return;
     GemmBf16Args g;
-    g.B = c.B; g.Tout = T; g.tiles_per_sample = (T + kGM - 1) / kGM;
+    g.B = c.B; g.Tout = T; g.spp = slabs_per_sample(T, false); g.n_mtiles = (c.B * g.spp + 3) / 4;
     g.ntaps = ntaps;
     for (int i = 0; i < 4; ++i) g.tap_off[i] = i < ntaps ? taps[i] : 0;
     g.c0_chunks = c0 / kGK; g.c1_chunks = c1 / kGK;
@@ -370,7 +382,7 @@ static void gemm_b(Ctx &c, int sflags, const bf16 *a0, int c0, const bf16 *a1, i
     g.loss_x1 = nullptr; g.loss_z = nullptr; g.loss_oms = 0.f; g.loss_sum = nullptr;
     if (c.fin_out || c.fin_loss) { g.fin_n = kMel; g.fin_xin = c.fin_xin; g.fin_dt = c.fin_dt; g.fin_out = c.fin_out; g.omask = c.mask; }
     if (c.fin_loss) { g.loss_x1 = c.loss_x1; g.loss_z = c.loss_z; g.loss_oms = c.loss_oms; g.loss_sum = c.loss_sums; }
-    const long long n_tiles = (long long)g.tiles_per_sample * c.B * (N / kGN);
+    const long long n_tiles = (long long)g.n_mtiles * (N / kGN);
     const int grid = (int)(n_tiles < kNumSMsB200 ? n_tiles : kNumSMsB200);      // persistent: one CTA per SM
     g.debug = c.debug;
     if ((long long)c.B * g.out_T * N >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
@@ -437,7 +449,7 @@ static void abuild_b(Ctx &c, int mode, const float *h, const double *gsum, const
     if (mode == 1) { if (!tmap_out_for(c, out16, false, N, N, T, T, 1, &mo, 32)) return; }
     else if (!tmap_out_for(c, out_f32, true, N, N, T, T, 1, &mo, 16)) return;
     AbuildArgs g;
-    g.B = c.B; g.T = T; g.tiles_per_sample = (T + kGM - 1) / kGM; g.N = N;
+    g.B = c.B; g.T = T; g.tiles_per_sample = (T + kGM - 1) / kGM; g.N = N;    // per-sample tiles: the slab version of this kernel measured slower
     g.h = h; g.gsum = gsum; g.gamma = gamma; g.beta = beta; g.mask = c.mask; g.mask_T = c.T;
     g.tb = tb; g.tb_per_sample = tb_per_sample; g.r = r; g.ln_g = ln_g; g.ln_b = ln_b; g.x1 = x1;
     g.bias = bias; g.gstats = gstats; g.desc_mode = desc_mode;
@@ -472,18 +484,18 @@ static void ffn_b(Ctx &c, const bf16 *a, int T, const bf16 *w1, const float *b1,
                   bool o_stream = true) {
     if (c.err) return;
     CUtensorMap ma, m1, m2, mo;
-    if (!tmap_for(c, a, 3, (uint64_t)kC, (uint64_t)T, (uint64_t)c.B, 64, kFfM, &ma)) return;
+    if (!tmap_for(c, a, 3, (uint64_t)kC, (uint64_t)T, (uint64_t)c.B, 64, 32, &ma)) return;
     if (!tmap_for(c, w1, 2, (uint64_t)kC, (uint64_t)kFfHid, 1, 64, kFfChunk, &m1)) return;
     if (!tmap_for(c, w2, 2, (uint64_t)kFfHid, (uint64_t)kC, 1, 64, kC, &m2)) return;
     mo = m2;
     if (wo && !tmap_for(c, wo, 2, (uint64_t)kC, (uint64_t)kC, 1, 64, kC, &mo)) return;
     FfnArgs g;
-    g.B = c.B; g.T = T; g.tiles_per_sample = (T + kFfM - 1) / kFfM;
+    g.B = c.B; g.T = T; g.spp = slabs_per_sample(T, false);
     g.b1 = b1; g.b2 = b2; g.res = res; g.out_f32 = out_f32; g.out_b16 = out_b16;
     g.omask = omask ? c.mask : nullptr; g.omask_T = c.T; g.debug = c.debug; g.o16_scale = o_stream ? stream_down(c) : 1.0f;
     g.ln_in = ln_in; g.ln_g = ln_g; g.ln_b = ln_b; g.bo = bo;
     if ((long long)c.B * T * kC >= 0x7fffffffLL) { c.err = MB200_ERR_UNSUPPORTED; return; }
-    const int grid = c.B * g.tiles_per_sample;
+    const int grid = (c.B * g.spp + 3) / 4;
     if (wo) {
         if (!bo || !ln_g || !ln_b || !res) { c.err = MB200_ERR_INVALID_ARG; return; }
         if (c.f16) launch(c, ffn_fused_kernel<true, true>, grid, kFfThreads, kFfSmemBytes, ma, m1, m2, mo, g);

@@ -42,7 +42,7 @@ constexpr int kFfThreads = 32 * (2 + kFfEpiWarps);
 constexpr int kFfEpiPitch = 36;                               // floats, final-epilogue transpose tiles (in the A/H region)
 
 struct FfnArgs {
-    int B, T, tiles_per_sample;
+    int B, T, spp;                     // spp: 32-row slabs per sample (gemm_bf16.cuh::slab_coords); CTA i owns slabs 4i .. 4i+3
     const float *bo;                   // OUTPROJ: to_out[0] bias [256]; res is then the block's input stream x1
     const float *b1, *b2;              // [1024], [256]
     const float *res;                  // fp32 [B][T][256]
@@ -100,7 +100,6 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     volatile uint32_t *tmem_slot_p = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_slot - base));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.x / g.tiles_per_sample, t0 = (blockIdx.x - b * g.tiles_per_sample) * kFfM;
 
     if (threadIdx.x == 0) {
         mbar_init(bar_a, (OUTPROJ || g.ln_in) ? (uint32_t)kFfEpiWarps : 1u); mbar_init(bar_a2f, 1u);
@@ -130,6 +129,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (warp == 0) {
         // ============================ TMA producer ============================
         if (lane == 0) {
+            int sb_[4], st_[4];                               // the tile's four slabs: sample, first frame
+#pragma unroll
+            for (int i = 0; i < 4; ++i) slab_coords(4 * (int)blockIdx.x + i, g.spp, g.B, g.T, sb_[i], st_[i]);
             uint32_t it = 0;
             auto stage_w1 = [&](int c, int half) {            // W1 rows [128c, 128c+128), k in [128 half, 128 half + 128)
                 const uint32_t s = it % kFfStages;
@@ -159,7 +161,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 stage_wo(0); stage_wo(1); stage_wo(2);
                 pdl_wait();
                 mbar_arrive_expect_tx(bar_att, 4 * kFfKb);
-                for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_att, kb * 64, t0, b);
+                for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) tma_load_3d(base + kFfOffA + kb * kFfKb + 4096u * i, &tmA, bar_att, kb * 64, st_[i], sb_[i]);
                 stage_wo(3);
                 stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
             } else {
@@ -167,7 +171,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 pdl_wait();
                 if (!g.ln_in) {
                     mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
-                    for (int kb = 0; kb < 4; ++kb) tma_load_3d(base + kFfOffA + kb * kFfKb, &tmA, bar_a, kb * 64, t0, b);
+                    for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) tma_load_3d(base + kFfOffA + kb * kFfKb + 4096u * i, &tmA, bar_a, kb * 64, st_[i], sb_[i]);
                 }
             }
             stage_w1(1, 1);
@@ -252,11 +258,13 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int cg = ew >> 2;                              // column group
         const int row = 32 * q + lane;                       // tile row = TMEM lane
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
+        int b, tq;                                           // this warp's lane quarter = slab q of the tile
+        slab_coords(4 * (int)blockIdx.x + q, g.spp, g.B, g.T, b, tq);
         if (OUTPROJ) {
             // ---- x2 = att Wo^T + bo + x1 (back into acc2), then A = LayerNorm(x2): thread = row, columns [64 cg, +64)
             pdl_wait();
-            const bool ok = t0 + row < g.T;
-            const float *x1p = g.res + ((size_t)b * g.T + (ok ? t0 + row : 0)) * kC + cg * 64;
+            const bool ok = tq + lane < g.T;
+            const float *x1p = g.res + ((size_t)b * g.T + (ok ? tq + lane : 0)) * kC + cg * 64;
             float4 rv[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) rv[i] = ok ? *reinterpret_cast<const float4 *>(x1p + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -342,6 +350,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // ---- A = LayerNorm(256, eps 1e-5) of the tile's rows, one warp per row (8 rows per warp, 4 in flight),
             //      written 16-bit into the four 128B-swizzled K-blocks the UMMA descriptors expect
             pdl_wait();
+            int rb, rt0;                                      // warp ew builds tile rows [8 ew, 8 ew + 8): slab ew / 4
+            slab_coords(4 * (int)blockIdx.x + (ew >> 2), g.spp, g.B, g.T, rb, rt0);
             const float4 lg0 = *reinterpret_cast<const float4 *>(g.ln_g + lane * 4), lg1 = *reinterpret_cast<const float4 *>(g.ln_g + 128 + lane * 4);
             const float4 lb0 = *reinterpret_cast<const float4 *>(g.ln_b + lane * 4), lb1 = *reinterpret_cast<const float4 *>(g.ln_b + 128 + lane * 4);
 #pragma unroll
@@ -350,8 +360,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int r = ew * 8 + half * 4 + j;
-                    const bool ok = t0 + r < g.T;
-                    const float *px = g.ln_in + ((size_t)b * g.T + t0 + r) * kC;
+                    const int rt = rt0 + (r & 31);
+                    const bool ok = rt < g.T;
+                    const float *px = g.ln_in + ((size_t)rb * g.T + (ok ? rt : 0)) * kC;
                     xa[j] = ok ? *reinterpret_cast<const float4 *>(px + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
                     xb[j] = ok ? *reinterpret_cast<const float4 *>(px + 128 + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
@@ -370,7 +381,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) qq += __shfl_xor_sync(0xffffffffu, qq, o);
                     const float rstd = rsqrtf(qq * (1.0f / kC) + 1e-5f);
-                    const bool ok = t0 + r < g.T;             // rows beyond T are zeros, as the TMA path delivers them
+                    const bool ok = rt0 + (r & 31) < g.T;   // rows beyond T are zeros, as the TMA path delivers them
                     const uint32_t p0 = ok ? pack16x2(d[0] * rstd * lg0.x + lb0.x, d[1] * rstd * lg0.y + lb0.y, F16) : 0u;
                     const uint32_t p1 = ok ? pack16x2(d[2] * rstd * lg0.z + lb0.z, d[3] * rstd * lg0.w + lb0.w, F16) : 0u;
                     const uint32_t p2 = ok ? pack16x2(d[4] * rstd * lg1.x + lb1.x, d[5] * rstd * lg1.y + lb1.y, F16) : 0u;
@@ -441,7 +452,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         float mk[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const int t = t0 + 32 * q + 4 * i + rsub;
+            const int t = tq + 4 * i + rsub;
             const bool ok = t < g.T;
             orow[i] = ok ? (int)(((long long)b * g.T + t) * kC) : -1;
             mk[i] = g.o16_scale * ((ok && g.omask) ? g.omask[(size_t)b * g.omask_T + t] : 1.0f);

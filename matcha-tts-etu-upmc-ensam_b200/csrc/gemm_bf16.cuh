@@ -35,7 +35,8 @@ constexpr int kGSmemBytes = kGStages * kGStageBytes + kGEpiBytes + kGBiasBytes +
 constexpr int kGThreads = 32 * (2 + kGEpiWarps);
 
 struct GemmBf16Args {
-    int B, Tout, tiles_per_sample;
+    int B, Tout;
+    int spp, n_mtiles;                 // 32-row slabs per sample and M tiles of the launch (slab_coords below)
     int ntaps, tap_off[4];
     int c0_chunks, c1_chunks;          // 64-channel chunks of source 0 / source 1 (concat)
     const float *bias;                 // [N] or nullptr
@@ -67,6 +68,17 @@ struct GemmBf16Args {
     const float *bias2;
     float *out2_f32;
 };
+
+// M tiling.  The rows of a launch are cut into 32-row SLABS: sample b owns slabs [b spp, (b + 1) spp), slab s of a sample covers
+// frames [32 s, 32 s + 32), and an M tile of 128 rows is any four consecutive slabs -- it may straddle samples, so a launch has
+// ceil(B spp / 4) tiles instead of B ceil(T / 128) (T = 400: 13 slabs = 3.25 tiles per sample instead of 4).  A slab is one
+// 32-row TMA box (rows beyond T come back as zeros: the conv padding), one TMEM lane quarter, one epilogue warp's rows; nothing
+// in memory changes.  Slabs past the last sample map to rows beyond T of sample 0: loads give zeros, stores are clipped.
+__device__ __forceinline__ void slab_coords(int slab, int spp, int B, int T, int &b, int &t0) {
+    b = slab / spp;
+    t0 = (slab - b * spp) * 32;
+    if (b >= B) { b = 0; t0 = T + 64; }
+}
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
     asm volatile(
@@ -168,7 +180,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     const int chunks = g.c0_chunks + g.c1_chunks;
     const int n_kb = g.ntaps * chunks;
     const int n_tiles_n = g.N / kGN;
-    const int n_mtiles = g.B * g.tiles_per_sample;
+    const int n_mtiles = g.n_mtiles;
     const int n_tiles = n_mtiles * n_tiles_n;
     auto tile_coords = [&](int tile, int &mt, int &n0) {
         if (g.n_split) { const int nt = tile / n_mtiles; mt = tile - nt * n_mtiles; n0 = nt * kGN; }     // N-major
@@ -203,7 +215,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 int mt, n0;
                 tile_coords(tile, mt, n0);
-                const int b = mt / g.tiles_per_sample, t0 = (mt - b * g.tiles_per_sample) * kGM;
+                int sb_[4], st_[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) slab_coords(4 * mt + i, g.spp, g.B, g.Tout, sb_[i], st_[i]);
                 const bool light = g.n_split && n0 >= g.n_split;
                 const int kb_lo = light ? g.kb2_begin : 0, kb_hi = light ? g.kb2_begin + g.kb2_count : n_kb;
                 for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
@@ -212,8 +226,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const int tap = kb / chunks, ch = kb - tap * chunks;
                     const uint32_t sa = base + s * kGStageBytes, sb = sa + kGStageA;
                     mbar_arrive_expect_tx(bar_full + 8u * s, kGStageBytes);
-                    if (ch < g.c0_chunks) tma_load_3d(sa, &tmA0, bar_full + 8u * s, ch * kGK, t0 + g.tap_off[tap], b);
-                    else tma_load_3d(sa, &tmA1, bar_full + 8u * s, (ch - g.c0_chunks) * kGK, t0 + g.tap_off[tap], b);
+                    const CUtensorMap *const am = ch < g.c0_chunks ? &tmA0 : &tmA1;
+                    const int ck = (ch < g.c0_chunks ? ch : ch - g.c0_chunks) * kGK;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)           // four 32-row boxes, one per slab (4 KB apart: whole swizzle atoms)
+                        tma_load_3d(sa + 4096u * i, am, bar_full + 8u * s, ck, st_[i] + g.tap_off[tap], sb_[i]);
                     tma_load_2d(sb, &tmB, bar_full + 8u * s, kb * kGK, n0);
                 }
             }
@@ -272,7 +289,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
             int mt, n0;
             tile_coords(tile, mt, n0);
-            const int b = mt / g.tiles_per_sample, t0 = (mt - b * g.tiles_per_sample) * kGM;
+            int b, trow0;                                             // this warp's slab: sample and first frame
+            slab_coords(4 * mt + q, g.spp, g.B, g.Tout, b, trow0);
             const bool light = g.n_split && n0 >= g.n_split;
             const int ldo = g.n_split ? g.n_split : g.N;              // output row pitch
             const int ncol0 = light ? n0 - g.n_split : n0;             // column of the tile in its output block
@@ -280,7 +298,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const float *const biasp = light ? g.bias2 : g.bias;
             const uint32_t acc = lt & 1;
             const uint32_t tacc = tmem_d + acc * kGN + ((uint32_t)(32 * q) << 16);
-            const int trow0 = t0 + 32 * q;
             mbar_wait_parked(bar_tfull + 8u * acc, (lt >> 1) & 1, 2000);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (dbg && lt == 0 && threadIdx.x == 64) g_gemm_dbg[2] = clock64();

@@ -9,7 +9,7 @@ lib = load_library()
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
 for mode in (1, 2):
-    for B, T in [(32, 400), (32, 800)]:
+    for B, T in ([(int(os.environ['AB_B']), int(os.environ['AB_T']))] if 'AB_B' in os.environ else [(32, 400), (32, 800)]):
         h = torch.randn(B, T, 256, device="cuda")
         g4 = h.double().view(B, T, 8, 32)
         gs = torch.stack([g4.sum((1, 3)), (g4 * g4).sum((1, 3))], -1).contiguous()

@@ -8,7 +8,7 @@ from matcha_b200._lib import check, load_library
 lib = load_library()
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
-for B, T in [(8, 800), (32, 800), (8, 400)]:
+for B, T in ([(8, int(os.environ['FB_T']))] if 'FB_T' in os.environ else [(8, 800), (32, 800), (8, 400)]):
     att = torch.randn(B, T, 256, device="cuda").half()
     wo = (torch.randn(256, 256, device="cuda") * 0.09).half()
     w1 = (torch.randn(1024, 256, device="cuda") * 0.09).half()
