@@ -313,11 +313,12 @@ static GemmKernel pick_gemm(int epi, int flags, bool f16) {
         case 1 * 16 + kGB16: return gemm_variant<1, kGB16>(f16);                          // FFN1 + erf-GELU
         case 1 * 16 + (kGF32 | kGB16 | kGRes): return gemm_variant<1, kGF32 | kGB16 | kGRes>(f16);   // tests only
         case 2 * 16 + 0: return gemm_variant<2, 0>(f16);                                  // final_proj + Euler update
+        case 3 * 16 + 0: return gemm_variant<3, 0>(f16);                                  // final_proj + loss sums (compute_loss)
     }
     return nullptr;
 }
 static int gemm_set_attributes() {
-    for (int epi = 0; epi < 3; ++epi)
+    for (int epi = 0; epi < 4; ++epi)
         for (int flags = 0; flags < 16; ++flags)
             for (int f16 = 0; f16 < 2; ++f16) {
                 const GemmKernel k = pick_gemm(epi, flags, f16 != 0);
@@ -389,7 +390,7 @@ static void gemm_b(Ctx &c, int sflags, const bf16 *a0, int c0, const bf16 *a1, i
     g.gstats = gstats;
     g.n_split = out2_f32 ? N / 2 : 0; g.kb2_begin = kb2_begin; g.kb2_count = kb2_count; g.bias2 = bias2; g.out2_f32 = out2_f32;
     const int flags = (res ? kGRes : 0) | (out_f32 ? kGF32 : 0) | (out_b16 ? kGB16 : 0) | (gstats ? kGStats : 0);
-    const GemmKernel k = pick_gemm(g.fin_n > 0 ? 2 : act, g.fin_n > 0 ? 0 : flags, c.f16 != 0);
+    const GemmKernel k = pick_gemm(g.fin_n > 0 ? (c.fin_loss ? 3 : 2) : act, g.fin_n > 0 ? 0 : flags, c.f16 != 0);
     if (!k) { c.err = MB200_ERR_UNSUPPORTED; return; }
     // TMA-store epilogue (one output, no residual): output tensor maps
     CUtensorMap mo = ma0, mo2 = ma0;

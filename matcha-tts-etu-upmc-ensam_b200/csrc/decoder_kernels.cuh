@@ -94,22 +94,47 @@ time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict
     }
     __syncthreads();
     const int warp = tid >> 5, lane = tid & 31;
-    for (int o = warp; o < kTimeDim; o += 8) {                  // one warp per output, coalesced weight rows
-        const float *wr = w.w1 + (size_t)o * kInCh;
-        float acc = 0.f;
+    // One warp per output with coalesced weight rows, EIGHT outputs in flight per warp: a single dot product per iteration is
+    // an L2 round trip plus a shuffle tree (~0.7 us) -- 128 of them in a row made this kernel 113 us of every solve / forward.
+    for (int o0 = warp * 8; o0 < kTimeDim; o0 += 64) {
+        float acc[8];
 #pragma unroll
-        for (int i = 0; i < kInCh / 32; ++i) acc = fmaf(wr[lane + 32 * i], emb[lane + 32 * i], acc);
-        for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
-        if (lane == 0) h1[o] = silu_f(acc + w.b1[o]);
+        for (int j = 0; j < 8; ++j) {
+            const float *wr = w.w1 + (size_t)(o0 + j) * kInCh;
+            float a = 0.f;
+#pragma unroll
+            for (int i = 0; i < kInCh / 32; ++i) a = fmaf(wr[lane + 32 * i], emb[lane + 32 * i], a);
+            acc[j] = a;
+        }
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], s);
+        if (lane == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) h1[o0 + j] = silu_f(acc[j] + w.b1[o0 + j]);
+        }
     }
     __syncthreads();
-    for (int oo = warp; oo < 64; oo += 8) {                     // one warp per output, coalesced weight rows
-        const int o = blockIdx.y * 64 + oo;
-        const float *wr = w.w2 + (size_t)o * kTimeDim;
-        float acc = 0.f;
-        for (int i = lane; i < kTimeDim; i += 32) acc = fmaf(wr[i], h1[i], acc);
-        for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
-        if (lane == 0) h2[(size_t)row * kTimeDim + o] = mish_f(acc + w.b2[o]);   // Mish of Resnet1D.mlp[0]
+    {                                                           // this block's 64 outputs: 8 per warp, all in flight
+        const int o0 = blockIdx.y * 64 + warp * 8;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll 4
+        for (int i = lane; i < kTimeDim; i += 32) {
+            const float hv = h1[i];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = fmaf(w.w2[(size_t)(o0 + j) * kTimeDim + i], hv, acc[j]);
+        }
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], s);
+        if (lane == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) h2[(size_t)row * kTimeDim + o0 + j] = mish_f(acc[j] + w.b2[o0 + j]);   // Mish of Resnet1D.mlp[0]
+        }
     }
 }
 // step 2, grid (n_rows, 6 stages x 4): out_tb[stage][row][o] = Linear_stage(h2[row])[o], 64 outputs per block

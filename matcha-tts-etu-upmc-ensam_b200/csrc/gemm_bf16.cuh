@@ -152,7 +152,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) { t
 // profiling aid: clock64 stamps of CTA 0 (start, first stage landed, first accumulator ready, first tile stored)
 __device__ long long g_gemm_dbg[8];
 
-// EPI: 0 plain, 1 erf-GELU, 2 final projection; FLAGS: which of residual / fp32 output / 16-bit output exist;
+// EPI: 0 plain, 1 erf-GELU, 2 final projection, 3 final projection + squared-error sums (compute_loss); FLAGS: which of residual / fp32 output / 16-bit output exist;
 // F16: operand format.  All compile-time: the epilogue is issue-bound, a runtime "if (g.res)" costs slots.
 constexpr int kGRes = 1, kGF32 = 2, kGB16 = 4, kGStats = 8;
 template <int EPI, int FLAGS, bool F16>
@@ -163,7 +163,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     constexpr bool RES = (FLAGS & kGRes) != 0, F32 = (FLAGS & kGF32) != 0, B16 = (FLAGS & kGB16) != 0, STATS = (FLAGS & kGStats) != 0;
     // Variants with exactly one output and no residual stay in the TMEM layout (thread = row) and leave through
     // 128B/64B-swizzled staging tiles and TMA stores; the others transpose through shared memory (below).
-    constexpr bool TMA_EPI = EPI != 2 && !RES && (F32 != B16);
+    constexpr bool FIN = EPI == 2 || EPI == 3;        // final projection; 3 = the loss variant (flow_matching.py:142-148)
+    constexpr bool LOSS = EPI == 3;
+    constexpr bool TMA_EPI = !FIN && !RES && (F32 != B16);
     extern __shared__ uint8_t gsm_raw[];
     const uint32_t base = (smem_u32(gsm_raw) + 1023u) & ~1023u;
     uint8_t *gbase = gsm_raw + (base - smem_u32(gsm_raw));
@@ -374,7 +376,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     }
                     ++n_st;
                 }
-            } else if (EPI == 2) {
+            } else if (FIN) {
                 // lane = frame t: for a fixed channel the warp writes 32 consecutive frames (coalesced, no transpose)
                 const int t = trow0 + lane;
                 const float mk = t < g.Tout ? g.omask[(size_t)b * g.omask_T + t] : 0.f;
@@ -385,11 +387,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {              // all loads of the chunk first
                         const int n = 32 * j + i;
-                        const bool ok = n < g.fin_n && t < g.Tout;
-                        const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
-                        xin[i] = 0.f;
-                        if (g.loss_sum) { if (ok) xin[i] = __fsub_rn(g.loss_x1[o], __fmul_rn(g.loss_oms, g.loss_z[o])); }
-                        else if (g.fin_xin && ok) xin[i] = g.fin_xin[o];
+                        if (LOSS) {                             // the regression target u = x1 - (1 - sigma) z, not masked
+                            const bool ok = n < g.fin_n && t < g.Tout;
+                            const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
+                            xin[i] = ok ? __fsub_rn(g.loss_x1[o], __fmul_rn(g.loss_oms, g.loss_z[o])) : 0.f;
+                        } else {
+                            xin[i] = (g.fin_xin && n < g.fin_n && t < g.Tout) ? g.fin_xin[((size_t)b * g.fin_n + n) * g.Tout + t] : 0.f;
+                        }
                     }
                     tmem_ld32(tacc + 32 * j, v);
 #pragma unroll
@@ -397,18 +401,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         const int n = 32 * j + i;
                         if (n < g.fin_n && t < g.Tout) {
                             const float vel = (__uint_as_float(v[i]) + g.bias[n]) * mk;
-                            const size_t o = ((size_t)b * g.fin_n + n) * g.Tout + t;
-                            if (g.loss_sum) {
+                            if (LOSS) {
                                 const float d = __fsub_rn(vel, xin[i]);
                                 lsum = fmaf(d, d, lsum);
-                                if (g.fin_out) g.fin_out[o] = vel;
+                                if (g.fin_out) g.fin_out[((size_t)b * g.fin_n + n) * g.Tout + t] = vel;
                             } else {
-                                g.fin_out[o] = g.fin_xin ? __fadd_rn(xin[i], __fmul_rn(g.fin_dt, vel)) : vel;
+                                g.fin_out[((size_t)b * g.fin_n + n) * g.Tout + t] = g.fin_xin ? __fadd_rn(xin[i], __fmul_rn(g.fin_dt, vel)) : vel;
                             }
                         }
                     }
                 }
-                if (g.loss_sum && jhalf * 32 < g.fin_n) {
+                if (LOSS && jhalf * 32 < g.fin_n) {
                     double ds = (double)lsum;
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
@@ -504,7 +507,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     if (dbg && lt == 0 && threadIdx.x == 64 && jj == 0) g_gemm_dbg[7] = clock64();
                 }
             }
-            if (EPI == 2) {
+            if (FIN) {
                 // this warp's TMEM reads are complete (tcgen05.wait::ld): hand the accumulator back to the MMA warp
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
