@@ -663,9 +663,12 @@ extern "C" long long matcha_b200_decoder_blob_bf16_bytes(void) { return build_we
 // chain leaves idle (wave quantisation, launch gaps, single-tile pipelines).  MB200_SPLIT=1 turns it off.
 constexpr int kMaxSplit = 8;
 static int solve_split(int B) {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("MB200_SPLIT"); v = e ? atoi(e) : 4; if (v < 1) v = 1; if (v > kMaxSplit) v = kMaxSplit; }
+    static int v = -1, forced = 0;
+    if (v < 0) { const char *e = getenv("MB200_SPLIT"); forced = e != nullptr; v = e ? atoi(e) : 4; if (v < 1) v = 1; if (v > kMaxSplit) v = kMaxSplit; }
     int s = v;
+    // from B = 64 on two chains already fill the machine and more only add contention (B = 64, T = 800, n = 10: 15.9 / 16.0 / 16.3 /
+    // 16.4 ms with 2 / 3 / 4 / 8; B = 32: 9.19 / 9.00 / 9.00 / 8.95; B = 16: no difference -- profiles/r2_split_sweep.log)
+    if (!forced && B >= 48 && s > 2) s = 2;
     while (s > 1 && B < 4 * s) --s;             // small batches stay whole
     return s;
 }
