@@ -90,6 +90,13 @@ def load_library():
     lib.matcha_b200_cfm_solve_euler.restype = c_int
     lib.matcha_b200_cfm_solve_euler.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                                 c_void_p, c_void_p, c_void_p, ll, c_int, c_int, c_int, c_void_p]
+    lib.matcha_b200_text_encoder_blob_floats.restype = ll
+    lib.matcha_b200_text_encoder_blob_floats.argtypes = [c_int]
+    lib.matcha_b200_text_encoder_workspace_bytes.restype = ll
+    lib.matcha_b200_text_encoder_workspace_bytes.argtypes = [c_int, c_int]
+    lib.matcha_b200_text_encoder_forward.restype = c_int
+    lib.matcha_b200_text_encoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                     c_void_p, c_int, c_int, c_void_p, ll, c_void_p]
     lib.matcha_b200_debug_attention.restype = c_int
     lib.matcha_b200_debug_attention.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]
     lib.matcha_b200_debug_gemm_bf16.restype = c_int
@@ -131,4 +138,7 @@ DECLARED_SYMBOLS = (
     "matcha_b200_decoder_forward",
     "matcha_b200_cfm_loss_forward",
     "matcha_b200_cfm_solve_euler",
+    "matcha_b200_text_encoder_blob_floats",
+    "matcha_b200_text_encoder_workspace_bytes",
+    "matcha_b200_text_encoder_forward",
 )

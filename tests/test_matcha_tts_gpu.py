@@ -1,0 +1,90 @@
+"""GPU tests of the assembled flows (matcha_b200.matcha_tts.MatchaTTS): synthesise and the training-step forward values
+against the torch restatements composed the way matcha_tts.py composes the reference modules."""
+import math
+
+import pytest
+import torch
+
+from oracle import alignment as oal
+from oracle import decoder as odec
+from oracle import text_encoder as oenc
+
+pytestmark = pytest.mark.gpu
+N_VOCAB = 178
+
+
+def rel_l2(a, b):
+    return float(torch.linalg.norm((a.double().cpu() - b.double().cpu())) / torch.linalg.norm(b.double().cpu()))
+
+
+@pytest.fixture(scope="module")
+def weights():
+    return oenc.make_weights(41, "rich", N_VOCAB), odec.make_weights(42, "rich")
+
+
+def build(weights, precision):
+    from matcha_b200.matcha_tts import MatchaTTS
+    we, wd = weights
+    sd = {"encoder." + k: v for k, v in we.items()}
+    sd.update({"decoder.estimator." + k: v for k, v in wd.items()})
+    return MatchaTTS(N_VOCAB, precision=precision).load_state_dict(sd)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-5), ("fp16", 2e-3)])
+def test_synthesise_matches_oracle_composition(weights, precision, tol):
+    """matcha_tts.py:212-249 with the same noise: the CUDA path draws z with torch.randn_like on the device, so the oracle
+    re-draws it from the same seed."""
+    we, wd = weights
+    model = build(weights, precision)
+    g = torch.Generator().manual_seed(1)
+    B, T = 3, 24
+    x = torch.randint(0, N_VOCAB, (B, T), generator=g)
+    x_lengths = torch.tensor([24, 17, 9])
+    torch.manual_seed(77)
+    out = model.synthesise(x.cuda(), x_lengths.cuda(), n_timesteps=3, temperature=0.667, length_scale=1.1)
+    # oracle: encoder -> durations -> generate_path -> mu_y -> Euler solve (fp32 on the CPU)
+    mu_x, logw, x_mask = oenc.text_encoder_forward(we, x, x_lengths)
+    w_ceil = torch.ceil(torch.exp(logw) * x_mask) * 1.1
+    y_lengths = torch.clamp_min(torch.sum(w_ceil, [1, 2]), 1).long()
+    y_max = int(y_lengths.max())
+    T_y = oal.fix_len_compatibility(y_max)
+    y_mask = oal.sequence_mask(y_lengths, T_y).unsqueeze(1).float()
+    attn = oal.generate_path(w_ceil.squeeze(1), (x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)).squeeze(1))
+    mu_y = torch.matmul(attn.transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+    # the durations come from ceil(exp(logw)): a 1e-6 difference in logw can move one of them across an integer, so the
+    # mel lengths are compared first and the rest only makes sense when they agree (they do for this seed)
+    assert torch.equal(out["mel_lengths"].cpu(), y_lengths)
+    assert out["encoder_outputs"].shape == (B, 80, y_max)
+    assert rel_l2(out["encoder_outputs"], mu_y[:, :, :y_max]) < 1e-5
+    torch.manual_seed(77)
+    z = (torch.randn(B, 80, T_y, device="cuda") * 0.667).cpu()
+    want = odec.solve_euler(wd, z, torch.linspace(0, 1, 4), mu_y, y_mask)[:, :, :y_max]
+    assert rel_l2(out["decoder_outputs"], want) < tol
+    assert torch.equal(out["mel"], out["decoder_outputs"])               # mel_mean 0, mel_std 1
+    assert out["attn"].shape[0] == B and out["attn"].shape[1] == 1
+
+
+def test_training_forward_values_match_oracle_composition(weights):
+    """matcha_tts.py:271-322 (no out_size): encoder -> log-prior -> MAS -> logw_ / mu_y -> the three losses."""
+    we, wd = weights
+    model = build(weights, "fp32")
+    g = torch.Generator().manual_seed(2)
+    B, T_x, T_y = 3, 20, 96
+    x = torch.randint(0, N_VOCAB, (B, T_x), generator=g)
+    x_lengths, y_lengths = torch.tensor([20, 15, 11]), torch.tensor([96, 80, 61])
+    y = torch.randn(B, 80, T_y, generator=g)
+    t, z = torch.rand(B, 1, 1, generator=g), torch.randn(B, 80, T_y, generator=g)
+    dur, prior, diff, attn = model(x.cuda(), x_lengths.cuda(), y.cuda(), y_lengths.cuda(), t=t.cuda(), z=z.cuda())
+    mu_x, logw, x_mask = oenc.text_encoder_forward(we, x, x_lengths)
+    y_mask = oal.sequence_mask(y_lengths, T_y).unsqueeze(1).float()
+    lp = oal.log_prior(mu_x, y)
+    oattn = oal.maximum_path(lp, (x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)).squeeze(1))
+    assert torch.equal(attn.cpu(), oattn)                                # same path although mu_x differs by ~1e-6
+    logw_ = torch.log(1e-8 + torch.sum(oattn.unsqueeze(1), -1)) * x_mask
+    odur = torch.sum((logw - logw_) ** 2) / torch.sum(x_lengths)
+    mu_y = torch.matmul(oattn.transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+    oprior = torch.sum(0.5 * ((y - mu_y) ** 2 + math.log(2 * math.pi)) * y_mask) / (torch.sum(y_mask) * 80)
+    odiff, _ = odec.compute_loss(wd, y, y_mask, mu_y, t, z)
+    assert abs(float(dur) - float(odur)) < 1e-5 * abs(float(odur))
+    assert abs(float(prior) - float(oprior)) < 1e-5 * abs(float(oprior))
+    assert abs(float(diff) - float(odiff)) < 2e-5 * abs(float(odiff))
