@@ -41,8 +41,7 @@ template <bool F16>
 __global__ void __launch_bounds__(128)
 attention_mma_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict__ mask, int mask_T,
                      __nv_bfloat16 *__restrict__ out, int T) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     extern __shared__ __align__(128) uint8_t fa_smem[];
     const uint32_t sQ = smem_u32(fa_smem);
     const uint32_t sKV = sQ + kFaBQ * 128;                  // [buf][K|V][64 rows][128 B]

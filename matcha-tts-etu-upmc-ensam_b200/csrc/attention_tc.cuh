@@ -116,8 +116,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot_p;
     const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
 
     if (warp == 0) {
         // ============================ TMA producer ============================

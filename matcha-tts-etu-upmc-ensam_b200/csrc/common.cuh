@@ -144,6 +144,40 @@ __device__ __forceinline__ bool elect_one() {
 // Both are no-ops for a normal launch.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Order of the two.  MB200_PDL_SAFE = 0 (decoder default): trigger first, so every kernel of a chain may be resident and
+// waiting while an earlier one still runs.  griddepcontrol.wait orders a kernel after its prerequisite grid (and, through that
+// grid's own wait, after everything before it), but it only promises VISIBILITY of the prerequisite grid's writes: a CTA that
+// was made resident while kernel N still ran can find, in its SM's L1, a line kernel N read there and kernel N+1 or N+2 has
+// since rewritten.  The text encoder's small kernels hit exactly that on two of six boxes (profiles/r2_te_pdl_race.log) and
+// therefore use the other order plus ld.global.cg loads (csrc/text_encoder.cu).  The decoder's chain is protected by its
+// shape: the kernels that read a re-written buffer with plain loads (A-building GEMMs, fused feed-forward) own their SM's
+// shared memory (~200 KB), so a waiting successor and the earlier reader are never on the same SM, and every other operand
+// arrives by TMA (L2).  MB200_PDL_SAFE = 1 compiles the conservative order into the decoder kernels too: a CTA lets the
+// successor be scheduled only after its own wait has returned (at most two grids of a chain in flight).  Measured on one box
+// (profiles/r2_pdl_order_ab.log): B=32 solve 8.97 -> 9.25 ms (+3 %), B=8 6.61 -> 6.27 ms (-5 %), B=64 15.84 -> 15.73 ms.
+#ifndef MB200_PDL_SAFE
+#define MB200_PDL_SAFE 0
+#endif
+__device__ __forceinline__ void pdl_entry() {            // kernels whose every thread waits at the top
+#if MB200_PDL_SAFE
+    pdl_wait();
+    pdl_launch_dependents();
+#else
+    pdl_launch_dependents();
+    pdl_wait();
+#endif
+}
+__device__ __forceinline__ void pdl_trigger_at_top() {   // kernels that wait later, per warp role (weights are fetched first)
+#if !MB200_PDL_SAFE
+    pdl_launch_dependents();
+#endif
+}
+__device__ __forceinline__ void pdl_wait_then_trigger() {   // the first wait of such a kernel's data-dependent warps
+    pdl_wait();
+#if MB200_PDL_SAFE
+    pdl_launch_dependents();
+#endif
+}
 
 #endif  // __CUDACC__
 }  // namespace mb200

@@ -623,8 +623,7 @@ using namespace mb200;
 namespace {
 struct TimeVals { float v[64]; };
 __global__ void stage_times_kernel(TimeVals tv, int n, float *out) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     if (threadIdx.x < n) out[threadIdx.x] = tv.v[threadIdx.x];
 }
 

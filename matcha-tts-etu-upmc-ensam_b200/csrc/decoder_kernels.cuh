@@ -81,8 +81,7 @@ struct TimeWeights {
 // step 1, grid (n_rows, 16): h2[row][o] = Mish(W2 SiLU(W1 emb(t[row]) + b1) + b2)[o] for 64 outputs per block
 __global__ void __launch_bounds__(256)
 time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict__ h2) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     __shared__ float emb[kInCh];
     __shared__ float h1[kTimeDim];
     const int row = blockIdx.x, tid = threadIdx.x;
@@ -140,8 +139,7 @@ time_embed1_kernel(TimeWeights w, const float *__restrict__ t, float *__restrict
 // step 2, grid (n_rows, 6 stages x 4): out_tb[stage][row][o] = Linear_stage(h2[row])[o], 64 outputs per block
 __global__ void __launch_bounds__(256)
 time_embed2_kernel(TimeWeights w, const float *__restrict__ h2, int n_rows, float *__restrict__ out_tb) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     __shared__ float hs[kTimeDim];
     const int row = blockIdx.x, st = blockIdx.y >> 2, part = blockIdx.y & 3, tid = threadIdx.x;
     for (int i = tid; i < kTimeDim; i += 256) hs[i] = h2[(size_t)row * kTimeDim + i];
@@ -162,8 +160,7 @@ time_embed2_kernel(TimeWeights w, const float *__restrict__ h2, int n_rows, floa
 __global__ void __launch_bounds__(256)
 pack_input_kernel(const float *__restrict__ x, const float *__restrict__ mu, float *__restrict__ out,
                   int B, int T) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     __shared__ float tile[32][33];
     const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 160 channels
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;                  // 32 x 8
@@ -207,8 +204,7 @@ constexpr int kBM = 128, kBN = 64, kBK = 16;
 
 __global__ void __launch_bounds__(256)
 gemm_f32_kernel(const GemmArgs g) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     __shared__ __align__(16) float As[kBK][kBM + 4];
     __shared__ __align__(16) float Bs[kBK][kBN + 4];
     const int tid = threadIdx.x;
@@ -314,8 +310,7 @@ gemm_f32_kernel(const GemmArgs g) {
 // the statistics run over the full padded T).
 __global__ void __launch_bounds__(256)
 gn_stats_kernel(const float *__restrict__ h, int T, float *__restrict__ stats) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     const int b = blockIdx.x / kGroups, grp = blockIdx.x % kGroups;
     const float *p = h + (size_t)b * T * kC + grp * kGroupCh;
     double s = 0.0, ss = 0.0;
@@ -351,8 +346,7 @@ gn_mish_kernel(const float *__restrict__ h, const float *__restrict__ stats, con
                const float *__restrict__ beta, const float *__restrict__ mask, int mask_T,
                const float *__restrict__ tb, int tb_per_sample, float *__restrict__ out,
                __nv_bfloat16 *__restrict__ out_bf16, int f16, int fast, int B, int T, const double *__restrict__ gsum) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     const size_t n4 = (size_t)B * T * (kC / 4);
     const double inv_n = 1.0 / ((double)T * kGroupCh);
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
@@ -411,8 +405,7 @@ gn_mish_rows_kernel(const float *__restrict__ h, const double *__restrict__ gsum
                     const float *__restrict__ ln_g, const float *__restrict__ ln_b, float *__restrict__ out_f32,
                     __nv_bfloat16 *__restrict__ out16, int f16, int B, int T) {
     __shared__ float s_stat[kGmRowsPerBlock][kGroups][2];
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     const size_t rows = (size_t)B * T;
     const size_t r0 = (size_t)blockIdx.x * kGmRowsPerBlock;
     const int b0 = (int)(r0 / T);
@@ -509,8 +502,7 @@ gn_mish_rows_kernel(const float *__restrict__ h, const double *__restrict__ gsum
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta,
                  float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int f16, size_t rows) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     const int lane = threadIdx.x & 31;
     const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -550,8 +542,7 @@ constexpr int kAttSmemBytes = (2 * kAttBK * kAttPitch + kAttBQ * kAttPitch) * 4;
 __global__ void __launch_bounds__(128)
 attention_f32_kernel(const float *__restrict__ qkv, const float *__restrict__ mask, int mask_T,
                      float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, int f16, int T) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     extern __shared__ __align__(16) float att_smem[];
     float (*Ks)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem);
     float (*Vs)[kAttPitch] = reinterpret_cast<float (*)[kAttPitch]>(att_smem + kAttBK * kAttPitch);
@@ -650,8 +641,7 @@ final_proj_kernel(const float *__restrict__ hf, const float *__restrict__ stats,
                   const float *__restrict__ beta, const float *__restrict__ mask, const float *__restrict__ wp,
                   const float *__restrict__ bp, const float *__restrict__ x_in, float dt,
                   float *__restrict__ out, int T) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     __shared__ float A[32][kC + 1];
     const int b = blockIdx.y, t0 = blockIdx.x * 32, tid = threadIdx.x;
     for (int i = tid; i < 32 * kC; i += 256) {
@@ -693,8 +683,7 @@ __global__ void __launch_bounds__(256)
 pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu, const float *__restrict__ mask,
                        __nv_bfloat16 *__restrict__ out, int f16, float scale, int B, int T, double *__restrict__ gstats, int n_gstats,
                        const PackLoss loss) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     __shared__ float tile[32][33];
     const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 192 channels
     if (blockIdx.x == 0 && blockIdx.y == 0)        // first kernel of an eval: clear the GroupNorm accumulators of its 13 convs
@@ -735,8 +724,7 @@ pack_input_bf16_kernel(const float *__restrict__ x, const float *__restrict__ mu
 __global__ void __launch_bounds__(256)
 resample_mask_bf16_kernel(const float *__restrict__ in, int Tin, const float *__restrict__ mask,
                           __nv_bfloat16 *__restrict__ out, int f16, float o16_scale, int B, int T) {
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     const size_t n4 = (size_t)B * T * (kC / 4);
     const float scale = (float)Tin / (float)T;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {

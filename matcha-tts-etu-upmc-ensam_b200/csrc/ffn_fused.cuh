@@ -122,7 +122,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot_p;
     const uint32_t tmem_acc2 = tmem, tmem_acc1 = tmem + 256;
-    pdl_launch_dependents();
+    pdl_trigger_at_top();
     const bool dbg = g.debug && blockIdx.x == 0;
     if (dbg && threadIdx.x == 0) g_ffn_dbg[0] = clock64();
 
@@ -159,7 +159,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // the weights do not depend on the predecessor kernel: the first stages are in flight before the wait
             if (OUTPROJ) {
                 stage_wo(0); stage_wo(1); stage_wo(2);
-                pdl_wait();
+                pdl_wait_then_trigger();
                 mbar_arrive_expect_tx(bar_att, 4 * kFfKb);
                 for (int kb = 0; kb < 4; ++kb)
 #pragma unroll
@@ -168,7 +168,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
             } else {
                 stage_w1(0, 0); stage_w1(0, 1); stage_w1(1, 0);
-                pdl_wait();
+                pdl_wait_then_trigger();
                 if (!g.ln_in) {
                     mbar_arrive_expect_tx(bar_a, 4 * kFfKb);
                     for (int kb = 0; kb < 4; ++kb)

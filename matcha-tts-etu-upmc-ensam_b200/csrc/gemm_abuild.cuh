@@ -90,7 +90,7 @@ gemm_abuild_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot_p;
-    pdl_launch_dependents();
+    pdl_trigger_at_top();
 
     if (warp == 0) {
         // ============================ TMA producer: W K-blocks only ============================
@@ -154,7 +154,7 @@ gemm_abuild_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
         // this lane's two 16-bit destinations inside an A row: channels c0.. in K-block lane / 16, c1.. two K-blocks on
         const uint32_t a_dst0 = base + kAbOffA + (uint32_t)(lane >> 4) * kAbAKb + (uint32_t)(lane & 1) * 8u;
         const uint32_t a_piece = (uint32_t)((lane & 15) >> 1);
-        pdl_wait();                                          // h, gsum, r come from the predecessor kernels
+        pdl_wait_then_trigger();                             // h, gsum, r come from the predecessor kernels
         uint32_t lt = 0, ac = 0, n_st = 0;
         for (int tile = blockIdx.x; tile < n_mtiles; tile += gridDim.x, ++lt) {
             const int b = tile / g.tiles_per_sample, t0 = (tile - b * g.tiles_per_sample) * kGM;

@@ -205,8 +205,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot_p;
     // barriers, TMEM and descriptors are set up while the previous kernel of the stream drains
-    pdl_launch_dependents();
-    pdl_wait();
+    pdl_entry();
     const bool dbg = g.debug && blockIdx.x == 0;
     if (dbg && threadIdx.x == 0) g_gemm_dbg[0] = clock64();
 
