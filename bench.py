@@ -575,44 +575,130 @@ def decoder_gpu_baseline(weights, z, t_span, mu, mask, flops, modes):
     return res
 
 
+def text_encoder_leg(a, dev, world, rank, dist, barrier):
+    """SURVEY §8f-4 / BASELINE configs[3] "text-encoder mu_x": TextEncoder.forward (text_encoder.py:377-402) on a synthetic
+    LJSpeech-shaped batch (32 x T_text 128 per GPU, ragged 0.7-1.0), in both precisions, with the torch restatement of the
+    reference module timed on the same GPU (eager fp32 with TF32 off / on, bf16 autocast) and on the host cores."""
+    import torch
+    from matcha_b200.text_encoder import TextEncoder
+    from oracle import text_encoder as oenc            # the checker: rel-L2 of the kernels' outputs, and the baselines
+    B, T = a.dec_batch, 128
+    rng = np.random.default_rng(5000 + rank)
+    xl_h, _ = ragged_lengths(rng, B, T, 800)
+    g = torch.Generator(device=dev); g.manual_seed(5000 + rank)
+    ids = torch.randint(0, 178, (B, T), device=dev, generator=g)
+    xl = torch.from_numpy(xl_h).to(dev)
+    encs = {p: TextEncoder(n_vocab=178, precision=p).initialize_weights(seed=1) for p in ("fp32", "fp16")}
+    w32 = {k: v.to(dev) for k, v in encs["fp32"].state_dict().items()}
+    with torch.no_grad():
+        ref = oenc.text_encoder_forward(oenc.cast_weights(w32, torch.float64), ids, xl.long())
+
+    def rel(x, r):
+        return float(torch.linalg.norm(x.double() - r) / torch.linalg.norm(r))
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / n], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    modes = {}
+    for prec, enc in encs.items():
+        ms = timed(lambda: enc(ids, xl), 20)
+        mu, logw, _ = enc(ids, xl)
+        modes[prec] = {"ms_per_forward": ms, "tokens_per_sec": world * B * T / (ms / 1e3), "launches": int(enc.last_launches),
+                       "rel_l2_vs_oracle_fp64": {"mu": rel(mu, ref[0]), "logw": rel(logw, ref[1])}}
+    gpu_base = None
+    if not a.no_gpu_baseline and world == 1:
+        gpu_base = {"kind": "port", "what": "oracle/text_encoder.py (torch restatement of the reference module, pinned to it bit for bit) "
+                                           "in PyTorch eager on the same GPU"}
+        old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+        with torch.no_grad():
+            for name, tf32, ac in (("fp32", False, False), ("tf32", True, False), ("bf16_autocast", True, True)):
+                torch.backends.cudnn.allow_tf32 = tf32; torch.backends.cuda.matmul.allow_tf32 = tf32
+                if ac:
+                    def fn():
+                        with torch.autocast("cuda", dtype=torch.bfloat16):
+                            return oenc.text_encoder_forward(w32, ids, xl.long())
+                else:
+                    fn = lambda: oenc.text_encoder_forward(w32, ids, xl.long())
+                ms = timed(fn, 5)
+                out = fn()
+                gpu_base[name] = {"ms_per_forward": ms, "tokens_per_sec": B * T / (ms / 1e3), "rel_l2_mu_vs_oracle_fp64": rel(out[0].float(), ref[0])}
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+    if rank != 0:
+        return None
+    best = modes["fp16"]
+    res = {"metric": "text_encoder_tokens_per_sec", "value": best["tokens_per_sec"], "unit": "tokens/s", "n_gpus": world, "scaling": "weak",
+           "dtype": "fp16", "data": "synthetic",
+           "config": {"workload": f"TextEncoder.forward B={B}/GPU T_text={T} ragged 0.7-1.0, random-init Matcha-size encoder (7.2 M parameters)"},
+           "modes": modes}
+    if gpu_base is not None:
+        gpu_base["speedup_fp16_vs_eager_bf16"] = gpu_base["bf16_autocast"]["ms_per_forward"] / modes["fp16"]["ms_per_forward"]
+        gpu_base["speedup_fp32_vs_eager_fp32"] = gpu_base["fp32"]["ms_per_forward"] / modes["fp32"]["ms_per_forward"]
+        res["gpu_baseline"] = gpu_base
+    if not a.no_cpu_baseline and world == 1:
+        torch.set_num_threads(host_cores())
+        w_cpu = encs["fp32"].state_dict()
+        with torch.no_grad():
+            oenc.text_encoder_forward(w_cpu, ids[:4].cpu(), xl[:4].cpu().long())
+            t1 = time.perf_counter()
+            oenc.text_encoder_forward(w_cpu, ids.cpu(), xl.cpu().long())
+            dt = time.perf_counter() - t1
+        res["cpu_baseline"] = {"value": B * T / dt, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": f"one forward of the same batch through the torch restatement on the host ({dt * 1e3:.0f} ms)"}
+    return res
+
+
 def training_leg(a, dev, world, rank, dist, barrier):
-    """BASELINE configs[3]: the training-step hot path after the text encoder (out of scope):
-    mu_x -> log-prior -> MAS -> logw_ / mu_y / prior loss -> CFM flow-matching loss forward, synthetic
-    LJSpeech-shaped batch 32 per GPU (T_text 128, T_mel 800, ragged 0.7-1.0)."""
+    """BASELINE configs[3]: the training-step hot path, forward values: token ids -> text encoder (mu_x, logw) ->
+    log-prior -> MAS -> logw_ / mu_y / prior loss -> CFM flow-matching loss forward, synthetic LJSpeech-shaped batch 32
+    per GPU (T_text 128, T_mel 800, ragged 0.7-1.0)."""
     import torch
     from types import SimpleNamespace
     from matcha_b200 import alignment as al
     from matcha_b200.flow_matching import CFM
+    from matcha_b200.text_encoder import TextEncoder
     B, T_x, T_y = a.dec_batch, 128, a.dec_T
     cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), _dec_params(), precision=a.dec_precision)
     cfm.estimator.initialize_weights(seed=0)
+    enc = TextEncoder(n_vocab=178, precision="fp32" if a.dec_precision == "fp32" else "fp16").initialize_weights(seed=1)
     rng = np.random.default_rng(3000 + rank)
     xl_h, yl_h = ragged_lengths(rng, B, T_x, T_y)
     g = torch.Generator(device=dev); g.manual_seed(3000 + rank)
-    mu_x = torch.randn(B, 80, T_x, device=dev, generator=g)
+    ids = torch.randint(0, 178, (B, T_x), device=dev, generator=g)
     y = torch.randn(B, 80, T_y, device=dev, generator=g)
-    logw = torch.randn(B, 1, T_x, device=dev, generator=g)
     xl, yl = torch.from_numpy(xl_h).to(dev), torch.from_numpy(yl_h).to(dev)
     y_mask = (torch.arange(T_y, device=dev)[None, :] < yl[:, None]).float().unsqueeze(1)
-    x_mask = (torch.arange(T_x, device=dev)[None, :] < xl[:, None]).float().unsqueeze(1)
 
-    def step(mu_x, y, logw):
+    def step(ids, y):
+        mu_x, logw, x_mask = enc(ids, xl)                                         # matcha_tts.py:271 (text_encoder.py:377-402)
         r = al.align(mu_x, y, xl, yl)                                             # matcha_tts.py:277-287, 314-321
-        dur_loss = torch.sum((logw * x_mask - r["logw_"]) ** 2) / torch.sum(xl)    # utils/model.py:117-135
+        dur_loss = torch.sum((logw - r["logw_"]) ** 2) / torch.sum(xl)            # utils/model.py:117-135
         diff_loss, _ = cfm.compute_loss(y, y_mask, r["mu_y"])                     # flow_matching.py:106-151
         return torch.stack([dur_loss, r["prior_loss"], diff_loss])
 
     for _ in range(3):
-        losses = step(mu_x, y, logw)
+        losses = step(ids, y)
     barrier()
     K = 10
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     ev[0].record()
     for _ in range(K):
-        losses = step(mu_x, y, logw)
+        losses = step(ids, y)
     ev[1].record()
     barrier()
     ms = torch.tensor([ev[0].elapsed_time(ev[1]) / K], device=dev, dtype=torch.float64)
+    mu_x, logw, _ = enc(ids, xl)
     # stage split (device time of each stage alone, same inputs)
 
     def timed(fn, n=10):
@@ -625,15 +711,16 @@ def training_leg(a, dev, world, rank, dist, barrier):
         return e0.elapsed_time(e1) / n
     lp = al.log_prior(mu_x, y, xl, yl)
     _, dur = al.maximum_path_with_durations(lp, xl, yl)
-    split = {"log_prior_ms": timed(lambda: al.log_prior(mu_x, y, xl, yl)),
+    split = {"text_encoder_ms": timed(lambda: enc(ids, xl)),
+             "log_prior_ms": timed(lambda: al.log_prior(mu_x, y, xl, yl)),
              "mas_ms": timed(lambda: al.maximum_path_with_durations(lp, xl, yl)),
              "expand_ms": timed(lambda: al.expand(dur, mu_x, xl, yl, y=y, want_logw=True, want_prior=True)),
              "cfm_loss_ms": timed(lambda: cfm.compute_loss(y, y_mask, y))}
-    # e2e: pinned host tensors in, the three losses out
-    mu_h, y_h, lw_h = mu_x.cpu().pin_memory(), y.cpu().pin_memory(), logw.cpu().pin_memory()
+    # e2e: pinned host tensors in (token ids, mel), the three losses out
+    ids_h, y_h = ids.cpu().pin_memory(), y.cpu().pin_memory()
 
     def e2e_once():
-        return step(mu_h.to(dev, non_blocking=True), y_h.to(dev, non_blocking=True), lw_h.to(dev, non_blocking=True)).cpu()
+        return step(ids_h.to(dev, non_blocking=True), y_h.to(dev, non_blocking=True)).cpu()
     e2e_once(); barrier()
     t0 = time.perf_counter()
     for _ in range(5):
@@ -648,22 +735,27 @@ def training_leg(a, dev, world, rank, dist, barrier):
     ms = float(ms.item())
     res = {"metric": "training_hot_path_utterances_per_sec", "value": world * B / (ms / 1e3), "unit": "utterances/s",
            "ms_per_step": ms, "n_gpus": world, "scaling": "weak", "dtype": a.dec_precision, "data": "synthetic",
-           "config": {"workload": f"mu_x -> log-prior -> MAS -> mu_y/logw_/prior loss -> CFM loss forward, B={B}/GPU "
-                                  f"T_text={T_x} T_mel={T_y} ragged 0.7-1.0 (BASELINE configs[3]); text encoder and "
+           "config": {"workload": f"token ids -> text encoder ({enc.precision}) -> log-prior -> MAS -> mu_y/logw_/prior loss -> CFM loss "
+                                  f"forward, B={B}/GPU T_text={T_x} T_mel={T_y} ragged 0.7-1.0 (BASELINE configs[3]); forward values, "
                                   f"backward pass out of scope"},
            "stage_ms": split, "losses": [float(v) for v in losses.cpu()],
            "e2e": {"value": world * B / float(e2e_s.item()), "unit": "utterances/s",
-                   "h2d_bytes_per_step": int(4 * (mu_x.numel() + y.numel() + logw.numel())), "d2h_bytes_per_step": 12,
-                   "api": "matcha_b200.alignment.align + matcha_b200.flow_matching.CFM.compute_loss on pinned host tensors"}}
+                   "h2d_bytes_per_step": int(8 * ids.numel() + 4 * y.numel()), "d2h_bytes_per_step": 12,
+                   "api": "matcha_b200.text_encoder.TextEncoder + alignment.align + flow_matching.CFM.compute_loss on pinned host tensors"}}
     if not a.no_cpu_baseline and world == 1:
         from oracle import alignment as oal, decoder as odec       # the checker, timed as the CPU baseline only
         from oracle import mas as omas
+        from oracle import text_encoder as oenc
         torch.set_num_threads(host_cores())
         omas.set_omp_threads(host_cores())
-        mc, yc = mu_x.cpu(), y.cpu()
+        yc = y.cpu()
+        t1 = time.perf_counter()
+        with torch.no_grad():
+            mc = oenc.text_encoder_forward(enc.state_dict(), ids.cpu(), xl.cpu().long())[0]
+        t_enc = time.perf_counter() - t1
         t1 = time.perf_counter()
         r = oal.align(mc, yc, xl.cpu(), yl.cpu(), use_ref=oal.omas.ref_available())
-        t_align = time.perf_counter() - t1
+        t_align = time.perf_counter() - t1 + t_enc
         bs = min(4, B)
         w = cfm.estimator.state_dict()
         tt, zz = torch.rand(bs, 1, 1), torch.randn(bs, 80, T_y)
@@ -672,23 +764,29 @@ def training_leg(a, dev, world, rank, dist, barrier):
         t_loss = (time.perf_counter() - t1) * B / bs
         res["cpu_baseline"] = {"value": B / (t_align + t_loss), "unit": "utterances/s", "cores": torch.get_num_threads(),
                                "kind": "reference" if oal.omas.ref_available() else "port",
-                               "sample": f"torch CPU restatement of matcha_tts.py:277-321 with the compiled core.pyx on the "
-                                         f"full batch ({t_align * 1e3:.0f} ms) + decoder loss forward on {bs} items scaled to {B}"}
+                               "sample": f"torch CPU restatement of matcha_tts.py:271-321: text encoder ({t_enc * 1e3:.0f} ms) + alignment with "
+                                         f"the compiled core.pyx on the full batch ({t_align * 1e3:.0f} ms together) + decoder loss forward "
+                                         f"on {bs} items scaled to {B}"}
     return res
 
 
 def synthesis_leg(a, dev, world, rank, dist, barrier):
     """BASELINE configs[4]: batched synthesis throughput, 512 synthetic utterances per GPU (4096 over 8 GPUs) in
-    batches of 32, MAS-free inference: durations -> generate_path / mu_y (matcha_tts.py:218-229) -> CFM Euler
-    solve with n_timesteps 2 / 4 / 10; at N > 1 each batch's mels are all-gathered over NCCL on a side stream while the
-    next batch's solve runs (the gathers are inside the timed region)."""
+    batches of 32, MAS-free inference: token ids -> text encoder -> durations -> generate_path / mu_y
+    (matcha_tts.py:212-229) -> CFM Euler solve with n_timesteps 2 / 4 / 10; at N > 1 each batch's mels are all-gathered
+    over NCCL on a side stream while the next batch's solve runs (the gathers are inside the timed region).
+    The encoder's mu_x is used as it comes; its predicted log-durations are computed and then REPLACED by synthetic
+    LJSpeech-shaped ones (a random-init duration predictor says ~1.5 frames per token, i.e. T_mel ~ 200, not the 800 the
+    config names)."""
     import torch
     from types import SimpleNamespace
     from matcha_b200 import alignment as al
     from matcha_b200.flow_matching import CFM
+    from matcha_b200.text_encoder import TextEncoder
     n_utt, bs, T_x, T_max = a.synth_utterances, a.dec_batch, 128, a.dec_T
     cfm = CFM(160, 80, SimpleNamespace(solver="euler", sigma_min=1e-4), _dec_params(), precision=a.dec_precision)
     cfm.estimator.initialize_weights(seed=0)
+    enc = TextEncoder(n_vocab=178, precision="fp32" if a.dec_precision == "fp32" else "fp16").initialize_weights(seed=1)
     rng = np.random.default_rng(4000 + rank)
     g = torch.Generator(device=dev); g.manual_seed(4000 + rank)
     batches = []
@@ -700,8 +798,8 @@ def synthesis_leg(a, dev, world, rank, dist, barrier):
             cuts = np.sort(rng.choice(np.arange(1, yl_h[i]), xl_h[i] - 1, replace=False))
             d[i, : xl_h[i]] = np.diff(np.concatenate([[0], cuts, [yl_h[i]]]))
         logw = torch.from_numpy(np.log(np.maximum(d, 1.0) - 0.5)).unsqueeze(1).to(dev)     # ceil(exp(logw)) == d
-        x_mask = (torch.arange(T_x, device=dev)[None, :] < torch.from_numpy(xl_h).to(dev)[:, None]).float().unsqueeze(1)
-        batches.append((torch.randn(bs, 80, T_x, device=dev, generator=g), logw, x_mask, int(yl_h.sum())))
+        ids = torch.randint(0, 178, (bs, T_x), device=dev, generator=g)
+        batches.append((ids, torch.from_numpy(xl_h).to(dev), logw, int(yl_h.sum())))
     frames = sum(b[3] for b in batches)
     nb = len(batches)
     mels = torch.zeros(nb, bs, 80, T_max, device=dev)
@@ -710,8 +808,9 @@ def synthesis_leg(a, dev, world, rank, dist, barrier):
 
     def run_all(n):
         main = torch.cuda.current_stream(dev)
-        for i, (mu_x, logw, x_mask, _) in enumerate(batches):
-            pre = al.synthesis_prestep(mu_x, logw, x_mask, 1.0)                   # matcha_tts.py:218-229
+        for i, (ids, xl, logw, _) in enumerate(batches):
+            mu_x, _logw_pred, x_mask = enc(ids, xl)                               # matcha_tts.py:212
+            pre = al.synthesis_prestep(mu_x, logw, x_mask, 1.0)                   # matcha_tts.py:218-229 (synthetic durations)
             out = cfm(pre["mu_y"], pre["y_mask"], n, 1.0)                         # :234 (randn + Euler solve)
             mels[i, :, :, : out.shape[-1]] = out
             if world > 1:
@@ -740,8 +839,9 @@ def synthesis_leg(a, dev, world, rank, dist, barrier):
     return {"metric": "synthesis_utterances_per_sec", "value": per_n["n_timesteps_10"]["utterances_per_sec"],
             "unit": "utterances/s", "n_gpus": world, "scaling": "weak", "dtype": a.dec_precision, "data": "synthetic",
             "config": {"workload": f"{n_utt} utterances/GPU in batches of {bs}, T_text={T_x}, T_mel<={T_max} (valid frames "
-                                   f"counted), durations -> generate_path/mu_y -> CFM solve, per-batch all-gather of mels on a side "
-                                   f"stream at N>1 (BASELINE configs[4]); text encoder and vocoder out of scope"},
+                                   f"counted), token ids -> text encoder ({enc.precision}) -> synthetic LJSpeech-shaped durations -> "
+                                   f"generate_path/mu_y -> CFM solve, per-batch all-gather of mels on a side stream at N>1 "
+                                   f"(BASELINE configs[4]); vocoder out of scope"},
             "by_n_timesteps": per_n}
 
 
@@ -983,8 +1083,9 @@ def run_ours(a):
     if not a.no_decoder:
         torch.cuda.empty_cache()
         dec = decoder_leg(a, dev, world, rank, dist, barrier)
-    train = synth = None
+    train = synth = tenc = None
     if not a.no_decoder and not a.no_pipeline_legs:
+        tenc = text_encoder_leg(a, dev, world, rank, dist, barrier)
         train = training_leg(a, dev, world, rank, dist, barrier)
         synth = synthesis_leg(a, dev, world, rank, dist, barrier)
     if rank == 0:
@@ -995,9 +1096,12 @@ def run_ours(a):
         if dec is not None:
             line["cfm_decoder"] = dec
             line["gpu_launches"] = a.steps + 5 * dec["gpu_launches_per_solve"]
+        if tenc is not None:
+            line["text_encoder"] = tenc
+            line["gpu_launches"] += 20 * 2 * 38             # 20 timed forwards in each precision, 38 kernels each
         if train is not None:
             line["training_step"] = train
-            line["gpu_launches"] += 10 * (3 + 2 + 185)      # 10 timed steps: align kernels, loss kernels, one graph-replayed eval
+            line["gpu_launches"] += 10 * (38 + 3 + 2 + 185)   # 10 timed steps: encoder, align kernels, loss kernels, one graph-replayed eval
         if synth is not None:
             line["synthesis"] = synth
         _emit(line)

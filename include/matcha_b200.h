@@ -205,22 +205,26 @@ int matcha_b200_cfm_solve_euler(const float *x0_dev, const float *mu_dev, const 
  *        matcha/models/components/text_encoder.py:377-402 (with ConvReluNorm :48-57, Encoder :307-331,
  *        MultiHeadAttention + RotaryPositionalEmbeddings :110-229, FFN :257-260, DurationPredictor :80-97)
  * for the configuration MatchaTTS builds (matcha_tts.py:122-139: 192 channels, 768 filter channels, 2 heads, 6 layers,
- * kernel 3, prenet; duration predictor 256 x kernel 3; 80 features), inference / eval mode (dropout = identity), fp32.
+ * kernel 3, prenet; duration predictor 256 x kernel 3; 80 features), inference / eval mode (dropout = identity).
+ * precision: MB200_PREC_F32 (SIMT fp32, rel-L2 <= 1e-5) or MB200_PREC_F16 (every Conv1d on tcgen05 tensor cores with fp16
+ * operands and fp32 accumulation; residual stream, LayerNorm, attention and the mean projection in fp32; rel-L2 <= 2e-3).
  *   ids_dev      [B][T] int64 token ids (ids outside [0, n_vocab) are clamped; torch raises)
  *   lengths_dev  [B] int32 valid lengths
  *   blob_dev     packed fp32 weights (matcha_b200.text_encoder.pack_weights; matcha_b200_text_encoder_blob_floats(n_vocab)
  *                floats, 16-byte aligned)
+ *   blob_f16_dev the same blob converted to IEEE fp16 element for element (MB200_PREC_F16; NULL otherwise)
  *   rope_cos_dev, rope_sin_dev  [>= T][48] fp32: the cos / sin caches of RotaryPositionalEmbeddings._build_cache
  *                (:110-128), built by the caller with the reference's own torch ops
  *   mu_dev [B][80][T], logw_dev [B][1][T], mask_dev [B][1][T]: the three outputs, fp32 (mask_dev is also read by the kernels)
- *   workspace_dev  matcha_b200_text_encoder_workspace_bytes(B, T) bytes, 16-byte aligned; nothing is allocated inside.
- * Returns the number of kernels launched (> 0) or a negative error.  No state is kept. */
+ *   workspace_dev  matcha_b200_text_encoder_workspace_bytes(B, T, precision) bytes, 16-byte aligned; nothing is allocated inside.
+ * Returns the number of kernels launched (> 0) or a negative error.  The only state kept is, per device, the opt-in
+ * shared-memory attribute of the tensor-core kernel. */
 long long matcha_b200_text_encoder_blob_floats(int n_vocab);
-long long matcha_b200_text_encoder_workspace_bytes(int B, int T);
-int matcha_b200_text_encoder_forward(const long long *ids_dev, const int *lengths_dev, const float *blob_dev, int n_vocab,
-                                     const float *rope_cos_dev, const float *rope_sin_dev, float *mu_dev, float *logw_dev,
-                                     float *mask_dev, int B, int T, void *workspace_dev, long long workspace_bytes,
-                                     void *stream);
+long long matcha_b200_text_encoder_workspace_bytes(int B, int T, int precision);
+int matcha_b200_text_encoder_forward(const long long *ids_dev, const int *lengths_dev, const float *blob_dev,
+                                     const void *blob_f16_dev, int n_vocab, const float *rope_cos_dev,
+                                     const float *rope_sin_dev, float *mu_dev, float *logw_dev, float *mask_dev, int B, int T,
+                                     int precision, void *workspace_dev, long long workspace_bytes, void *stream);
 
 #ifdef __cplusplus
 }

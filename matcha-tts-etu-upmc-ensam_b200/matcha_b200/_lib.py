@@ -93,10 +93,10 @@ def load_library():
     lib.matcha_b200_text_encoder_blob_floats.restype = ll
     lib.matcha_b200_text_encoder_blob_floats.argtypes = [c_int]
     lib.matcha_b200_text_encoder_workspace_bytes.restype = ll
-    lib.matcha_b200_text_encoder_workspace_bytes.argtypes = [c_int, c_int]
+    lib.matcha_b200_text_encoder_workspace_bytes.argtypes = [c_int, c_int, c_int]
     lib.matcha_b200_text_encoder_forward.restype = c_int
-    lib.matcha_b200_text_encoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
-                                                     c_void_p, c_int, c_int, c_void_p, ll, c_void_p]
+    lib.matcha_b200_text_encoder_forward.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                     c_void_p, c_int, c_int, c_int, c_void_p, ll, c_void_p]
     lib.matcha_b200_debug_attention.restype = c_int
     lib.matcha_b200_debug_attention.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]
     lib.matcha_b200_debug_gemm_bf16.restype = c_int

@@ -25,7 +25,8 @@ _DECODER_PARAMS = dict(channels=(256, 256), dropout=0.05, attention_head_dim=64,
 
 class MatchaTTS(torch.nn.Module):
     """``MatchaTTS(n_vocab, out_channels=80, hidden_channels=192)`` as in the reference's simplified constructor
-    (matcha_tts.py:108-176); ``precision`` selects the decoder's arithmetic ("fp32", "fp16", "bf16")."""
+    (matcha_tts.py:108-176); ``precision`` selects the arithmetic: "fp32" (SIMT everywhere), "fp16" (tensor cores in the
+    encoder and the decoder) or "bf16" (decoder operands in bf16, encoder in fp16)."""
 
     def __init__(self, n_vocab, out_channels=80, hidden_channels=192, data_statistics=None, prior_loss=True,
                  use_precomputed_durations=False, precision="fp16"):
@@ -36,7 +37,7 @@ class MatchaTTS(torch.nn.Module):
         self.prior_loss = prior_loss
         self.use_precomputed_durations = use_precomputed_durations
         ep, dp = default_params()
-        self.encoder = TextEncoder("RoPE Encoder", ep, dp, n_vocab)
+        self.encoder = TextEncoder("RoPE Encoder", ep, dp, n_vocab, precision="fp32" if precision == "fp32" else "fp16")
         self.decoder = CFM(in_channels=2 * out_channels, out_channel=out_channels,
                            cfm_params=SimpleNamespace(solver="euler", sigma_min=1e-4), decoder_params=_DECODER_PARAMS,
                            precision=precision)

@@ -15,7 +15,9 @@ from types import SimpleNamespace
 import torch
 
 from ._lib import check, load_library
-from .decoder import _stream_ptr
+from .decoder import PREC_F16, PREC_F32, _stream_ptr
+
+_PRECISIONS = {"fp32": PREC_F32, "f32": PREC_F32, "fp16": PREC_F16, "f16": PREC_F16}
 
 C, FILTER, HEADS, LAYERS, KERNEL = 192, 768, 2, 6, 3
 DP_FILTER, DP_KERNEL, N_FEATS = 256, 3, 80
@@ -112,8 +114,14 @@ def rope_tables(seq_len):
 class TextEncoder(torch.nn.Module):
     """Same constructor signature and ``forward`` as the reference TextEncoder (text_encoder.py:341-402)."""
 
-    def __init__(self, encoder_type="RoPE Encoder", encoder_params=None, duration_predictor_params=None, n_vocab=178):
+    def __init__(self, encoder_type="RoPE Encoder", encoder_params=None, duration_predictor_params=None, n_vocab=178,
+                 precision="fp32"):
+        """``precision``: "fp32" (SIMT kernels, rel-L2 <= 1e-5 against the reference) or "fp16" (every Conv1d on the
+        tcgen05 tensor cores with fp16 operands and fp32 accumulation, rel-L2 <= 2e-3)."""
         super().__init__()
+        if precision not in _PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}")
+        self.precision = precision
         ep, dp = default_params()
         encoder_params = encoder_params or ep
         duration_predictor_params = duration_predictor_params or dp
@@ -128,6 +136,7 @@ class TextEncoder(torch.nn.Module):
         self.feature_dim, self.channel_dim = N_FEATS, C
         self._weights = None
         self._blob = {}               # device -> packed fp32 blob
+        self._blob16 = {}             # device -> the same blob in fp16 (tensor-core mode)
         self._rope = {}               # device -> (seq_len, cos, sin)
         self._ws = {}                 # one plain-launch workspace kept
         self._graphs = OrderedDict()  # (device, B, T) -> (graph, buffers); every entry owns its workspace and I/O tensors
@@ -173,6 +182,7 @@ class TextEncoder(torch.nn.Module):
             raise KeyError(f"state_dict mismatch: missing {missing[:4]}..., wrong shape {bad[:4]}...")
         self._weights = OrderedDict((k, sd[k].detach().to("cpu", torch.float32).clone()) for k in exp)
         self._blob.clear()
+        self._blob16.clear()
         self._graphs.clear()          # captured graphs hold pointers into the old weight blob
         self._seen.clear()
         return self
@@ -188,6 +198,15 @@ class TextEncoder(torch.nn.Module):
             self._blob[key] = pack_weights(self._weights, self.vocab_size).to(device)
         return self._blob[key]
 
+    def _blob16_on(self, device):
+        """fp16 twin of the blob, element for element (the C side addresses a tensor at the same element offset)."""
+        if _PRECISIONS[self.precision] == PREC_F32:
+            return None
+        key = str(device)
+        if key not in self._blob16:
+            self._blob16[key] = self._blob_on(device).to(torch.float16)
+        return self._blob16[key]
+
     def _rope_on(self, device, T):
         key = str(device)
         cur = self._rope.get(key)
@@ -200,7 +219,8 @@ class TextEncoder(torch.nn.Module):
         return cur[1], cur[2]
 
     def _new_workspace(self, device, B, T):
-        return torch.empty(int(load_library().matcha_b200_text_encoder_workspace_bytes(B, T)), dtype=torch.uint8, device=device)
+        n = int(load_library().matcha_b200_text_encoder_workspace_bytes(B, T, _PRECISIONS[self.precision]))
+        return torch.empty(n, dtype=torch.uint8, device=device)
 
     # -- forward ----------------------------------------------------------------------------
     @torch.no_grad()
@@ -213,20 +233,21 @@ class TextEncoder(torch.nn.Module):
         B, T = text_input.shape
         ids = text_input.to(torch.int64).contiguous()
         lens = text_lengths.to(dev, torch.int32).contiguous()
-        blob = self._blob_on(dev)
+        blob, blob16 = self._blob_on(dev), self._blob16_on(dev)
         cos, sin = self._rope_on(dev, T)
+        prec = _PRECISIONS[self.precision]
 
         def launch(ids, lens, mu, logw, mask, ws):
             with torch.cuda.device(dev):
                 self.last_launches = check(lib.matcha_b200_text_encoder_forward(
-                    ids.data_ptr(), lens.data_ptr(), blob.data_ptr(), self.vocab_size, cos.data_ptr(), sin.data_ptr(),
-                    mu.data_ptr(), logw.data_ptr(), mask.data_ptr(), B, T, ws.data_ptr(), ws.numel(), _stream_ptr(dev)),
-                    "text_encoder_forward")
+                    ids.data_ptr(), lens.data_ptr(), blob.data_ptr(), blob16.data_ptr() if blob16 is not None else None,
+                    self.vocab_size, cos.data_ptr(), sin.data_ptr(), mu.data_ptr(), logw.data_ptr(), mask.data_ptr(), B, T, prec,
+                    ws.data_ptr(), ws.numel(), _stream_ptr(dev)), "text_encoder_forward")
 
         def outputs():
             return (torch.empty(B, N_FEATS, T, device=dev), torch.empty(B, 1, T, device=dev), torch.empty(B, 1, T, device=dev))
 
-        key = (str(dev), B, T)
+        key = (str(dev), B, T, self.precision)
         graphable = self.use_graph and not torch.cuda.is_current_stream_capturing()
         entry = None
         if graphable:
@@ -239,7 +260,7 @@ class TextEncoder(torch.nn.Module):
                 self._seen[key] = 1
                 graphable = False
         if not graphable:
-            wkey = (str(dev), B, T)
+            wkey = (str(dev), B, T, self.precision)
             if wkey not in self._ws:
                 self._ws = {wkey: self._new_workspace(dev, B, T)}
             mu, logw, mask = outputs()

@@ -14,20 +14,22 @@ NV = 178
 w = oenc.make_weights(23, "rich", NV)
 wd = oenc.cast_weights({k: v.to(dev) for k, v in w.items()}, torch.float64)
 B, T = int(sys.argv[1]), int(sys.argv[2])
+PREC = int(sys.argv[3]) if len(sys.argv) > 3 else 0          # 0 fp32, 2 fp16
 g = torch.Generator().manual_seed(5)
 ids = torch.randint(0, NV, (B, T), generator=g).to(dev)
 lens = torch.tensor([T] + [max(1, int(T * 0.7))] * (B - 1), dtype=torch.int32).to(dev)
 blob = te.pack_weights(w, NV).to(dev)
+blob16 = blob.half()
 cos, sin = te.rope_tables(max(T, 512)); cos, sin = cos.to(dev), sin.to(dev)
 M = B * T
 def r64(n): return (n + 63) // 64 * 64
-names = [("x0", 192), ("x", 192), ("y", 192), ("ha", 192), ("hb", 192), ("qkv", 576), ("att", 192), ("f1", 768), ("dp1", 256)]
+names = [("x0", 192), ("x", 192), ("y", 192), ("qkv", 576)]
 for nl in (0, 1, 2, 6):
     os.environ["MB200_TE_LAYERS"] = str(nl)
-    ws = torch.zeros(int(lib.matcha_b200_text_encoder_workspace_bytes(B, T)) // 4, device=dev)
+    ws = torch.zeros(int(lib.matcha_b200_text_encoder_workspace_bytes(B, T, PREC)) // 4, device=dev)
     mu, logw, mask = torch.empty(B, 80, T, device=dev), torch.empty(B, 1, T, device=dev), torch.empty(B, 1, T, device=dev)
-    rc = lib.matcha_b200_text_encoder_forward(ids.data_ptr(), lens.data_ptr(), blob.data_ptr(), NV, cos.data_ptr(), sin.data_ptr(),
-                                              mu.data_ptr(), logw.data_ptr(), mask.data_ptr(), B, T, ws.data_ptr(), ws.numel() * 4, None)
+    rc = lib.matcha_b200_text_encoder_forward(ids.data_ptr(), lens.data_ptr(), blob.data_ptr(), blob16.data_ptr(), NV, cos.data_ptr(), sin.data_ptr(),
+                                              mu.data_ptr(), logw.data_ptr(), mask.data_ptr(), B, T, PREC, ws.data_ptr(), ws.numel() * 4, None)
     torch.cuda.synchronize()
     buf, off = {}, 0
     for n, c in names:
