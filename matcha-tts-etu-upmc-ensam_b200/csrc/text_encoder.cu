@@ -302,6 +302,11 @@ te_gemm_kernel(const GemmArgs g) {
 // ------------------------------------------------------------------ attention with rotary embeddings (fp32 SIMT)
 // qkv rows are [q(192) | k(192) | v(192)], head h at columns h*96.  One CTA per (sample, head, 32 queries); four threads per
 // query row, each holding the whole rotated q, 8 of the 32 keys of a block and 24 of the 96 output features.
+__device__ __forceinline__ uint32_t pack_half2_sat(float a, float b) {      // a -> low half; saturating (never inf)
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
 __device__ __forceinline__ long long gtime() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 constexpr int kAQ = 32, kAK = 32, kAPK = 100, kAPP = 36;
 constexpr int kAttTile = kAK * kAPK * 4;                              // one K or V tile: 12.8 KB
@@ -476,6 +481,185 @@ te_attention_kernel(const float *__restrict__ qkv, const float *__restrict__ mas
     }
 }
 
+
+// ------------------------------------------------------------------ attention on the tensor cores (fp16 mode)
+// Same arithmetic as te_attention_kernel with QK^T and PV as mma.sync m16n8k16 (fp16 operands, fp32 accumulate, fp32 online
+// softmax in the exp2 domain).  Input: the fp16 q|k|v rows the fused projection's epilogue wrote (RoPE already applied),
+// [B*T][576], head h at columns h*96.  One CTA = 4 warps x 16 queries; K / V stream through double-buffered shared-memory tiles
+// filled by cp.async (rows of 96 halves at a 256-byte pitch, 16-byte pieces XOR-swizzled by row & 7); fragments by ldmatrix.
+// (The SIMT kernel spends its time on shared-memory reads: one 4-FMA group per 16 bytes, 40 us per call; the tensor-core
+// form reads each K / V element once per 16 query rows.)
+constexpr int kMaBQ = 64, kMaBK = 64, kMaPitch = 256, kMaChunks = kD * 2 / 16;            // 12 sixteen-byte pieces per row
+constexpr int kMaTile = kMaBK * kMaPitch;                                                   // 16 KB
+constexpr int kMaSmemBytes = kMaBQ * kMaPitch + 4 * kMaTile + 2 * kMaBK * 4;                // Q + 2 x (K, V) + 2 mask tiles = 80.5 KB
+
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void mma16816_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(128)
+te_attention_mma_kernel(const __half *__restrict__ qkv, const float *__restrict__ mask, __half *__restrict__ out, int T) {
+    extern __shared__ __align__(128) uint8_t ma_smem[];
+    const uint32_t sQ = smem_u32(ma_smem);
+    const uint32_t sKV = sQ + kMaBQ * kMaPitch;                 // [buf][K | V][64 rows][256 B]
+    const float *sMf = reinterpret_cast<const float *>(ma_smem + kMaBQ * kMaPitch + 4 * kMaTile);
+    pdl_prologue();
+    const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * kMaBQ;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const __half *base = qkv + (size_t)b * T * (3 * kC) + h * kD;
+    const float *mrow = mask + (size_t)b * T;
+
+    auto load_tile = [&](uint32_t dst, int col_off, int row0) {          // 64 rows x 12 pieces of 16 B; rows beyond T zero-filled
+#pragma unroll
+        for (int i = 0; i < kMaBK * kMaChunks / 128; ++i) {
+            const int idx = tid + i * 128, r = idx / kMaChunks, ch = idx - r * kMaChunks;
+            const int t = row0 + r;
+            const uint32_t nbytes = t < T ? 16u : 0u;
+            const __half *src = base + (size_t)(t < T ? t : 0) * (3 * kC) + col_off + ch * 8;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + r * kMaPitch + ((ch ^ (r & 7)) << 4)), "l"(src), "r"(nbytes) : "memory");
+        }
+    };
+    // key mask of a block: read through L2 (the rule of this file), parked in shared memory one block ahead
+    float *sMw = reinterpret_cast<float *>(ma_smem + kMaBQ * kMaPitch + 4 * kMaTile);
+    auto fetch_mask = [&](int row0) { return (tid < kMaBK && row0 + tid < T) ? ld_act(mrow + row0 + tid) : 0.f; };
+    load_tile(sQ, 0, q0);
+    load_tile(sKV, kC, 0);
+    load_tile(sKV + kMaTile, 2 * kC, 0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (tid < kMaBK) sMw[tid] = fetch_mask(0);
+
+    const int g = lane >> 2, qd = lane & 3;
+    float mq[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int t = q0 + warp * 16 + g + 8 * i;
+        mq[i] = t < T ? ld_act(mrow + t) : 0.f;
+    }
+    float o[kD / 8][4];
+#pragma unroll
+    for (int i = 0; i < kD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+    uint32_t qa[kD / 16][4];
+    const float kLog2e = 1.4426950408889634f;
+    const float kScale = 0.10206207261596577f;                  // 1 / sqrt(96)
+    const int nkb = (T + kMaBK - 1) / kMaBK;
+
+    for (int kb = 0; kb < nkb; ++kb) {
+        const uint32_t sK = sKV + (uint32_t)(kb & 1) * 2u * kMaTile, sV = sK + kMaTile;
+        if (kb + 1 < nkb) {                                    // prefetch the next K / V block
+            const uint32_t nK = sKV + (uint32_t)((kb + 1) & 1) * 2u * kMaTile;
+            load_tile(nK, kC, (kb + 1) * kMaBK);
+            load_tile(nK + kMaTile, 2 * kC, (kb + 1) * kMaBK);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        const float m_next = kb + 1 < nkb ? fetch_mask((kb + 1) * kMaBK) : 0.f;      // in flight under this block's MMAs
+        __syncthreads();
+        if (kb == 0) {
+#pragma unroll
+            for (int ks = 0; ks < kD / 16; ++ks) {
+                const int r = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, ch = 2 * ks + (lane >> 4);
+                ldsm_x4(sQ + r * kMaPitch + ((ch ^ (r & 7)) << 4), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+            }
+        }
+        // S = Q K^T  (16 queries x 64 keys per warp)
+        float s[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f; }
+#pragma unroll
+        for (int ks = 0; ks < kD / 16; ++ks) {
+#pragma unroll
+            for (int np = 0; np < 4; ++np) {
+                const int r = np * 16 + (lane & 7) + (lane >> 4) * 8, ch = 2 * ks + ((lane >> 3) & 1);
+                uint32_t b0, b1, b2, b3;
+                ldsm_x4(sK + r * kMaPitch + ((ch ^ (r & 7)) << 4), b0, b1, b2, b3);
+                mma16816_f16(s[2 * np], qa[ks], b0, b1);
+                mma16816_f16(s[2 * np + 1], qa[ks], b2, b3);
+            }
+        }
+        // logits = masked_fill(s / sqrt(96), mask_q * mask_k == 0, -1e4) (:213-220); keys beyond T do not exist
+        float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const int kl = nt * 8 + 2 * qd, key = kb * kMaBK + kl;
+            const float mk0 = sMf[(kb & 1) * kMaBK + kl], mk1 = sMf[(kb & 1) * kMaBK + kl + 1];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int ky = key + (e & 1);
+                const float mkk = (e & 1) ? mk1 : mk0, mqq = mq[e >> 1];
+                float v = s[nt][e] * kScale;
+                if (mqq * mkk == 0.f) v = -1e4f;
+                s[nt][e] = ky < T ? v : -INFINITY;
+            }
+            mx[0] = fmaxf(mx[0], fmaxf(s[nt][0], s[nt][1]));
+            mx[1] = fmaxf(mx[1], fmaxf(s[nt][2], s[nt][3]));
+        }
+        float corr[2], msc[2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            mx[i] = fmaxf(mx[i], __shfl_xor_sync(0xffffffffu, mx[i], 1));
+            mx[i] = fmaxf(mx[i], __shfl_xor_sync(0xffffffffu, mx[i], 2));
+            const float m_new = fmaxf(m_run[i], mx[i]);
+            corr[i] = exp2f((m_run[i] - m_new) * kLog2e);
+            m_run[i] = m_new;
+            msc[i] = m_new * kLog2e;
+        }
+        float ps[2] = {0.f, 0.f};
+        uint32_t pa[4][4];                                       // P as A fragments, 4 k-steps of 16 keys
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const float p0 = exp2f(fmaf(s[nt][0], kLog2e, -msc[0])), p1 = exp2f(fmaf(s[nt][1], kLog2e, -msc[0]));
+            const float p2 = exp2f(fmaf(s[nt][2], kLog2e, -msc[1])), p3 = exp2f(fmaf(s[nt][3], kLog2e, -msc[1]));
+            ps[0] += p0 + p1; ps[1] += p2 + p3;
+            pa[nt >> 1][(nt & 1) * 2 + 0] = pack_half2_sat(p0, p1);
+            pa[nt >> 1][(nt & 1) * 2 + 1] = pack_half2_sat(p2, p3);
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            ps[i] += __shfl_xor_sync(0xffffffffu, ps[i], 1);
+            ps[i] += __shfl_xor_sync(0xffffffffu, ps[i], 2);
+            l_run[i] = l_run[i] * corr[i] + ps[i];
+        }
+#pragma unroll
+        for (int dt = 0; dt < kD / 8; ++dt) { o[dt][0] *= corr[0]; o[dt][1] *= corr[0]; o[dt][2] *= corr[1]; o[dt][3] *= corr[1]; }
+        // O += P V
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+#pragma unroll
+            for (int dp = 0; dp < kD / 16; ++dp) {
+                const int r = j * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, ch = 2 * dp + (lane >> 4);
+                uint32_t b0, b1, b2, b3;
+                ldsm_x4_t(sV + r * kMaPitch + ((ch ^ (r & 7)) << 4), b0, b1, b2, b3);
+                mma16816_f16(o[2 * dp], pa[j], b0, b1);
+                mma16816_f16(o[2 * dp + 1], pa[j], b2, b3);
+            }
+        }
+        if (tid < kMaBK) sMw[((kb + 1) & 1) * kMaBK + tid] = m_next;
+        __syncthreads();                                         // the buffer is refilled two iterations later
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int t = q0 + warp * 16 + g + 8 * i;
+        if (t < T) {
+            const float inv = 1.0f / l_run[i];
+            uint32_t *po = reinterpret_cast<uint32_t *>(out + ((size_t)b * T + t) * kC + h * kD + 2 * qd);
+#pragma unroll
+            for (int dt = 0; dt < kD / 8; ++dt) po[dt * 4] = pack_half2_sat(o[dt][2 * i] * inv, o[dt][2 * i + 1] * inv);
+        }
+    }
+}
+
 // ------------------------------------------------------------------ mean projection, channels-first output
 // mu[b][n][t] = (sum_c x[b][t][c] * W[n][c] + bias[n]) * mask[b][t]      text_encoder.py:398
 __global__ void __launch_bounds__(256)
@@ -600,11 +784,6 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
           "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
           "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
           "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
-}
-__device__ __forceinline__ uint32_t pack_half2_sat(float a, float b) {      // a -> low half; saturating (never inf)
-    uint32_t r;
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
-    return r;
 }
 
 template <int NT>
@@ -892,7 +1071,7 @@ static long long build_weights(const float *blob, int n_vocab, EncW *w) {
 
 struct EncWs {
     float *x0, *x, *y, *ha, *hb, *qkv, *att, *f1, *dp1;                       // fp32 (fp16 mode: x0, x, y, qkv only)
-    __half *x0h, *xh, *yh, *hah, *hbh, *atth, *f1h, *dp1h;                    // fp16 GEMM operands (fp16 mode)
+    __half *x0h, *xh, *yh, *hah, *hbh, *atth, *f1h, *dp1h, *qkvh;             // fp16 GEMM / attention operands (fp16 mode)
 };
 static long long carve_workspace(float *base, int B, int T, int precision, EncWs *ws) {
     const long long M = (long long)B * T;
@@ -900,12 +1079,13 @@ static long long carve_workspace(float *base, int B, int T, int precision, EncWs
     auto take = [&](long long n) { float *p = base ? base + off : nullptr; off += (n + 63) & ~63LL; return p; };
     auto take_h = [&](long long n) { return reinterpret_cast<__half *>(take((n + 1) / 2)); };
     EncWs w = {};
-    w.x0 = take(M * kC); w.x = take(M * kC); w.y = take(M * kC); w.qkv = take(M * 3 * kC);
+    w.x0 = take(M * kC); w.x = take(M * kC); w.y = take(M * kC);
     if (precision == MB200_PREC_F32) {
+        w.qkv = take(M * 3 * kC);
         w.ha = take(M * kC); w.hb = take(M * kC); w.att = take(M * kC); w.f1 = take(M * kF); w.dp1 = take(M * kDp);
     } else {
         w.x0h = take_h(M * kC); w.xh = take_h(M * kC); w.yh = take_h(M * kC); w.hah = take_h(M * kC); w.hbh = take_h(M * kC);
-        w.atth = take_h(M * kC); w.f1h = take_h(M * kF); w.dp1h = take_h(M * kDp);
+        w.atth = take_h(M * kC); w.f1h = take_h(M * kF); w.dp1h = take_h(M * kDp); w.qkvh = take_h(M * 3 * kC);
     }
     if (ws) *ws = w;
     return off * (long long)sizeof(float);
@@ -1014,6 +1194,7 @@ static int set_attributes() {
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return MB200_ERR_NO_DEVICE;
     if (done[dev]) return MB200_OK;
     MB200_CUDA_TRY(cudaFuncSetAttribute(te_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmemBytes));
+    MB200_CUDA_TRY(cudaFuncSetAttribute(te_attention_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaSmemBytes));
     MB200_CUDA_TRY(cudaFuncSetAttribute(te_gemm_tc_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes<192>(3, true)));
     MB200_CUDA_TRY(cudaFuncSetAttribute(te_gemm_tc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes<256>(4, false)));
     done[dev] = true;
@@ -1065,9 +1246,8 @@ static void forward_f16(Ctx &c, const EncW &W, const float *blob, const __half *
     if (const char *e = getenv("MB200_TE_LAYERS")) n_layers = atoi(e) < kL ? atoi(e) : kL;     // debugging aid
     for (int i = 0; i < n_layers; ++i) {
         const LayerW &l = W.layer[i];
-        { Epi16 o; o.out_f32 = ws.qkv; o.rope_cos = rope_cos; o.rope_sin = rope_sin; gemm_tc(c, ws.xh, kC, 1, h(l.wqkv), l.bqkv, 3 * kC, o); }
-        launch_smem(c, te_attention_kernel, dim3((c.T + kAQ - 1) / kAQ, kH, c.B), dim3(128), (size_t)kAttSmemBytes, ws.qkv, c.mask, rope_cos, rope_sin, 1,
-                    (float *)nullptr, ws.atth, c.T, (long long *)nullptr);
+        { Epi16 o; o.out16 = ws.qkvh; o.rope_cos = rope_cos; o.rope_sin = rope_sin; gemm_tc(c, ws.xh, kC, 1, h(l.wqkv), l.bqkv, 3 * kC, o); }
+        launch_smem(c, te_attention_mma_kernel, dim3((c.T + kMaBQ - 1) / kMaBQ, kH, c.B), dim3(128), (size_t)kMaSmemBytes, ws.qkvh, c.mask, ws.atth, c.T);
         { Epi16 o; o.e.res = ws.x; o.e.ln_g = l.ln1g; o.e.ln_b = l.ln1b; o.out_f32 = ws.y; o.out16 = ws.yh; o.mask16 = 1;
           gemm_tc(c, ws.atth, kC, 1, h(l.wo), l.bo, kC, o); }
         { Epi16 o; o.e.relu_pre = 1; o.out16 = ws.f1h; gemm_tc(c, ws.yh, kC, kK, h(l.w1), l.b1, kF, o); }
@@ -1172,5 +1352,16 @@ extern "C" int matcha_b200_debug_te_gemm_tc(const void *a16, int Cin, const floa
     o.e.mask_post = mask_post; o.e.dp_w = dp_w; o.e.dp_b = dp_b; o.e.dp_out = dp_out;
     o.out_f32 = out_f32; o.out16 = reinterpret_cast<__half *>(out16); o.mask16 = mask16; o.rope_cos = rope_cos; o.rope_sin = rope_sin; o.stamps = stamps_dev;
     te::gemm_tc(c, reinterpret_cast<const __half *>(a16), Cin, ntaps, reinterpret_cast<const __half *>(w16), bias, N, o);
+    return c.err ? c.err : c.launches;
+}
+
+// fp16 attention on its own: qkv16 fp16 [B][T][576] (RoPE already applied), out16 fp16 [B][T][192]
+extern "C" int matcha_b200_debug_te_attention_mma(const void *qkv16, const float *mask, void *out16, int B, int T, void *stream) {
+    if (!qkv16 || !mask || !out16 || B <= 0 || T <= 0) return MB200_ERR_INVALID_ARG;
+    te::Ctx c;
+    c.st = (cudaStream_t)stream; c.B = B; c.T = T; c.mask = mask;
+    c.err = te::set_attributes();
+    te::launch_smem(c, te::te_attention_mma_kernel, dim3((T + te::kMaBQ - 1) / te::kMaBQ, te::kH, B), dim3(128), (size_t)te::kMaSmemBytes,
+                    reinterpret_cast<const __half *>(qkv16), mask, reinterpret_cast<__half *>(out16), T);
     return c.err ? c.err : c.launches;
 }

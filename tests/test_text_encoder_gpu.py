@@ -265,3 +265,26 @@ def test_simt_gemm_kernel(case):
     assert rel_l2(out, v) < 2e-6
     if dp:
         assert rel_l2(dpo, ((v * mask[..., None]) @ dpw.double() + dpb[0].double()) * mask) < 2e-6
+
+
+@pytest.mark.parametrize("B,T", [(2, 50), (32, 128), (1, 1), (3, 65), (2, 257)])
+def test_attention_mma_kernel(B, T):
+    """te_attention_mma_kernel (fp16 mode: mma.sync QK^T / PV on fp16 q|k|v rows, RoPE already applied) against torch in fp64 on
+    the same fp16-rounded inputs.  P is rounded to fp16 for the PV product and the output is stored in fp16: 1.5e-3."""
+    from matcha_b200._lib import load_library
+    lib = load_library()
+    g = torch.Generator().manual_seed(7 * B + T)
+    dev = "cuda"
+    qkv16 = torch.randn(B, T, 576, generator=g).to(dev).half()
+    lens = torch.tensor([T] + [max(1, int(T * 0.6))] * (B - 1))
+    mask = (torch.arange(T)[None] < lens[:, None]).float().to(dev)
+    out16 = torch.full((B, T, 192), float("nan"), device=dev, dtype=torch.float16)
+    assert lib.matcha_b200_debug_te_attention_mma(_P(qkv16), _P(mask), _P(out16), B, T, None) == 1
+    torch.cuda.synchronize()
+    d = qkv16.double()
+    q, k, v = (d[..., i * 192:(i + 1) * 192].view(B, T, 2, 96).transpose(1, 2) for i in range(3))
+    sc = q @ k.transpose(-1, -2) / 96 ** 0.5
+    sc = sc.masked_fill((mask[:, None, :, None] * mask[:, None, None, :]) == 0, -1e4)
+    want = (torch.softmax(sc, -1) @ v).transpose(1, 2).reshape(B, T, 192)
+    assert torch.isfinite(out16).all()
+    assert rel_l2(out16.float(), want) < 1.5e-3
