@@ -7,10 +7,13 @@
       text encoder -> log-prior -> MAS -> logw_ / mu_y -> duration, prior and flow-matching losses (FORWARD VALUES:
       the kernels are inference kernels, the backward pass of training is outside this path)
 Same argument meaning and result layout as the reference; ``state_dict`` keys are the reference's (``encoder.*``,
-``decoder.estimator.*``).  The ``out_size`` random cut (:290-312) is host-side slicing around ``compute_loss`` and is
-not mirrored (``forward`` raises when it is given).  No CPU fallback.
+``decoder.estimator.*``).  The ``out_size`` random cut (:290-312) is mirrored too: offsets are drawn on the host with Python's
+``random`` exactly as the reference does, and the cut is applied to ``y``, ``attn`` and ``mu_y`` (cutting ``mu_y`` is the same as
+forming it from the cut ``attn``: every column of ``attn`` is one-hot).  No CPU fallback.
 """
 import datetime as dt
+import math
+import random
 from collections import OrderedDict
 from types import SimpleNamespace
 
@@ -79,8 +82,6 @@ class MatchaTTS(torch.nn.Module):
     def forward(self, x, x_lengths, y, y_lengths, out_size=None, cond=None, durations=None, *, t=None, z=None):
         """Returns (dur_loss, prior_loss, diff_loss, attn) as the reference does; ``t`` / ``z`` may be injected for the
         flow-matching loss (tests share them with the oracle)."""
-        if out_size is not None:
-            raise NotImplementedError("the out_size cut (matcha_tts.py:290-312) is host-side slicing and stays with the caller")
         dev = y.device
         mu_x, logw, x_mask = self.encoder(x, x_lengths)                                          # :271
         T_y = y.shape[-1]
@@ -95,5 +96,25 @@ class MatchaTTS(torch.nn.Module):
             r = alignment.align(mu_x, y, x_lengths, y_lengths, prior_loss=self.prior_loss)       # :281-291, 314-321
             attn, logw_, mu_y, prior = r["attn"], r["logw_"], r["mu_y"], r["prior_loss"]
         dur_loss = torch.sum((logw - logw_) ** 2) / torch.sum(x_lengths.to(dev))                 # utils/model.py:117-135
+        if out_size is not None:                                                                 # :290-312
+            max_offset = (y_lengths - out_size).clamp(0)
+            offset_ranges = list(zip([0] * max_offset.shape[0], max_offset.cpu().numpy()))
+            out_offset = [int(random.choice(range(start, end))) if end > start else 0 for start, end in offset_ranges]
+            attn_cut = torch.zeros(attn.shape[0], attn.shape[1], out_size, dtype=attn.dtype, device=dev)
+            y_cut = torch.zeros(y.shape[0], self.n_feats, out_size, dtype=y.dtype, device=dev)
+            mu_cut = torch.zeros(y.shape[0], self.n_feats, out_size, dtype=mu_y.dtype, device=dev)
+            y_cut_lengths = []
+            yl_host = y_lengths.cpu().tolist()
+            for i, off in enumerate(out_offset):
+                n = out_size + min(yl_host[i] - out_size, 0)
+                y_cut_lengths.append(n)
+                y_cut[i, :, :n] = y[i, :, off:off + n]
+                attn_cut[i, :, :n] = attn[i, :, off:off + n]
+                mu_cut[i, :, :n] = mu_y[i, :, off:off + n]
+            y_cut_lengths = torch.tensor(y_cut_lengths, device=dev)
+            y_mask = (torch.arange(out_size, device=dev).unsqueeze(0) < y_cut_lengths.unsqueeze(1)).unsqueeze(1).to(x_mask.dtype)
+            attn, y, mu_y = attn_cut, y_cut, mu_cut
+            if self.prior_loss:                                                                  # :319-322 on the cut tensors
+                prior = torch.sum(0.5 * ((y - mu_y) ** 2 + math.log(2 * math.pi)) * y_mask) / (torch.sum(y_mask) * self.n_feats)
         diff_loss, _ = self.decoder.compute_loss(x1=y, mask=y_mask, mu=mu_y, cond=cond, t=t, z=z)   # :317
         return dur_loss, prior, diff_loss, attn

@@ -95,3 +95,39 @@ def test_training_forward_values_match_oracle_composition(weights):
     assert abs(float(dur) - float(odur)) < 1e-5 * abs(float(odur))
     assert abs(float(prior) - float(oprior)) < 1e-5 * abs(float(oprior))
     assert abs(float(diff) - float(odiff)) < 2e-5 * abs(float(odiff))
+
+
+def test_training_forward_with_out_size_cut(weights):
+    """matcha_tts.py:290-312: the random segment cut.  The offsets come from Python's `random` in the reference's order, so the
+    oracle composition re-seeds it and draws the same ones."""
+    import random
+    we, wd = weights
+    model = build(weights, "fp32")
+    g = torch.Generator().manual_seed(3)
+    B, T_x, T_y, out_size = 3, 20, 96, 32                               # out_size divisible by 4 (two U-Net downsamplings)
+    x = torch.randint(0, N_VOCAB, (B, T_x), generator=g)
+    x_lengths, y_lengths = torch.tensor([20, 15, 11]), torch.tensor([96, 70, 28])      # the last one is shorter than out_size
+    y = torch.randn(B, 80, T_y, generator=g)
+    t, z = torch.rand(B, 1, 1, generator=g), torch.randn(B, 80, out_size, generator=g)
+    random.seed(5)
+    dur, prior, diff, attn = model(x.cuda(), x_lengths.cuda(), y.cuda(), y_lengths.cuda(), out_size=out_size, t=t.cuda(), z=z.cuda())
+    # oracle composition
+    mu_x, logw, x_mask = oenc.text_encoder_forward(we, x, x_lengths)
+    y_mask = oal.sequence_mask(y_lengths, T_y).unsqueeze(1).float()
+    oattn = oal.maximum_path(oal.log_prior(mu_x, y), (x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)).squeeze(1))
+    random.seed(5)
+    max_offset = (y_lengths - out_size).clamp(0)
+    offs = [random.choice(range(0, int(e))) if int(e) > 0 else 0 for e in max_offset]
+    attn_cut, y_cut, lens = torch.zeros(B, T_x, out_size), torch.zeros(B, 80, out_size), []
+    for i, off in enumerate(offs):
+        n = out_size + min(int(y_lengths[i]) - out_size, 0)
+        lens.append(n)
+        y_cut[i, :, :n] = y[i, :, off:off + n]
+        attn_cut[i, :, :n] = oattn[i, :, off:off + n]
+    cut_mask = oal.sequence_mask(torch.tensor(lens), out_size).unsqueeze(1).float()
+    mu_y = torch.matmul(attn_cut.transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+    oprior = torch.sum(0.5 * ((y_cut - mu_y) ** 2 + math.log(2 * math.pi)) * cut_mask) / (torch.sum(cut_mask) * 80)
+    odiff, _ = odec.compute_loss(wd, y_cut, cut_mask, mu_y, t, z)
+    assert attn.shape == (B, T_x, out_size) and torch.equal(attn.cpu(), attn_cut)
+    assert abs(float(prior) - float(oprior)) < 1e-5 * abs(float(oprior))
+    assert abs(float(diff) - float(odiff)) < 2e-5 * abs(float(odiff))
