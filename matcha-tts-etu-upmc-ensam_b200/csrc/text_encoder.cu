@@ -709,7 +709,7 @@ te_mean_proj_kernel(const float *__restrict__ x, const float *__restrict__ w, co
 //               the duration predictor's 256 -> 1 projection as a per-row dot product.
 // One 128-row tile per CTA (grid = B * ceil(T / 128) x N / NT): the encoder's GEMMs have 32-100 tiles, fewer than SMs.
 constexpr int kTcMaxStages = 4, kTcM = 128, kTcK = 64, kTcStageA = kTcM * kTcK * 2;
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;                    // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
 constexpr int kTcParamBytes = 4 * 256 * 4;          // bias | ln_g | ln_b | dp_w of the tile's columns, staged once per CTA
 // store staging: per epilogue warp a [32 rows][128 B] tile that turns thread = row into row-contiguous stores; it lives in the
 // first 16 KB of the TMA ring, which is free once the accumulator is complete (every MMA has read its stage by then)
@@ -828,7 +828,7 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const bool stamp = g.stamps && blockIdx.x == 0 && blockIdx.y == 0;
     if (stamp && threadIdx.x == 0) g.stamps[0] = gtime();
     if (warp >= 2) {             // the tile's per-column parameters (weights: no dependency on the predecessor kernel)
-        for (int i = threadIdx.x - 64; i < NT; i += 128) {
+        for (int i = threadIdx.x - 64; i < NT; i += 256) {
             spar[i] = g.bias[n0 + i];
             spar[256 + i] = g.ln_g ? g.ln_g[n0 + i] : 1.f;
             spar[512 + i] = g.ln_g ? g.ln_b[n0 + i] : 0.f;
@@ -871,6 +871,9 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     } else {
         // ============================ epilogue: thread = row ============================
         const int q = warp & 3;                          // TMEM lane quarter this warp may touch
+        const int half = (warp - 2) >> 2;                // ... and the half of the tile's columns it owns (chunks [jlo, jhi))
+        constexpr int NJ = NT / 32;
+        const int jlo = half * (NJ / 2), jhi = jlo + NJ / 2;
         const int t = t0 + 32 * q + lane;
         const bool valid = t < g.T;
         const size_t m = (size_t)b * g.T + (valid ? t : 0);
@@ -881,9 +884,9 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // lanes copy consecutive 16-byte pieces of a row, so every instruction touches whole 128-byte lines
         const uint32_t res_row = base + res_off + (uint32_t)trow * TcSizes<NT>::kResPitch;
         if (g.res) {
-            constexpr int kPieces = NT / 4;                      // 16-byte pieces per row
+            constexpr int kPieces = NT / 8;                      // 16-byte pieces of this warp's half of a row
             for (int idx = lane; idx < 32 * kPieces; idx += 32) {
-                const int rr = idx / kPieces, pc = idx - rr * kPieces;
+                const int rr = idx / kPieces, pc = idx - rr * kPieces + half * kPieces;
                 const int tt = t0 + 32 * q + rr;
                 if (tt < g.T) {
                     const float *rp = g.res + ((size_t)b * g.T + tt) * g.N + n0 + 4 * pc;
@@ -893,7 +896,7 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");     // parameters staged by all four epilogue warps
+        asm volatile("bar.sync 1, 256;" ::: "memory");     // parameters staged by all eight epilogue warps
         mbar_wait_parked(bar_tfull, 0u, 1000);
         if (stamp && threadIdx.x == 64) g.stamps[3] = gtime();
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -956,12 +959,16 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
             __syncwarp();
         };
+        // exchange area of the two warps that share a row (LayerNorm partial sums, duration-projection partial dot products): in the
+        // ring too, behind the eight staging tiles
+        float2 *const xch = reinterpret_cast<float2 *>(gbase + stg_off + 8 * 4096);
         if (g.rope_cos && n0 < 2 * kC) {
             // q (tile 0) or k (tile 1) of the fused projection: head hh = columns [96 hh, 96 hh + 96) of the tile, of which the
             // first 48 are rotated: x'[d] = x[d] cos[d] - x[d+24] sin[d], x'[d+24] = x[d+24] cos[d+24] + x[d] sin[d+24], d < 24
             // (RotaryPositionalEmbeddings.forward, :135-148, with the reference's two roundings per product pair).
             const float *cs = g.rope_cos + (size_t)(valid ? t : 0) * kRope, *sn = g.rope_sin + (size_t)(valid ? t : 0) * kRope;
-            for (int hh = 0; hh < 2; ++hh) {
+            {
+                const int hh = half;                            // one head per warp of the pair
                 uint32_t v0[32], v1[32];
                 tmem_ld32(tacc + 32 * (3 * hh), v0);
                 tmem_ld32(tacc + 32 * (3 * hh + 1), v1);
@@ -991,7 +998,7 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             float mean = 0.f, rstd = 1.f;
             if (ln) {
                 float s1 = 0.f, s2 = 0.f;
-                for (int j = 0; j < NT / 32; ++j) {
+                for (int j = jlo; j < jhi; ++j) {
                     uint32_t v[32];
                     tmem_ld32(tacc + 32 * j, v);
                     pre(j, v);
@@ -1000,12 +1007,16 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     tmem_st32(tacc + 32 * j, v);
                 }
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                xch[half * kTcM + trow] = make_float2(s1, s2);              // the other half's sums come from the partner warp
+                asm volatile("bar.sync 2, 256;" ::: "memory");
+                const float2 oth = xch[(half ^ 1) * kTcM + trow];
+                s1 += oth.x; s2 += oth.y;
                 mean = s1 * (1.0f / NT);
                 const float var = fmaxf(s2 * (1.0f / NT) - mean * mean, 0.f);
                 rstd = 1.0f / sqrtf(var + 1e-5f);
             }
             float dp = 0.f;
-            for (int j = 0; j < NT / 32; ++j) {
+            for (int j = jlo; j < jhi; ++j) {
                 uint32_t v[32];
                 tmem_ld32(tacc + 32 * j, v);
                 if (!ln) pre(j, v);
@@ -1024,7 +1035,12 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     for (int i = 0; i < 32; ++i) dp = fmaf(x[i] * mk, spar[768 + 32 * j + i], dp);
                 }
             }
-            if (g.dp_w && valid) g.dp_out[m] = (dp + __ldg(g.dp_b)) * mk;
+            if (g.dp_w) {                                        // the row's dot product = the two halves' partial ones
+                float *const dx = reinterpret_cast<float *>(xch + 2 * kTcM);
+                if (half == 1) dx[trow] = dp;
+                asm volatile("bar.sync 2, 256;" ::: "memory");
+                if (half == 0 && valid) g.dp_out[m] = (dp + dx[trow] + __ldg(g.dp_b)) * mk;
+            }
         }
     }
     if (stamp && threadIdx.x == 64) g.stamps[4] = gtime();
