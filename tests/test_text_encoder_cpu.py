@@ -61,3 +61,22 @@ def test_no_cpu_fallback():
     m = te.TextEncoder(n_vocab=178).initialize_weights(0)
     with pytest.raises(RuntimeError):
         m(torch.zeros(1, 8, dtype=torch.long), torch.tensor([8]))
+
+
+def test_matcha_tts_state_dict_round_trip_and_errors():
+    """The MatchaTTS mirror ingests a checkpoint-shaped state_dict (encoder.* and decoder.estimator.*) and hands the same keys back."""
+    from matcha_b200.matcha_tts import MatchaTTS
+    from oracle import decoder as odec
+    we, wd = oenc.make_weights(2, "init", 178), odec.make_weights(3, "init")
+    sd = {"encoder." + k: v for k, v in we.items()}
+    sd.update({"decoder.estimator." + k: v for k, v in wd.items()})
+    m = MatchaTTS(178, precision="fp16").load_state_dict(sd)
+    out = m.state_dict()
+    assert set(out.keys()) == set(sd.keys())
+    assert torch.equal(out["encoder.encoder.ffn_layers.5.conv_net.3.weight"], sd["encoder.encoder.ffn_layers.5.conv_net.3.weight"])
+    assert torch.equal(out["decoder.estimator.final_proj.bias"], sd["decoder.estimator.final_proj.bias"])
+    assert m.encoder.precision == "fp16" and MatchaTTS(178, precision="fp32").encoder.precision == "fp32"
+    with pytest.raises(NotImplementedError):
+        MatchaTTS(178, out_channels=100)
+    with pytest.raises(RuntimeError):                                   # no CPU fallback anywhere in the flow
+        m.synthesise(torch.zeros(1, 8, dtype=torch.long), torch.tensor([8]), n_timesteps=2)
