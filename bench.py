@@ -8,8 +8,8 @@ hot path (configs[3]) and batched synthesis (configs[4]) ride along as extra key
 
 A "step" is one monotonic-alignment pass over one batch of B utterances (per GPU; weak scaling: every rank
 owns its own batch slice).  At N > 1 the step also all-gathers the alignment over NCCL in its compact form
-(the kernel's per-token durations) right behind the kernel; the dense forms of the gather are timed beside it
-under "mas_gather".  `value` is timed with inputs resident in HBM (C ABI, device pointers);
+(the kernel's per-token durations), on a high-priority side stream under the next step's kernel; the dense forms of
+the gather are timed beside it under "mas_gather".  `value` is timed with inputs resident in HBM (C ABI, device pointers);
 `e2e` goes through the host-buffer entry that mirrors core.pyx's compute_batch_alignments(paths, values,
 t_xs, t_ys) with pinned numpy buffers, H2D and D2H inside the timed region.  Prints ONE JSON line on rank 0.
 """
@@ -912,21 +912,40 @@ def run_ours(a):
     lib = load_library()
     if world > 1:
         # N > 1: the kernel also emits the per-token durations (matcha_b200_mas_align) and every step all-gathers them over
-        # NCCL right behind the kernel, on the same stream and inside the timed region.  (Measured at N = 2: the gather adds
-        # ~10 us to a step; putting it on a side stream to overlap the next kernel was slower -- the persistent MAS kernel
-        # fills every SM, so the NCCL kernel only gets in at a kernel boundary anyway, and the stream hand-offs cost more.)
-        dur = torch.empty(B, T_x, dtype=torch.int32, device=dev)
-        dur_all = torch.empty(world * B, T_x, dtype=torch.int32, device=dev)
+        # NCCL, inside the timed region.
+        # MB200_BENCH_GATHER=overlap (default): the gather of step i runs on a HIGH-PRIORITY side stream while the kernel of
+        # step i+1 runs (durations double-buffered); the persistent MAS kernel fills every SM, so the NCCL kernel's CTAs get in as the
+        # first CTAs of the running kernel retire -- with the higher priority they are placed before the next kernel's CTAs.  The
+        # collective's latency and the wait for the slowest rank then sit beside the kernel instead of behind it; the timed region
+        # ends only when the last gather has landed.  =inorder: kernel, then gather, on one stream.
+        mode = os.environ.get("MB200_BENCH_GATHER", "overlap")
+        dur = [torch.empty(B, T_x, dtype=torch.int32, device=dev) for _ in range(2)]
+        dur_all = [torch.empty(world * B, T_x, dtype=torch.int32, device=dev) for _ in range(2)]
         stream_ptr = lambda: ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        comm = torch.cuda.Stream(device=dev, priority=-1) if mode == "overlap" else None
+        gathered = [None, None]          # event of the last gather that read dur[k]
+        state = {"i": 0}
 
         def step():
-            rc = lib.matcha_b200_mas_align(path.data_ptr(), 1, dur.data_ptr(), value.data_ptr(), None, t_x.data_ptr(), t_y.data_ptr(),
+            k = state["i"] & 1
+            state["i"] += 1
+            if comm is not None and gathered[k] is not None:
+                torch.cuda.current_stream(dev).wait_event(gathered[k])          # buffer k is free: gather i-2 has finished
+            rc = lib.matcha_b200_mas_align(path.data_ptr(), 1, dur[k].data_ptr(), value.data_ptr(), None, t_x.data_ptr(), t_y.data_ptr(),
                                            B, T_x, T_y, ctypes.c_float(-1e9), None, stream_ptr())
             assert rc == 0, rc
-            dist.all_gather_into_tensor(dur_all, dur)
+            if comm is None:
+                dist.all_gather_into_tensor(dur_all[k], dur[k])
+            else:
+                comm.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(comm):
+                    dist.all_gather_into_tensor(dur_all[k], dur[k])
+                    gathered[k] = torch.cuda.Event()
+                    gathered[k].record(comm)
 
         def finish():
-            pass
+            if comm is not None:
+                torch.cuda.current_stream(dev).wait_stream(comm)
     else:
         def step():
             ma.maximum_path_from_lengths(value, t_x, t_y, out=path)
@@ -1042,8 +1061,9 @@ def run_ours(a):
                        "l2": "inputs+outputs 6.5 GB per step >> 126 MB L2, no flush needed",
                        "launch": {"grid": out[0], "block": out[1], "smem": out[2], "rows_per_lane": out[3],
                                   "stages": out[4], "tma": out[5], "ctas_per_sm": out[6]},
-                       "parallelism": (f"batch-sharded x{world}; every step all-gathers the alignment (compact: int32 durations) over NCCL "
-                                       f"right behind the kernel, inside the timed region") if world > 1 else "single GPU, no collective"},
+                       "parallelism": (f"batch-sharded x{world}; every step all-gathers the alignment (compact: int32 durations) over NCCL, "
+                                       + ("on a high-priority side stream under the next step's kernel" if os.environ.get("MB200_BENCH_GATHER", "overlap") == "overlap"
+                                          else "right behind the kernel on the same stream") + ", inside the timed region") if world > 1 else "single GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                          "kernel_ms": k_ms, "kernel": "mas_kernel<R,HAS_MASK=false>"},
