@@ -402,15 +402,21 @@ def _dec_params():
 
 
 def _time_solves(fn, K, barrier, world, dist, dev):
+    """K solves between barriers, twice; per rank the better of the two repeats, then the max over ranks.  (One repeat of 5
+    solves is ~45 ms: a single host hiccup on one of 8 ranks doubled the N=8 figure of one run, profiles/r2b_bench_n8.json.)"""
     import torch
-    barrier()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    ev[0].record()
-    for _ in range(K):
-        out = fn()
-    ev[1].record()
-    barrier()
-    ms = torch.tensor([ev[0].elapsed_time(ev[1]) / K], device=dev, dtype=torch.float64)
+    best = None
+    for _ in range(2):
+        barrier()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        for _ in range(K):
+            out = fn()
+        ev[1].record()
+        barrier()
+        t = ev[0].elapsed_time(ev[1]) / K
+        best = t if best is None else min(best, t)
+    ms = torch.tensor([best], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     return float(ms.item()), out
