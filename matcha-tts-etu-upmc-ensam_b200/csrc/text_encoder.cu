@@ -700,12 +700,15 @@ te_mean_proj_kernel(const float *__restrict__ x, const float *__restrict__ w, co
 //   warp 0      TMA producer: A boxes (64 channels x 128 frames of one sample) from a 3-D map over the fp16 activation
 //               [B][T][Cin] -- the conv taps are row offsets, frames outside [0, T) come back as zeros = the conv's zero
 //               padding -- and W boxes (64 x NT) from a 2-D map over the fp16 weight [N][K], K = tap * Cin + channel; both
-//               land in the 128B-swizzled K-major layout the UMMA shared-memory descriptor describes.  4-stage ring.
+//               land in the 128B-swizzled K-major layout the UMMA shared-memory descriptor describes.  4-stage ring (3 when a
+//               residual tile shares the shared memory).
 //   warp 1      allocates 256 TMEM columns and issues tcgen05.mma (one lane; UMMA 128 x NT x 16, four per stage);
 //               tcgen05.commit frees the stage / publishes the accumulator.
-//   warps 2..5  epilogue, thread = output row = TMEM lane: bias, ReLU, mask, residual; LayerNorm over the row's NT columns
-//               in two passes over TMEM (pass 1 forms the pre-norm values, writes them back with tcgen05.st and sums;
-//               pass 2 normalises); fp32 and / or fp16 stores (the fp16 copy optionally x mask: the next conv's operand);
+//   warps 2..9  epilogue, thread = output row = TMEM lane, two warps per lane quarter, each owning half of the tile's columns:
+//               bias, ReLU, mask, residual; LayerNorm over the row's NT columns in two passes over TMEM (pass 1 forms the
+//               pre-norm values, writes them back with tcgen05.st and sums -- the two halves' sums cross through shared
+//               memory; pass 2 normalises); RoPE for the q / k tiles of the fused projection (one head per warp); fp32 and / or
+//               fp16 stores through a swizzled shared-memory tile (the fp16 copy optionally x mask: the next conv's operand);
 //               the duration predictor's 256 -> 1 projection as a per-row dot product.
 // One 128-row tile per CTA (grid = B * ceil(T / 128) x N / NT): the encoder's GEMMs have 32-100 tiles, fewer than SMs.
 constexpr int kTcMaxStages = 4, kTcM = 128, kTcK = 64, kTcStageA = kTcM * kTcK * 2;
