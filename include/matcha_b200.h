@@ -54,6 +54,8 @@ const char *matcha_b200_version(void);
  *               outer product of two prefix masks built at matcha_tts.py:271.
  *   t_xs_dev, t_ys_dev  [B] int32 valid lengths.
  *   penalty     boundary_penalty / max_neg_val (-1e9 in the reference).
+ *   Shapes the wavefront kernel does not take (T_x > 1344, or a stage ring beyond shared memory) run on a slower one-CTA-per-
+ *   utterance fallback with the same results; MB200_ERR_UNSUPPORTED only when T_x exceeds ~14 000.
  *   status_dev  NULL, or one int32 that receives (atomically added) the number of items
  *               whose lengths violate 1 <= t_x <= t_y, t_x <= T_x, t_y <= T_y.  The reference
  *               has undefined behaviour for those; here their path is all zeros.

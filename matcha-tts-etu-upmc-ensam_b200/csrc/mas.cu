@@ -515,6 +515,81 @@ mas_kernel(const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ C
     }
 }
 
+
+// ------------------------------------------------------------------ fallback for tall inputs
+// Inputs the wavefront kernel does not take (T_x > 1344 tokens, or a stage ring that does not fit shared memory): one CTA per
+// utterance, the DP column in shared memory, one __syncthreads per mel frame, a single-thread backtrack.  The same arithmetic
+// (core.pyx:52-92: one __fadd_rn per cell, `prev >= same` ties to the diagonal, forced diagonal at x == y, penalty outside the
+// band) and the same bit words parked at the head of the utterance's own output slab; ~1 us per frame, i.e. a correctness path for
+// shapes the reference accepts (it takes any T_x), not a fast one.
+__global__ void __launch_bounds__(256)
+mas_tall_kernel(const MasParams p) {
+    extern __shared__ __align__(16) uint8_t tall_smem[];
+    float *qa = reinterpret_cast<float *>(tall_smem), *qb = qa + p.T_x;
+    uint32_t *bw = reinterpret_cast<uint32_t *>(qb + p.T_x);          // this chunk's "came from x-1" bits, one word per token
+    int *cs = reinterpret_cast<int *>(bw + p.T_x);                    // [T_x + 1] first frame of every token
+    const int tid = threadIdx.x;
+    const size_t n = (size_t)p.T_x * p.T_y;
+    const float P = p.penalty;
+    for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
+        const int tx = p.t_xs[b], ty = p.t_ys[b];
+        const bool valid = tx >= 1 && tx <= ty && tx <= p.T_x && ty <= p.T_y;
+        uint32_t *out = p.out + (size_t)b * n;
+        if (valid) {
+            const float *V = p.value + (size_t)b * n;
+            const float *Mk = p.mask ? p.mask + (size_t)b * n : nullptr;
+            for (int x = tid; x < tx; x += 256) { qa[x] = P; bw[x] = 0u; }
+            __syncthreads();
+            float *prev = qa, *cur = qb;
+            for (int y = 0; y < ty; ++y) {
+                const int lo = max(0, tx + y - ty), hi = min(tx, y + 1);
+                const bool flush = (y & 31) == 31 || y == ty - 1;
+                for (int x = tid; x < tx; x += 256) {                 // a token stays with its thread: bw[x] needs no barrier
+                    float q = P;
+                    if (x >= lo && x < hi) {
+                        const float pv = (x == 0) ? (y == 0 ? 0.0f : P) : prev[x - 1];
+                        const float sm = (x == y) ? P : (y > 0 ? prev[x] : P);
+                        const bool diag = (pv >= sm) || (x == y);
+                        float sc = V[(size_t)x * p.T_y + y];
+                        if (Mk) sc = __fmul_rn(sc, Mk[(size_t)x * p.T_y + y]);
+                        q = __fadd_rn(diag ? pv : sm, sc);
+                        if (diag) bw[x] |= 1u << (y & 31);
+                    }
+                    cur[x] = q;
+                    if (flush) { out[(size_t)(y >> 5) * p.T_x + x] = bw[x]; bw[x] = 0u; }
+                }
+                __syncthreads();
+                float *t = prev; prev = cur; cur = t;
+            }
+            if (tid == 0) {                                           // core.pyx:87-92
+                int idx = tx - 1;
+                cs[tx] = ty;
+                for (int y = ty - 1; y > 0; --y) {
+                    const uint32_t wv = __ldcg(out + (size_t)(y >> 5) * p.T_x + idx);
+                    if (idx > 0 && (idx == y || ((wv >> (y & 31)) & 1u))) { cs[idx] = y; --idx; }
+                }
+                for (int x = idx; x >= 0; --x) cs[x] = 0;             // idx is 0 here for valid lengths (the forced diagonal)
+            }
+        }
+        __syncthreads();
+        for (size_t i = tid; i < n; i += 256) __stcs(out + i, 0u);
+        __syncthreads();
+        if (valid) {
+            for (int x = tid; x < tx; x += 256) {
+                uint32_t *row = out + (size_t)x * p.T_y;
+                for (int c = cs[x]; c < cs[x + 1]; ++c) __stcs(row + c, p.one_bits);
+            }
+        } else if (tid == 0 && p.status != nullptr) {
+            atomicAdd(p.status, 1);
+        }
+        if (p.durations != nullptr) {
+            int *d = p.durations + (size_t)b * p.T_x;
+            for (int x = tid; x < p.T_x; x += 256) d[x] = (valid && x < tx) ? cs[x + 1] - cs[x] : 0;
+        }
+        __syncthreads();
+    }
+}
+
 // t_xs[b] = (int) sum_x mask[b][x][0], t_ys[b] = (int) sum_y mask[b][0][y]  (__init__.py:52-53)
 __global__ void __launch_bounds__(128)
 mas_lengths_kernel(const float *__restrict__ mask, int T_x, int T_y, int *__restrict__ t_xs,
@@ -671,6 +746,20 @@ static int mas_launch(
                            (!has_mask || (uintptr_t)mask_dev % 16 == 0);
     MasPlan pl;
     int rc = mas_make_plan(B, T_x, T_y, has_mask, aligned16, &pl);
+    if (rc == MB200_ERR_UNSUPPORTED) {
+        // taller than the wavefront kernel takes: the one-CTA-per-utterance fallback (any T_x whose DP columns fit shared memory)
+        const size_t smem = (size_t)(4 * T_x + 4) * 4;
+        if (smem > (size_t)kMaxSmemPerBlock) return MB200_ERR_UNSUPPORTED;
+        MB200_CUDA_TRY(cudaFuncSetAttribute(mas_tall_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MasParams p = {};
+        p.value = values_dev; p.mask = mask_dev; p.out = (uint32_t *)paths_dev;
+        p.t_xs = t_xs_dev; p.t_ys = t_ys_dev; p.status = status_dev; p.durations = durations_dev;
+        p.B = B; p.T_x = T_x; p.T_y = T_y; p.penalty = penalty;
+        p.one_bits = (path_dtype == MB200_PATH_F32) ? 0x3f800000u : 1u;
+        mas_tall_kernel<<<B < 2 * kNumSMsB200 ? B : 2 * kNumSMsB200, 256, smem, (cudaStream_t)stream>>>(p);
+        MB200_CUDA_TRY(cudaGetLastError());
+        return MB200_OK;
+    }
     if (rc != MB200_OK) return rc;
     pl.vec_store = (T_y % 4 == 0) && ((uintptr_t)paths_dev % 16 == 0);
 

@@ -203,3 +203,39 @@ def test_band_edge_many_utterances_per_cta(ma):
     m[::3] = gen.ragged_mask(rng, B, T_x, T_y, lo=0.6)[::3]
     want = omas.maximum_path_oracle(v, m)
     assert np.array_equal(_run(ma, v, m, mask_mode="prefix"), want)
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# Inputs taller than the wavefront kernel takes (T_x > 1344): the one-CTA-per-utterance fallback (mas_tall_kernel).  The
+# reference accepts any T_x (core.pyx:16-96), so these are parity cases like any other.
+@pytest.mark.parametrize("mask_mode", ["prefix", "full"])
+def test_tall_inputs_take_the_fallback_kernel(ma, mask_mode):
+    rng = np.random.default_rng(77)
+    B, T_x, T_y = 3, 1400, 1500
+    v = rng.standard_normal((B, T_x, T_y), dtype=np.float32)
+    m = np.zeros((B, T_x, T_y), np.float32)
+    lens = [(1400, 1500), (1377, 1377), (901, 1432)]                               # full length, t_x == t_y, ragged
+    for b, (tx, ty) in enumerate(lens):
+        m[b, :tx, :ty] = 1
+    want = omas.maximum_path_oracle(v, m)
+    got = _run(ma, v, m, mask_mode=mask_mode)
+    assert np.array_equal(got, want)
+    check_path_properties(got, [l[0] for l in lens], [l[1] for l in lens])
+
+
+def test_tall_inputs_ties_and_durations(ma):
+    """Dense ties (quantised scores) through the fallback, and the per-token durations it emits."""
+    from matcha_b200 import alignment as al
+    rng = np.random.default_rng(78)
+    B, T_x, T_y = 2, 1350, 1400
+    v = np.round(rng.standard_normal((B, T_x, T_y)) * 2).astype(np.float32)
+    tx, ty = np.array([1350, 1203], np.int32), np.array([1400, 1399], np.int32)
+    m = np.zeros((B, T_x, T_y), np.float32)
+    for b in range(B):
+        m[b, :tx[b], :ty[b]] = 1
+    want = omas.maximum_path_oracle(v, m)
+    dev = torch.device("cuda:0")
+    path, dur = al.maximum_path_with_durations(torch.from_numpy(v).to(dev), torch.from_numpy(tx).to(dev), torch.from_numpy(ty).to(dev))
+    torch.cuda.synchronize()
+    assert np.array_equal(path.cpu().numpy().astype(np.int32), want)
+    assert np.array_equal(dur.cpu().numpy(), want.sum(-1).astype(np.int32))
