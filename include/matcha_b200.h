@@ -6,7 +6,7 @@
  * All *_dev pointers are device pointers on the current CUDA device; `stream` is a
  * cudaStream_t passed as void* (NULL = legacy default stream).  Device entry points
  * are asynchronous on `stream`, thread-safe and allocate no device memory.  The MAS / alignment entry points keep no
- * state at all.  The decoder entry points keep, per DEVICE and behind a mutex, the opt-in shared-memory attribute of
+ * state at all (matcha_b200_mas_durations_static alone caches, per device, the address of its built-in slab).  The decoder entry points keep, per DEVICE and behind a mutex, the opt-in shared-memory attribute of
  * their kernels and the side streams + events of the sub-batch split (created on first use; a call holds the device's
  * mutex while it enqueues, so two host threads driving one device queue their calls one after the other).
  *
@@ -119,6 +119,41 @@ int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int alig
 int matcha_b200_mas_align(
     void *paths_dev, int path_dtype, int *durations_dev,
     const float *values_dev, const float *mask_dev,
+    const int *t_xs_dev, const int *t_ys_dev,
+    int B, int T_x, int T_y, float penalty,
+    int *status_dev, void *stream);
+
+/*
+ * Durations only, with no device buffer beyond the inputs and the [B][T_x] output.  (No counterpart in the reference: its
+ * Cython core mallocs its own scratch, core.pyx:39-41; this entry point exists for GPU callers that may not allocate.)
+ *
+ * The MAS kernel always needs a [B][T_x][T_y] slab of 4-byte cells: it parks the DP's decision bits there and then lays the
+ * dense path over them.  matcha_b200_mas_align borrows the caller's paths buffer for that.  This variant uses a fixed array
+ * of MB200_MAS_STATIC_MAX_CELLS cells (8 MiB) that is part of the library's device image, so it makes no cudaMalloc / cudaFree
+ * call and needs no allocator on the caller's side.  It is meant for
+ *   - a host thread that aligns batches while another thread captures a decoder solve into a CUDA graph: cudaMalloc from any
+ *     thread breaks a global-mode capture;
+ *   - a C / ctypes caller (e.g. a duration-extraction script) sharing the GPU with a trainer whose caching allocator has
+ *     already claimed the memory, where a cudaMalloc can fail, and in any case synchronises the whole device;
+ *   - serving loops that keep cudaMalloc off the request path.
+ * durations_dev, values_dev, mask_dev, t_xs_dev, t_ys_dev, penalty, status_dev, stream: exactly as matcha_b200_mas_align;
+ * the result is identical to its durations_dev.  The dense path is not returned.
+ *
+ * Limits and sharing:
+ *   - B*T_x*T_y <= MB200_MAS_STATIC_MAX_CELLS (matcha_b200_mas_durations_static_max_cells() returns it), e.g. 16 x 128 x 800;
+ *     anything larger returns MB200_ERR_UNSUPPORTED and launches nothing.  Split the batch, or use matcha_b200_mas_align.
+ *   - Every GPU on which the library's kernels are loaded holds its own 8 MiB copy until the process exits.
+ *   - The first call on each device looks the array's device address up (cudaGetSymbolAddress with that device current) and
+ *     caches it; make that first call outside any stream capture.  Later calls only enqueue the kernel.
+ *   - All calls on one device share the one array and it keeps whatever the last call wrote.  Nothing in it has to be
+ *     cleared between calls (every cell is rewritten before it is read), but two calls that may run on the GPU at the
+ *     same time -- different streams, or different host threads without a common stream -- race on it and both results
+ *     are then garbage.  Put such calls on one stream, or order them with events.
+ */
+#define MB200_MAS_STATIC_MAX_CELLS (2 * 1024 * 1024)
+long long matcha_b200_mas_durations_static_max_cells(void);
+int matcha_b200_mas_durations_static(
+    int *durations_dev, const float *values_dev, const float *mask_dev,
     const int *t_xs_dev, const int *t_ys_dev,
     int B, int T_x, int T_y, float penalty,
     int *status_dev, void *stream);

@@ -29,6 +29,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 namespace mb200 {
 
 constexpr int kChunk = 32;        // mel frames per tile
@@ -849,6 +851,62 @@ extern "C" int matcha_b200_mas_apply_mask(float *scores_dev, const float *values
     mas_apply_mask_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(scores_dev, values_dev, mask_dev, (size_t)n);
     MB200_CUDA_TRY(cudaGetLastError());
     return MB200_OK;
+}
+
+// ------------------------------------------------------------------ durations without a caller-side slab
+// matcha_b200_mas_durations_static: the same kernels as matcha_b200_mas_align, for a caller that wants only the per-token
+// durations and has no [B][T_x][T_y] buffer to lend.  The wavefront kernel needs that slab whatever the caller asks for: the
+// "came from x-1" bit words of the DP are parked in it until the backtrack has read them, and the dense 0/1 path is laid over
+// them afterwards.  Here the slab is a fixed array in the library's own device image, so the call performs no allocation.
+// Who needs this: a host thread that runs alignments beside a thread that is capturing one of this library's decoder solves
+// into a CUDA graph (cudaMalloc from ANY thread is illegal during a global-mode capture and poisons it); a plain C / ctypes
+// binding of the reference's data-prep scripts that shares the GPU with a training process whose caching allocator already
+// holds nearly all of the memory, so a 6.5 MB cudaMalloc may fail or stall on the implicit device synchronisation; and
+// latency-sensitive serving loops that forbid cudaMalloc / cudaFree on the request path for the same synchronisation.
+//
+// In HOST code `g_mas_static_slab` is only a handle for the runtime's symbol table, not a device address, so it is never
+// handed to a kernel; each device's real address comes from cudaGetSymbolAddress, asked once per device with that device
+// current (every device that loads the library has its own copy of the array), and is cached below.
+static __device__ __align__(256) uint32_t g_mas_static_slab[MB200_MAS_STATIC_MAX_CELLS];
+
+namespace {
+constexpr int kSlabMaxDevices = 64;
+std::mutex g_slab_mu;
+uint32_t *g_slab_addr[kSlabMaxDevices] = {};   // device address of g_mas_static_slab on device i, nullptr = not asked yet
+
+// Address of the current device's copy of the slab (first call per device: one cudaGetSymbolAddress, no allocation).
+int mas_static_slab(uint32_t **out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kSlabMaxDevices) { (void)cudaGetLastError(); return MB200_ERR_NO_DEVICE; }
+    std::lock_guard<std::mutex> lock(g_slab_mu);
+    if (g_slab_addr[dev] == nullptr) {
+        void *ptr = nullptr;
+        MB200_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_mas_static_slab));
+        if (ptr == nullptr) return MB200_ERR_CUDA;
+        g_slab_addr[dev] = static_cast<uint32_t *>(ptr);
+    }
+    *out = g_slab_addr[dev];
+    return MB200_OK;
+}
+}  // namespace
+
+extern "C" long long matcha_b200_mas_durations_static_max_cells(void) { return (long long)MB200_MAS_STATIC_MAX_CELLS; }
+
+extern "C" int matcha_b200_mas_durations_static(
+    int *durations_dev, const float *values_dev, const float *mask_dev, const int *t_xs_dev, const int *t_ys_dev,
+    int B, int T_x, int T_y, float penalty, int *status_dev, void *stream) {
+    if (B < 0 || T_x <= 0 || T_y <= 0) return MB200_ERR_INVALID_ARG;
+    if (B == 0) return MB200_OK;
+    if (!durations_dev || !values_dev || !t_xs_dev || !t_ys_dev) return MB200_ERR_INVALID_ARG;
+    // the whole batch's slab must fit the fixed array: refuse, never truncate or spill into an allocation
+    if ((long long)B * T_x * T_y > (long long)MB200_MAS_STATIC_MAX_CELLS) return MB200_ERR_UNSUPPORTED;
+    uint32_t *slab = nullptr;
+    const int rc = mas_static_slab(&slab);
+    if (rc != MB200_OK) return rc;
+    // Nothing in the slab has to start at zero: the kernels write every bit word before the backtrack reads it and overwrite
+    // all B*T_x*T_y cells with the dense path, so whatever the previous call left behind is never read.
+    return mas_launch(slab, MB200_PATH_I32, values_dev, mask_dev, t_xs_dev, t_ys_dev, B, T_x, T_y, penalty,
+                      status_dev, durations_dev, stream);
 }
 
 // profiling aid, not part of the public header: copies the clock64 stamps out

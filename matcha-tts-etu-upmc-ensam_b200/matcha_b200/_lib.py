@@ -63,6 +63,11 @@ def load_library():
     lib.matcha_b200_mas_align.argtypes = [
         c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
         c_int, c_int, c_int, c_float, c_void_p, c_void_p]
+    lib.matcha_b200_mas_durations_static_max_cells.restype = ll
+    lib.matcha_b200_mas_durations_static.restype = c_int
+    lib.matcha_b200_mas_durations_static.argtypes = [
+        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_int, c_int, c_int, c_float, c_void_p, c_void_p]
     lib.matcha_b200_align_log_prior.restype = c_int
     lib.matcha_b200_align_log_prior.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                                 c_int, c_int, c_int, c_int, c_void_p]
@@ -127,6 +132,8 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_query_launch",
     "matcha_b200_mas_apply_mask",
     "matcha_b200_mas_align",
+    "matcha_b200_mas_durations_static_max_cells",
+    "matcha_b200_mas_durations_static",
     "matcha_b200_align_log_prior",
     "matcha_b200_align_expand",
     "matcha_b200_cfm_loss_mix",
