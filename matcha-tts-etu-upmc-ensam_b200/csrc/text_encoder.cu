@@ -40,26 +40,35 @@ namespace te {
 constexpr int kC = 192, kF = 768, kH = 2, kD = 96, kRope = 48, kL = 6, kDp = 256, kFeats = 80;
 constexpr int kPreK = 5, kPreL = 3, kK = 3;
 
-// Programmatic dependent launch.  These kernels are short (5-20 us), so the chain lives on how early the next launch can be
-// made resident: every kernel triggers its dependents at the top and then waits (TE_PDL_EARLY = 1), which lets three or four
-// kernels of the chain sit resident and waiting at once.  Ordering is safe by construction (a kernel cannot complete before
-// its own wait has returned, so completion is transitive), but VISIBILITY is not: griddepcontrol.wait only promises that the
-// prerequisite grid's writes are visible.  A CTA made resident while kernel N still ran can find, in its SM's L1, a line
-// kernel N read there (old contents) after kernel N+2 has rewritten it in L2 -- its own L1 invalidation happened at launch,
-// before kernel N's read.  With plain loads that returned wrong results from the second encoder layer on, on two of six
-// boxes (profiles/r2_te_pdl_race.log: x is read by the out-projection as residual, rewritten by FFN2, read by the next
+// Programmatic dependent launch.  Every kernel of the chain runs te_pdl_entry() in every thread at its top: griddepcontrol.wait,
+// then griddepcontrol.launch_dependents (TE_PDL_EARLY = 0, the shipped order) -- a kernel lets its successor become resident only
+// after its own wait has returned, so at most two kernels of the chain are in flight and the successor's prologue (barriers,
+// TMEM allocation, descriptors, parameter loads) overlaps this kernel's body.  Ordering is transitive (a kernel cannot complete
+// before its own wait has returned).  VISIBILITY is the delicate part: griddepcontrol.wait only promises that the prerequisite
+// grid's writes are visible.  A CTA made resident while kernel N still ran can find, in its SM's L1, a line kernel N read there
+// (old contents) after kernel N+2 has rewritten it in L2 -- its own L1 invalidation happened at launch, before kernel N's read.
+// A round-2 build that triggered before waiting, with plain loads, returned wrong results from the second encoder layer on, on
+// two of six boxes (profiles/r2_te_pdl_race.log: x is read by the out-projection as residual, rewritten by FFN2, read by the next
 // q|k|v projection).  Hence the rule of this file: every tensor that a kernel of the chain writes is read through L2 only
 // -- ld.global.cg (ld_act*), cp.async.cg, or TMA -- and only weights, biases and the RoPE tables use the default path.
-// TE_PDL_EARLY = 0 (wait first, then trigger: at most two kernels in flight) and TE_LDCG = 0 are kept as A/B switches.
+// History: between ece6bc9 and round 3 this helper was called pdl_prologue() and, with TE_PDL_EARLY = 1, called
+// ITSELF; nvcc deleted the call, so the shipped kernels carried no griddepcontrol instruction at all although they were launched
+// with the PDL attribute.  Round 3 measured the three builds on one box (profiles/r3_te_pdl_ab.log): trigger-then-wait (TE_PDL_EARLY
+// = 1, now real) 440 / 539 / 429 us at 32x128 / 8x128 / 1x128 fp16, wait-then-trigger 437 / 413 / 406 us, both bit-stable over 300
+// graph replays and equal to the fp64 restatement within tolerance.  The early trigger buys nothing here (three resident waiting
+// kernels take SM slots from the one that runs), so the conservative order ships.  tests/test_cabi_cpu.py checks the SASS of
+// every te_* kernel for the wait (ACQBULK) so that the instruction cannot silently disappear again.
+// TE_PDL_EARLY = 1 and TE_LDCG = 0 are kept as A/B switches.
 #ifndef TE_PDL_EARLY
-#define TE_PDL_EARLY 1
+#define TE_PDL_EARLY 0
 #endif
 #ifndef TE_LDCG
 #define TE_LDCG 1
 #endif
-__device__ __forceinline__ void pdl_prologue() {
+__device__ __forceinline__ void te_pdl_entry() {    // named apart from every helper in common.cuh: it must never resolve to itself
 #if TE_PDL_EARLY
-    pdl_prologue();
+    pdl_launch_dependents();
+    pdl_wait();
 #else
     pdl_wait();
     pdl_launch_dependents();
@@ -92,7 +101,7 @@ __device__ __forceinline__ float4 ld_act4(const float *p) {
 __global__ void __launch_bounds__(256)
 te_embed_kernel(const long long *__restrict__ ids, const int *__restrict__ lengths, const float *__restrict__ emb,
                 int n_vocab, float *__restrict__ x0, __half *__restrict__ x0_16, float *__restrict__ mask, int B, int T) {
-    pdl_prologue();
+    te_pdl_entry();
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= B * T) return;
@@ -147,7 +156,7 @@ te_gemm_kernel(const GemmArgs g) {
     constexpr int NB4 = NT * 16 / 4 / 256;        // float4 weight loads per thread per 16-wide K chunk
     __shared__ __align__(16) float As[2][16][PA];
     __shared__ __align__(16) float Bs[2][16][PB];
-    pdl_prologue();
+    te_pdl_entry();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int M = g.B * g.T;
     const int m0 = blockIdx.x * 32, n0 = blockIdx.y * NT;
@@ -328,7 +337,7 @@ te_attention_kernel(const float *__restrict__ qkv, const float *__restrict__ mas
     const uint32_t sm0 = smem_u32(att_smem);
     const bool stamp = stamps && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0;
     if (stamp) stamps[0] = gtime();
-    pdl_prologue();
+    te_pdl_entry();
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * kAQ;
     const int tid = threadIdx.x, r = tid >> 2, quarter = tid & 3;
     const int tq = q0 + r;
@@ -512,7 +521,7 @@ te_attention_mma_kernel(const __half *__restrict__ qkv, const float *__restrict_
     const uint32_t sQ = smem_u32(ma_smem);
     const uint32_t sKV = sQ + kMaBQ * kMaPitch;                 // [buf][K | V][64 rows][256 B]
     const float *sMf = reinterpret_cast<const float *>(ma_smem + kMaBQ * kMaPitch + 4 * kMaTile);
-    pdl_prologue();
+    te_pdl_entry();
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * kMaBQ;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const __half *base = qkv + (size_t)b * T * (3 * kC) + h * kD;
@@ -666,7 +675,7 @@ __global__ void __launch_bounds__(256)
 te_mean_proj_kernel(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ bias,
                     const float *__restrict__ mask, float *__restrict__ mu, int T) {
     __shared__ float A[32][kC + 1];
-    pdl_prologue();
+    te_pdl_entry();
     const int b = blockIdx.y, t0 = blockIdx.x * 32, tid = threadIdx.x;
     for (int i = tid; i < 32 * kC; i += 256) {
         const int tt = i / kC, c = i - tt * kC;
@@ -838,7 +847,7 @@ te_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             spar[768 + i] = g.dp_w ? g.dp_w[n0 + i] : 0.f;
         }
     }
-    pdl_prologue();              // barriers, TMEM, descriptors and parameters were set up while the previous kernel drained
+    te_pdl_entry();              // barriers, TMEM, descriptors and parameters were set up while the previous kernel drained
     if (stamp && threadIdx.x == 0) g.stamps[1] = gtime();
 
     if (warp == 0) {
