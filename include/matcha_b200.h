@@ -110,6 +110,22 @@ int matcha_b200_mas_apply_mask(float *scores_dev, const float *values_dev, const
  * out[7]=DP warps per CTA. */
 int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mask, int aligned16, int out[8]);
 
+/* Which kernel a launch with this shape takes (matcha_b200_mas_query_launch describes the wavefront kernel only and
+ * returns MB200_ERR_UNSUPPORTED where matcha_b200_mas_compute_batch_alignments / _align still succeed on the fallback):
+ *   MB200_MAS_PATH_WAVEFRONT       the TMA-fed wavefront kernel (the fast path)
+ *   MB200_MAS_PATH_TALL            the one-CTA-per-utterance fallback (T_x > 1344): same results, ~1 us per mel frame
+ *   MB200_MAS_PATH_TALL_MASK_ONLY  has_mask = 1 and only the fused-mask stage ring does not fit (T_x roughly 900..1344): the
+ *                                  launch would run the slow fallback, although the wavefront kernel takes this shape WITHOUT a
+ *                                  mask.  A direct C caller should form value*mask with matcha_b200_mas_apply_mask into a buffer
+ *                                  of their own and pass mask_dev = NULL (what matcha_b200.monotonic_align.maximum_path does); the
+ *                                  library cannot do that itself because it allocates no device memory.
+ *   MB200_ERR_UNSUPPORTED          no kernel takes the shape (T_x beyond ~14 000)
+ * Needs no device.  (No counterpart in the reference.) */
+#define MB200_MAS_PATH_WAVEFRONT       0
+#define MB200_MAS_PATH_TALL            1
+#define MB200_MAS_PATH_TALL_MASK_ONLY  2
+int matcha_b200_mas_query_path(int B, int T_x, int T_y, int has_mask, int aligned16);
+
 /*
  * maximum_path plus the compact form of the result: durations_dev [B][T_x] int32 (may be NULL) receives the
  * number of frames each token owns (= sum_y path[b][x][y], what matcha_tts.py:287 reduces the path to; 0

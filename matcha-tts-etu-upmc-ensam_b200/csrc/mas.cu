@@ -831,6 +831,19 @@ extern "C" int matcha_b200_mas_query_launch(int B, int T_x, int T_y, int has_mas
     return MB200_OK;
 }
 
+// Which kernel mas_launch takes for a shape: the same plan logic, no device needed.
+extern "C" int matcha_b200_mas_query_path(int B, int T_x, int T_y, int has_mask, int aligned16) {
+    if (B <= 0 || T_x <= 0 || T_y <= 0) return MB200_ERR_INVALID_ARG;
+    if ((long long)B * T_x > 0x7fffffffLL) return MB200_ERR_UNSUPPORTED;
+    MasPlan pl;
+    int rc = mas_make_plan(B, T_x, T_y, has_mask != 0, aligned16 != 0, &pl);
+    if (rc == MB200_OK) return MB200_MAS_PATH_WAVEFRONT;
+    if (rc != MB200_ERR_UNSUPPORTED) return rc;
+    if (has_mask && mas_make_plan(B, T_x, T_y, false, aligned16 != 0, &pl) == MB200_OK) return MB200_MAS_PATH_TALL_MASK_ONLY;
+    if ((size_t)(4 * (size_t)T_x + 4) * 4 > (size_t)kMaxSmemPerBlock) return MB200_ERR_UNSUPPORTED;
+    return MB200_MAS_PATH_TALL;
+}
+
 extern "C" int matcha_b200_mas_lengths_from_mask(const float *mask_dev, int B, int T_x, int T_y,
                                                   int *t_xs_dev, int *t_ys_dev, void *stream) {
     if (B < 0 || T_x <= 0 || T_y <= 0) return MB200_ERR_INVALID_ARG;

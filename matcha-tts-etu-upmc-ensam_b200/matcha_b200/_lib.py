@@ -56,6 +56,8 @@ def load_library():
     lib.matcha_b200_mas_host_release.restype = c_int
     lib.matcha_b200_mas_query_launch.restype = c_int
     lib.matcha_b200_mas_query_launch.argtypes = [c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int * 8)]
+    lib.matcha_b200_mas_query_path.restype = c_int
+    lib.matcha_b200_mas_query_path.argtypes = [c_int, c_int, c_int, c_int, c_int]
     lib.matcha_b200_mas_apply_mask.restype = c_int
     lib.matcha_b200_mas_apply_mask.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_void_p]
     ll = ctypes.c_longlong
@@ -130,6 +132,7 @@ DECLARED_SYMBOLS = (
     "matcha_b200_mas_maximum_path_host_h",
     "matcha_b200_mas_host_release",
     "matcha_b200_mas_query_launch",
+    "matcha_b200_mas_query_path",
     "matcha_b200_mas_apply_mask",
     "matcha_b200_mas_align",
     "matcha_b200_mas_durations_static_max_cells",

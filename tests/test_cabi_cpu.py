@@ -65,6 +65,20 @@ def test_unsupported_shape_is_reported(lib):
     assert lib.matcha_b200_mas_query_launch(1, 1400, 4000, 0, 1, ctypes.byref(out)) == -2
 
 
+def test_query_path_agrees_with_what_the_launch_does(lib):
+    q = lib.matcha_b200_mas_query_path
+    assert q(16, 128, 800, 0, 1) == 0 and q(16, 128, 800, 1, 1) == 0          # wavefront kernel, with or without the mask
+    assert q(1024, 400, 2000, 1, 1) == 0
+    assert q(1, 1400, 1500, 0, 1) == 1 and q(1, 1400, 1500, 1, 1) == 1        # taller than the wavefront kernel: fallback
+    assert q(1, 1200, 1500, 0, 1) == 0 and q(1, 1200, 1500, 1, 1) == 2        # only the fused-mask ring does not fit
+    assert q(1, 20000, 20000, 0, 1) == -2 and q(0, 4, 4, 0, 1) == -1
+    out = (ctypes.c_int * 8)()
+    for shape in [(2, 64, 200), (2, 1200, 1500), (1, 1400, 1500)]:            # query_launch == OK exactly on the wavefront path
+        for has_mask in (0, 1):
+            rc = lib.matcha_b200_mas_query_launch(*shape, has_mask, 1, ctypes.byref(out))
+            assert (rc == 0) == (q(*shape, has_mask, 1) == 0)
+
+
 def test_no_cpu_fallback_without_cuda():
     import torch
     if torch.cuda.is_available():
@@ -72,3 +86,36 @@ def test_no_cpu_fallback_without_cuda():
     from matcha_b200 import monotonic_align
     with pytest.raises(RuntimeError):
         monotonic_align.maximum_path(torch.zeros(1, 2, 3), torch.ones(1, 2, 3))
+
+
+def test_pdl_kernels_carry_the_wait(lib):
+    """Every kernel the library launches with the programmatic-dependent-launch attribute (all text-encoder kernels,
+    text_encoder.cu launch_smem; all decoder kernels, decoder.cu launch helper) must execute griddepcontrol.wait
+    (SASS: ACQBULK) and griddepcontrol.launch_dependents (SASS: PREEXIT).  Round 2 shipped text-encoder kernels
+    whose PDL helper called itself; nvcc dropped the call without a diagnostic and the kernels ran with the launch
+    attribute and no wait."""
+    import shutil
+    import subprocess
+    from matcha_b200._lib import lib_path
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.run([cuobjdump, "-sass", lib_path()], capture_output=True, text=True, check=True).stdout
+    wait, trigger, fn = {}, {}, None
+    for line in sass.splitlines():
+        if "Function :" in line:
+            fn = line.split("Function :")[1].strip()
+            wait[fn], trigger[fn] = 0, 0
+        elif fn is not None:
+            wait[fn] += "ACQBULK" in line
+            trigger[fn] += "PREEXIT" in line
+    te = [f for f in wait if "5mb2002te" in f]
+    assert len(te) >= 8, te
+    decoder = [f for f in wait if any(k in f for k in (
+        "gemm_bf16_kernel", "gemm_abuild_kernel", "ffn_fused_kernel", "attention_tc_kernel", "gemm_f32_kernel",
+        "attention_f32_kernel", "gn_mish", "gn_stats_kernel", "layernorm_kernel", "final_proj_kernel", "pack_input",
+        "time_embed", "resample_mask_bf16_kernel")) and "2te" not in f]
+    assert len(decoder) >= 40, len(decoder)
+    for f in te + decoder:
+        assert wait[f] >= 1, f"{f}: launched with the PDL attribute but has no griddepcontrol.wait"
+        assert trigger[f] >= 1, f"{f}: no griddepcontrol.launch_dependents"
