@@ -9,6 +9,7 @@ module can be copied over 1:1 with ``load_state_dict``.  Inference / eval only (
 all arithmetic happens in ``lib/libmatcha_b200.so`` -- no CPU fallback.
 """
 import math
+import os
 from collections import OrderedDict
 from types import SimpleNamespace
 
@@ -122,6 +123,7 @@ class TextEncoder(torch.nn.Module):
         if precision not in _PRECISIONS:
             raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}")
         self.precision = precision
+        self.check_inputs = os.environ.get("MB200_CHECK_INPUTS", "0") == "1"    # validate ids / lengths like nn.Embedding (costs a sync)
         ep, dp = default_params()
         encoder_params = encoder_params or ep
         duration_predictor_params = duration_predictor_params or dp
@@ -233,6 +235,15 @@ class TextEncoder(torch.nn.Module):
         B, T = text_input.shape
         ids = text_input.to(torch.int64).contiguous()
         lens = text_lengths.to(dev, torch.int32).contiguous()
+        if self.check_inputs:
+            # nn.Embedding raises on ids outside [0, n_vocab) (text_encoder.py:377-379); the kernel clamps them instead, so a symbol
+            # table that does not match n_vocab would give plausible but wrong mu / logw.  This check reads two scalars back
+            # (one device synchronisation), hence a switch: check_inputs=True or MB200_CHECK_INPUTS=1.
+            lo, hi, lmax = int(ids.min()), int(ids.max()), int(lens.max())
+            if lo < 0 or hi >= self.vocab_size:
+                raise IndexError(f"token ids span [{lo}, {hi}] but n_vocab = {self.vocab_size} (index out of range in embedding)")
+            if lmax > T or int(lens.min()) < 0:
+                raise ValueError(f"text_lengths up to {lmax} exceed the padded length T = {T}")
         blob, blob16 = self._blob_on(dev), self._blob16_on(dev)
         cos, sin = self._rope_on(dev, T)
         prec = _PRECISIONS[self.precision]

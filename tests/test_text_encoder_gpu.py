@@ -102,6 +102,28 @@ def test_int32_ids_and_cpu_lengths(encoder):
     assert all(torch.equal(x, y) for x, y in zip(a, b))
 
 
+def test_check_inputs_raises_like_the_reference_embedding(encoder):
+    # nn.Embedding raises IndexError on an id outside [0, n_vocab) (text_encoder.py:377-379); the kernel clamps, so the
+    # Python mirror validates when asked to (check_inputs / MB200_CHECK_INPUTS=1)
+    ids = torch.zeros(2, 12, dtype=torch.int64)
+    lens = torch.tensor([12, 7])
+    encoder.check_inputs = True
+    try:
+        encoder(ids.cuda(), lens)                                       # in range: passes
+        bad = ids.clone(); bad[1, 3] = encoder.vocab_size
+        with pytest.raises(IndexError):
+            encoder(bad.cuda(), lens)
+        bad[1, 3] = -1
+        with pytest.raises(IndexError):
+            encoder(bad.cuda(), lens)
+        with pytest.raises(ValueError):
+            encoder(ids.cuda(), torch.tensor([13, 7]))
+    finally:
+        encoder.check_inputs = False
+    out = encoder(bad.cuda(), lens)                                     # default: clamped, no error (documented deviation)
+    assert all(bool(torch.isfinite(o).all()) for o in out)
+
+
 def test_c_abi_argument_checks(encoder):
     import ctypes
     from matcha_b200._lib import load_library
