@@ -67,6 +67,41 @@ def workload_name(a):
     return f"maximum_path B={a.batch}/GPU T_text={a.tx} T_mel={a.ty} ragged 0.7-1.0 (BASELINE configs[1])"
 
 
+def bench_config(a):
+    """The `config` object of the JSON line: the same dict in both arms (per-arm remarks live under `notes`)."""
+    gb = 2 * 4.0 * a.batch * a.tx * a.ty / 1e9
+    return {"workload": workload_name(a), "batch_per_gpu": a.batch, "T_text": a.tx, "T_mel": a.ty,
+            "l2": f"inputs+outputs {gb:.1f} GB per step >> 126 MB L2, no flush needed"}
+
+
+def bench_summary(line):
+    """Compact digest (< 600 characters) of every leg, emitted as the LAST key of the JSON line."""
+    def r(x, n=3):
+        return None if x is None else float(f"{x:.{n}g}")
+    sm = {"n": line["n_gpus"], "mas_Malign_s": r(line["value"] / 1e6), "mas_hbm_frac": r(line["roofline"]["frac"]),
+          "mas_e2e_kalign_s": r(line["e2e"]["value"] / 1e3)}
+    dec = line.get("cfm_decoder")
+    if dec:
+        bp = dec.get("by_precision", {})
+        sm["dec_ms"] = {k: r(v["ms_per_solve"]) for k, v in bp.items()}
+        sm["dec_frac"] = r(dec["roofline"]["frac"])
+        sm["dec_relL2"] = {k: r(v, 2) for k, v in (dec.get("rel_l2_vs_oracle") or {}).items()}
+        gb = dec.get("gpu_baseline", {}).get("speedup_ours_over_eager")
+        if gb:
+            sm["dec_vs_eager"] = {"fp32": r(gb["fp32_mode_vs_eager_fp32"]), "fp16_vs_bf16ac": r(gb["fp16_mode_vs_eager_bf16_autocast"])}
+    te = line.get("text_encoder")
+    if te:
+        sm["te_ms"] = {k: r(v["ms_per_forward"]) for k, v in te["modes"].items()}
+    tr = line.get("training_step")
+    if tr:
+        sm["train_utt_s"] = r(tr["value"])
+        sm["train_e2e_utt_s"] = r((tr.get("e2e") or {}).get("value"))
+    sy = line.get("synthesis")
+    if sy:
+        sm["synth_utt_s"] = {k.replace("n_timesteps_", "n"): r(v["utterances_per_sec"]) for k, v in sy["by_n_timesteps"].items()}
+    return sm
+
+
 def traffic_record(kernel, workload):
     """DRAM bytes per launch (or per solve) from the committed ncu --set full capture of THIS workload, else None.
     profiles/r2_traffic.json is preferred; profiles/r1_traffic.json is the round-1 capture (older kernel revision)."""
@@ -441,7 +476,7 @@ def decoder_leg(a, dev, world, rank, dist, barrier):
     mu = torch.randn(B, 80, T, device=dev, generator=g)
     z = torch.randn(B, 80, T, device=dev, generator=g)
     mask = torch.ones(B, 1, T, device=dev)
-    t_span = torch.linspace(0, 1, n + 1, device=dev)
+    t_span = torch.linspace(0, 1, n + 1, device=dev).cpu()      # host copy, read back once: what CFM.forward hands solve_ode_euler
     modes, outs, weights, launches = {}, {}, None, 0
     order = [a.dec_precision] + [p for p in ("fp32", "bf16", "fp16") if p != a.dec_precision]
     sampler = ClockSampler(dev.index or 0)
@@ -493,7 +528,7 @@ def decoder_leg(a, dev, world, rank, dist, barrier):
         from oracle import decoder as odec
         idx = sorted(set([0, B // 2, B - 1]))
         w64 = odec.cast_weights({k: v.to(dev) for k, v in weights.items()}, torch.float64)
-        want = odec.solve_euler(w64, z[idx].double(), t_span.cpu(), mu[idx].double(), mask[idx].double())
+        want = odec.solve_euler(w64, z[idx].double(), t_span, mu[idx].double(), mask[idx].double())
         for prec, o in outs.items():
             rel[prec] = float(torch.linalg.norm((o[idx].double() - want)) / torch.linalg.norm(want))
         del w64, want
@@ -548,29 +583,36 @@ def decoder_gpu_baseline(weights, z, t_span, mu, mask, flops, modes):
     old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32, odec.USE_SDPA)
     odec.USE_SDPA = True
     res = {"kind": "port", "what": "oracle/decoder.py (torch restatement pinned to the reference modules) on cuda through PyTorch eager, "
-                                   "attention via F.scaled_dot_product_attention(attn_mask=float); 1 warm-up + 2 timed solves, CUDA events"}
+                                   "attention via F.scaled_dot_product_attention(attn_mask=float)",
+           "timing": "same protocol as the library arm: 3 warm-up solves, better of two repeats of K solves (K = 2 for fp32, 5 otherwise), CUDA events"}
 
-    def timed(fn):
+    def timed(fn, K):
+        # the library arm's protocol (_time_solves): 3 warm-up solves, then the better of two repeats of K solves, CUDA events
         with torch.inference_mode():
-            fn(); torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(2):
+            for _ in range(3):
                 fn()
-            e1.record(); torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 2
-        return {"ms_per_solve": ms, "mel_frames_per_sec": B * T / (ms / 1e3), "tflops": flops / (ms / 1e3) / 1e12}
+            torch.cuda.synchronize()
+            ms = None
+            for _ in range(2):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(K):
+                    fn()
+                e1.record(); torch.cuda.synchronize()
+                t = e0.elapsed_time(e1) / K
+                ms = t if ms is None else min(ms, t)
+        return {"ms_per_solve": ms, "mel_frames_per_sec": B * T / (ms / 1e3), "tflops": flops / (ms / 1e3) / 1e12, "timed_solves": K}
 
     try:
         torch.backends.cuda.matmul.allow_tf32 = False; torch.backends.cudnn.allow_tf32 = False
-        res["eager_fp32_tf32_off"] = timed(lambda: odec.solve_euler(w, z, t_span.cpu(), mu, mask))
+        res["eager_fp32_tf32_off"] = timed(lambda: odec.solve_euler(w, z, t_span, mu, mask), modes["fp32"].get("timed_solves", 2))
         torch.backends.cuda.matmul.allow_tf32 = True; torch.backends.cudnn.allow_tf32 = True
-        res["eager_tf32"] = timed(lambda: odec.solve_euler(w, z, t_span.cpu(), mu, mask))
+        res["eager_tf32"] = timed(lambda: odec.solve_euler(w, z, t_span, mu, mask), 5)
 
         def bf16():
             with torch.autocast("cuda", dtype=torch.bfloat16):
-                return odec.solve_euler(w, z, t_span.cpu(), mu, mask)
-        res["eager_bf16_autocast"] = timed(bf16)
+                return odec.solve_euler(w, z, t_span, mu, mask)
+        res["eager_bf16_autocast"] = timed(bf16, 5)
     finally:
         torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32, odec.USE_SDPA = old
     res["speedup_ours_over_eager"] = {
@@ -872,9 +914,10 @@ def run_reference(a):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "batch_per_gpu": a.batch, "T_text": a.tx, "T_mel": a.ty,
-                   "sample_per_step": f"{a.batch} utterances on the host (the whole batch of our arm's step; a CPU has no ranks, "
-                                      f"so the value does not grow with --gpus)"},
+        "config": bench_config(a),
+        "notes": {"sample_per_step": f"{a.batch} utterances on the host (the whole batch of our arm's step; a CPU has no ranks, "
+                                     f"so the value does not grow with --gpus)",
+                  "inputs": "one block of min(B,128) N(0,1) utterances tiled to B (the DP's cost does not depend on the data); our arm draws B distinct ones"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": min(cores, a.batch), "kind": kind, "omp_threads_in_force": eff,
                          "sample": f"{a.batch} utterances per step, core.pyx compute_batch_alignments on numpy buffers, OpenMP prange over "
                                    f"the batch, {a.warmup} warm-up + mean of {a.steps} timed steps",
@@ -1063,9 +1106,8 @@ def run_ours(a):
             "metric": METRIC, "value": value_rate, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "batch_per_gpu": B, "T_text": T_x, "T_mel": T_y,
-                       "l2": "inputs+outputs 6.5 GB per step >> 126 MB L2, no flush needed",
-                       "launch": {"grid": out[0], "block": out[1], "smem": out[2], "rows_per_lane": out[3],
+            "config": bench_config(a),
+            "notes": {"launch": {"grid": out[0], "block": out[1], "smem": out[2], "rows_per_lane": out[3],
                                   "stages": out[4], "tma": out[5], "ctas_per_sm": out[6]},
                        "parallelism": (f"batch-sharded x{world}; every step all-gathers the alignment (compact: int32 durations) over NCCL, "
                                        + ("on a high-priority side stream under the next step's kernel" if os.environ.get("MB200_BENCH_GATHER", "overlap") == "overlap"
@@ -1130,6 +1172,7 @@ def run_ours(a):
             line["gpu_launches"] += 10 * (38 + 3 + 2 + 185)   # 10 timed steps: encoder, align kernels, loss kernels, one graph-replayed eval
         if synth is not None:
             line["synthesis"] = synth
+        line["summary"] = bench_summary(line)        # last key: a driver that keeps only the line's tail still sees every leg
         _emit(line)
     if world > 1:
         dist.destroy_process_group()

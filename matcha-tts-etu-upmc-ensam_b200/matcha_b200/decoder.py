@@ -120,6 +120,7 @@ class Decoder(torch.nn.Module):
         self._blob16 = {}             # device -> bf16 GEMM weights (bf16 mode)
         self._ws = {}                 # (device, B, T, rows) -> workspace of the plain-launch path (one shape kept)
         self._graphs = OrderedDict()      # captured Euler solves, LRU; every entry OWNS its workspace and I/O tensors
+        self._grids = {}                  # (t_k, dt_k) per host t_span, so a repeated solve does no tensor arithmetic on the host
         self._fwd_graphs = OrderedDict()  # captured single evals (forward), LRU, same ownership
         self._fwd_seen = {}           # forward() shapes seen once: captured only when they come back
         self.graph_cache_size = 4     # shapes kept per cache
@@ -315,7 +316,14 @@ class Decoder(torch.nn.Module):
         lib = load_library()
         B, _, T = x.shape
         dev = x.device
-        ts, dts = euler_time_grid(t_span.detach().to("cpu", torch.float32))
+        # a host t_span (what CFM.forward passes) costs nothing here; a device one is read back, which synchronises the device
+        tkey = tuple(t_span.tolist()) if not t_span.is_cuda else None
+        grid = self._grids.get(tkey) if tkey is not None else None
+        if grid is None:
+            grid = euler_time_grid(t_span.detach().to("cpu", torch.float32))
+            if tkey is not None and len(self._grids) < 64:
+                self._grids[tkey] = grid
+        ts, dts = grid
         n = len(ts)
         if use_graph is None:
             use_graph = self.use_graph

@@ -28,8 +28,17 @@ class BaseConditionalFlowMatching(torch.nn.Module):
     @torch.inference_mode()
     def forward(self, mu, mask, n_timesteps, temperature=1.0, spks=None, cond=None):
         z = torch.randn_like(mu) * temperature                                    # flow_matching.py:59
-        t_span = torch.linspace(0, 1, n_timesteps + 1, device=mu.device)          # :62
-        return self.solve_ode_euler(z, t_span, mu, mask, spks, cond)
+        return self.solve_ode_euler(z, self._host_t_span(n_timesteps, mu.device), mu, mask, spks, cond)
+
+    def _host_t_span(self, n_timesteps, device):
+        """torch.linspace(0, 1, n + 1, device=mu.device) (:62), read back ONCE per (n, device) and kept on the host: the C entry
+        point takes the (t_k, dt_k) grid as host floats, so handing solve_euler a device tensor costs a device synchronisation
+        on every call (one pipeline bubble per synthesised batch)."""
+        key = (int(n_timesteps), str(device))
+        cache = self.__dict__.setdefault("_t_span_host", {})
+        if key not in cache:
+            cache[key] = torch.linspace(0, 1, n_timesteps + 1, device=device).to("cpu", torch.float32)
+        return cache[key]
 
     def solve_ode_euler(self, x, t_span, mu, mask, spks, cond):
         return self.estimator.solve_euler(x, t_span, mu, mask)                    # :67-104 in one call
