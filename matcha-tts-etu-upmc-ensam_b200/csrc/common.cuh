@@ -149,15 +149,20 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 // grid's own wait, after everything before it), but it only promises VISIBILITY of the prerequisite grid's writes: a CTA that
 // was made resident while kernel N still ran can find, in its SM's L1, a line kernel N read there and kernel N+1 or N+2 has
 // since rewritten.  The text encoder's small kernels hit exactly that on two of six boxes (profiles/r2_te_pdl_race.log) and
-// therefore use the other order plus ld.global.cg loads (csrc/text_encoder.cu).  The decoder's chain is protected by its
-// shape: the kernels that read a re-written buffer with plain loads (A-building GEMMs, fused feed-forward) own their SM's
-// shared memory (~200 KB), so a waiting successor and the earlier reader are never on the same SM, and every other operand
-// arrives by TMA (L2).  MB200_PDL_SAFE = 1 compiles the conservative order into the decoder kernels too: a CTA lets the
+// therefore use the other order plus ld.global.cg loads (csrc/text_encoder.cu).  The decoder's tensor-core chain reads every
+// re-written activation through L2 as well: operands by TMA, and the residual / A-build inputs of gemm_bf16, gemm_abuild and
+// ffn_fused by ld.global.cg (ld_chain4, round 3).  Until round 3 those were plain loads and the chain leaned on its shape (the
+// readers take ~200 KB of shared memory, so a waiting successor and the earlier reader never shared an SM) -- an argument
+// that two CTAs per SM would have voided.  MB200_PDL_SAFE = 1 compiles the conservative order into the decoder kernels too: a CTA lets the
 // successor be scheduled only after its own wait has returned (at most two grids of a chain in flight).  Measured on one box
 // (profiles/r2_pdl_order_ab.log): B=32 solve 8.97 -> 9.25 ms (+3 %), B=8 6.61 -> 6.27 ms (-5 %), B=64 15.84 -> 15.73 ms.
 #ifndef MB200_PDL_SAFE
 #define MB200_PDL_SAFE 0
 #endif
+// Loads of a tensor that an earlier kernel of a PDL chain wrote (and that a later one rewrites): through L2 only.  A CTA that
+// became resident while an older grid still ran may share its SM's L1 with that grid's reads; ld.global.cg never looks there,
+// so correctness does not rest on "the reader owns its SM" (1 CTA/SM by shared-memory footprint) any more.
+__device__ __forceinline__ float4 ld_chain4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
 __device__ __forceinline__ void pdl_entry() {            // kernels whose every thread waits at the top
 #if MB200_PDL_SAFE
     pdl_wait();

@@ -267,7 +267,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const float *x1p = g.res + ((size_t)b * g.T + (ok ? tq + lane : 0)) * kC + cg * 64;
             float4 rv[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) rv[i] = ok ? *reinterpret_cast<const float4 *>(x1p + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = 0; i < 8; ++i) rv[i] = ok ? ld_chain4(x1p + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
             if (dbg && threadIdx.x == 64) g_ffn_dbg[4] = clock64();
             mbar_wait_parked(bar_g0, 0, 200);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -289,7 +289,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
                 if (hh == 0) {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) rv[i] = ok ? *reinterpret_cast<const float4 *>(x1p + 32 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int i = 0; i < 8; ++i) rv[i] = ok ? ld_chain4(x1p + 32 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
                 tmem_st32(tmem_acc2 + cg * 64 + hh * 32 + lane_off, v);
                 const float m = sum * (1.0f / 32.0f);
@@ -363,8 +363,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const int rt = rt0 + (r & 31);
                     const bool ok = rt < g.T;
                     const float *px = g.ln_in + ((size_t)rb * g.T + (ok ? rt : 0)) * kC;
-                    xa[j] = ok ? *reinterpret_cast<const float4 *>(px + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    xb[j] = ok ? *reinterpret_cast<const float4 *>(px + 128 + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    xa[j] = ok ? ld_chain4(px + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    xb[j] = ok ? ld_chain4(px + 128 + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -462,7 +462,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int n = cg * 64 + jj * 32 + c4;
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                rv[i] = orow[i] >= 0 ? ld_chain4(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
         };
         if (!OUTPROJ) load_res(0);                            // in flight while the last FFN2 chunks complete
         else {

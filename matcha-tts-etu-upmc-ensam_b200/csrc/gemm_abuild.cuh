@@ -189,11 +189,11 @@ gemm_abuild_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
                     const bool ok = i < AROWS && t >= 0 && t < g.T;
                     const size_t row = (size_t)b * g.T + (ok ? t : 0);
                     mk[set][j] = ok ? g.mask[(size_t)b * g.mask_T + t] : 0.f;
-                    v0[set][j] = ok ? *reinterpret_cast<const float4 *>(g.h + row * kC + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    v1[set][j] = ok ? *reinterpret_cast<const float4 *>(g.h + row * kC + c1) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v0[set][j] = ok ? ld_chain4(g.h + row * kC + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v1[set][j] = ok ? ld_chain4(g.h + row * kC + c1) : make_float4(0.f, 0.f, 0.f, 0.f);
                     if (MODE == 1) {
-                        r0[set][j] = ok ? *reinterpret_cast<const float4 *>(g.r + row * kC + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
-                        r1[set][j] = ok ? *reinterpret_cast<const float4 *>(g.r + row * kC + c1) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        r0[set][j] = ok ? ld_chain4(g.r + row * kC + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        r1[set][j] = ok ? ld_chain4(g.r + row * kC + c1) : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
             };

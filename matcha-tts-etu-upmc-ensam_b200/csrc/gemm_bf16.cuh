@@ -434,7 +434,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const int n = ncol0 + 32 * jj + c4;
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
-                        rv[i] = orow[i] >= 0 ? *reinterpret_cast<const float4 *>(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        rv[i] = orow[i] >= 0 ? ld_chain4(g.res + orow[i] + n) : make_float4(0.f, 0.f, 0.f, 0.f);
                 };
                 if (RES) load_res(jhalf);
                 uint32_t v[2][32];                               // TMEM chunk j+1 is in flight while chunk j is processed

@@ -160,6 +160,25 @@ def test_b32_t800_n10_slices_vs_fp64_oracle(w64, cfms, precision):
     assert err < TOL[precision] and err2 < TOL[precision]
 
 
+@pytest.mark.parametrize("precision", ["fp16", "fp32"])
+def test_replayed_b32_solves_are_bit_identical(cfms, precision):
+    """Stress for the programmatic-dependent-launch chain (round-2 review): the bench configuration (B = 32, T = 800, n = 10,
+    four sub-batch streams, graph replay) solved over and over must return the very same bits every time.  A kernel that
+    reads a chain-written tensor before its prerequisite has flushed it, or out of a stale L1 line, shows up as a replay
+    that differs on some box (the text encoder's first PDL build did, profiles/r2_te_pdl_race.log)."""
+    g = torch.Generator().manual_seed(4242)
+    lengths = [800] + [int(800 * (0.7 + 0.3 * float(torch.rand((), generator=g)))) for _ in range(31)]
+    z, mu, mask = inputs(4242, 32, 800, lengths)
+    t_span = torch.linspace(0, 1, 11)
+    n_rep = 200 if precision == "fp16" else 12                 # ~9 ms and ~150 ms per solve
+    first = cfms[precision].solve_ode_euler(z, t_span, mu, mask, None, None).clone()
+    assert bool(torch.isfinite(first).all())
+    differing = 0
+    for _ in range(n_rep):
+        differing += int(not torch.equal(cfms[precision].solve_ode_euler(z, t_span, mu, mask, None, None), first))
+    assert differing == 0, f"{differing} of {n_rep} replays differ from the first solve"
+
+
 def test_graph_replay_survives_other_shapes(cfms):
     """A cached graph owns its workspace: plain launches and captures of other shapes in between must not disturb a
     later replay (round-1 bug: the shared workspace was freed while a graph still pointed at it)."""

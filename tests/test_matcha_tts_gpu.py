@@ -97,6 +97,52 @@ def test_training_forward_values_match_oracle_composition(weights):
     assert abs(float(diff) - float(odiff)) < 2e-5 * abs(float(odiff))
 
 
+@pytest.mark.parametrize("data", ["aligned", "random"])
+def test_fp16_training_forward_against_oracle_composition(weights, data):
+    """The benchmarked training step runs the fp16 tensor-core encoder and decoder (bench.py training_step); this is its
+    end-to-end check against the fp32 oracle composition of matcha_tts.py:271-322.  mu_x moves by ~3e-4 in fp16 mode, so MAS
+    may legitimately pick a different token for some frames; the test reports that fraction and bounds it, and bounds the three
+    losses.  "aligned": y is mu_x stretched along a random monotone alignment plus noise (what training data looks like once
+    the encoder has learnt something); "random": y is pure noise, the flattest score landscape MAS can be given."""
+    we, wd = weights
+    model = build(weights, "fp16")
+    g = torch.Generator().manual_seed(7)
+    B, T_x, T_y = 6, 48, 320
+    x = torch.randint(0, N_VOCAB, (B, T_x), generator=g)
+    x_lengths = torch.tensor([48, 44, 40, 33, 25, 12])
+    y_lengths = torch.tensor([320, 300, 251, 200, 163, 90])
+    mu_x, logw, x_mask = oenc.text_encoder_forward(we, x, x_lengths)
+    y = torch.randn(B, 80, T_y, generator=g)
+    if data == "aligned":
+        for b in range(B):
+            tx, ty = int(x_lengths[b]), int(y_lengths[b])
+            cuts = torch.sort(torch.randperm(ty - 1, generator=g)[:tx - 1] + 1).values
+            tok = torch.bucketize(torch.arange(ty), cuts, right=True)           # frame -> token, monotone, every token used
+            y[b, :, :ty] = mu_x[b][:, tok] + 0.3 * y[b, :, :ty]
+    t, z = torch.rand(B, 1, 1, generator=g), torch.randn(B, 80, T_y, generator=g)
+    dur, prior, diff, attn = model(x.cuda(), x_lengths.cuda(), y.cuda(), y_lengths.cuda(), t=t.cuda(), z=z.cuda())
+    y_mask = oal.sequence_mask(y_lengths, T_y).unsqueeze(1).float()
+    oattn = oal.maximum_path(oal.log_prior(mu_x, y), (x_mask.unsqueeze(-1) * y_mask.unsqueeze(2)).squeeze(1))
+    logw_ = torch.log(1e-8 + torch.sum(oattn.unsqueeze(1), -1)) * x_mask
+    odur = torch.sum((logw - logw_) ** 2) / torch.sum(x_lengths)
+    mu_y = torch.matmul(oattn.transpose(1, 2), mu_x.transpose(1, 2)).transpose(1, 2)
+    oprior = torch.sum(0.5 * ((y - mu_y) ** 2 + math.log(2 * math.pi)) * y_mask) / (torch.sum(y_mask) * 80)
+    odiff, _ = odec.compute_loss(wd, y, y_mask, mu_y, t, z)
+    got = attn.cpu()
+    assert torch.equal(got.sum(1), y_mask.squeeze(1))                           # still a valid alignment: one token per valid frame
+    frames_moved = float(((got.argmax(1) != oattn.argmax(1)) & (y_mask.squeeze(1) > 0)).sum() / y_mask.sum())
+    rel = [abs(float(a) - float(b)) / abs(float(b)) for a, b in ((dur, odur), (prior, oprior), (diff, odiff))]
+    print(f"fp16 training step [{data}]: frames with another token {frames_moved:.4f}; rel. error dur {rel[0]:.2e} prior {rel[1]:.2e} diff {rel[2]:.2e}")
+    assert frames_moved <= FP16_STEP_TOL[data]["frames"]
+    assert rel[0] <= FP16_STEP_TOL[data]["dur"] and rel[1] <= FP16_STEP_TOL[data]["prior"] and rel[2] <= FP16_STEP_TOL[data]["diff"]
+
+
+# tolerances of the fp16 training step against the fp32 oracle composition.  Measured on B200 (profiles/r3_fp16_training_step.log):
+# aligned: 0 frames moved, dur 2.6e-5, prior 6e-8, diff 4.7e-5;  random: 0.23 % of frames moved, dur 2.2e-3, prior 2.1e-5, diff 6.0e-5
+FP16_STEP_TOL = {"aligned": {"frames": 0.005, "dur": 1e-3, "prior": 1e-4, "diff": 1e-3},
+                 "random": {"frames": 0.02, "dur": 2e-2, "prior": 5e-4, "diff": 1e-3}}
+
+
 def test_training_forward_with_out_size_cut(weights):
     """matcha_tts.py:290-312: the random segment cut.  The offsets come from Python's `random` in the reference's order, so the
     oracle composition re-seeds it and draws the same ones."""
